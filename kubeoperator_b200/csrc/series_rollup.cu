@@ -1,0 +1,1139 @@
+// Window statistics over columnar f64 series: sum / count / mean / min / max / last + exact nearest-rank
+// quantiles.  BUILD-DEFINED semantics (oracle/rollup_oracle.py series_stats); the reference only ships
+// PromQL strings for this (core/apps/kubeops_api/prometheus_client.py:90-111), see include/korollup.h.
+//
+// HBM-bound: 8 algorithmic bytes per sample, read once.  Three kernels per call:
+//   classify_series   — builds the work list of long series (scratch) and validates offsets
+//   series_small      — one warp per series of <= 1024 samples (coalesced streaming loads, shuffle
+//                       reductions, warp-private shared-memory radix select for quantiles)
+//   series_long       — persistent CTAs, one series at a time per CTA: a producer warp streams the series
+//                       through a 4-stage TMA ring (cp.async.bulk + mbarrier) while 8 consumer warps
+//                       fuse the statistics with a bracketed selection: a strided pre-sample (sorted in
+//                       shared memory) gives a value bracket per quantile; the single streaming pass counts
+//                       samples below each bracket and captures the few inside it into shared memory,
+//                       where a shared-memory radix select finds the exact order statistic.  Brackets
+//                       that miss or overflow are refined by further passes (histogram in key space),
+//                       so the result is always exact.
+#include <math.h>
+
+#include "ko_common.cuh"
+
+namespace {
+
+constexpr int SMALL_MAX = 1024;      // series up to this length take the warp path
+constexpr int NCONS = 256;           // consumer threads of series_long
+constexpr int NCWARPS = NCONS / 32;
+constexpr int NTHREADS = NCONS + 32; // + one producer warp
+constexpr int TILE = 1024;           // doubles per ring stage (8 KB)
+constexpr int STAGES = 4;
+constexpr int SAMPLE_BIG = 1024;     // pre-sample size for L >= 8192
+constexpr int SAMPLE_SMALL = 256;    // pre-sample size for shorter long series
+constexpr int SLOTS = 32;            // thread-private candidate slots per consumer thread
+constexpr int OVQ = 1024;            // shared overflow queue entries
+constexpr int NI_MAX = KO_MAX_QUANTILES;
+constexpr int HBINS = 256;
+constexpr double CSIG = 3.0;         // bracket half width in binomial sigmas of the pre-sample
+
+enum { M_COUNT = 0, M_CAPTURE = 1, M_HIST = 2 };
+enum { A_NONE = 0, A_SELECT = 1 };
+
+struct SeriesArgs {
+    const double* values;
+    const int64_t* offsets;
+    int64_t n_series;
+    double* out_sum;
+    double* out_mean;
+    double* out_min;
+    double* out_max;
+    double* out_last;
+    int64_t* out_count;
+    double* out_quant;
+    int* counters;  // [0] n_long  [1] work cursor  [2] error flag  [3] series needing extra passes
+    int* long_list;
+    int nq;
+    double q[NI_MAX];   // ascending
+    int qcol[NI_MAX];   // output column of q[j]
+};
+
+struct Plan {
+    int ni;
+    int mode[NI_MAX];
+    int hshift[NI_MAX];
+    int slot0[NI_MAX], nslots[NI_MAX];
+    int ov0[NI_MAX], ovcap[NI_MAX];
+    unsigned long long kA[NI_MAX], kB[NI_MAX];
+    double tA[NI_MAX], tB[NI_MAX];
+    // per quantile
+    int q_iv[NI_MAX];
+    int q_done[NI_MAX];
+    int q_act[NI_MAX];
+    unsigned q_rho[NI_MAX];
+    double q_val[NI_MAX];
+    // pass results
+    unsigned cA[NI_MAX];
+    unsigned nin[NI_MAX];
+    unsigned ovcnt[NI_MAX];
+    int more;
+    int passes;
+    unsigned nvalid;
+    int sample_valid;
+    double sum, mn, mx, last;
+    // radix select scratch
+    int sel_digit;
+    unsigned sel_cum, sel_cnt;
+    unsigned long long sel_key;
+    int work;
+};
+
+// ------------------------------------------------------------------------------------------------ PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "KO_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra KO_DONE;\n"
+        "bra KO_WAIT;\n"
+        "KO_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory"); }
+
+__device__ __forceinline__ unsigned nearest_rank_dev(unsigned n, double q) {
+    double r = ceil(q * (double)n);
+    if (!(r >= 1.0)) r = 1.0;
+    if (r > (double)n) r = (double)n;
+    return (unsigned)r;
+}
+
+// ------------------------------------------------------------------------------------ classify kernel
+__global__ void classify_series(SeriesArgs a) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n_series) return;
+    int64_t L = a.offsets[i + 1] - a.offsets[i];
+    if (L < 0 || L >= 2147483647LL) {
+        atomicExch(&a.counters[2], 1);
+        return;
+    }
+    if (L > SMALL_MAX) {
+        int pos = atomicAdd(&a.counters[0], 1);
+        a.long_list[pos] = (int)i;
+    }
+}
+
+// ------------------------------------------------------------------------------- warp path (<= 1024)
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_min(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ unsigned warp_sum_u(unsigned v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Locate the digit whose cumulative count first reaches rho.  Called by one full warp on a 256-bin
+// histogram; returns (digit, count before the digit, count of the digit) in every lane.
+__device__ __forceinline__ void warp_find_digit(const unsigned* hist, unsigned rho, int lane, int& digit,
+                                                unsigned& before, unsigned& cnt) {
+    unsigned c[8];
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        c[i] = hist[lane * 8 + i];
+        s += c[i];
+    }
+    unsigned incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    unsigned ballot = __ballot_sync(0xffffffffu, incl >= rho);
+    int src = ballot ? (__ffs(ballot) - 1) : 31;
+    int d = 0;
+    unsigned b = 0, n = 0;
+    if (lane == src) {
+        unsigned run = incl - s;
+        d = 7;
+        n = c[7];
+        b = run + (s - c[7]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (run + c[i] >= rho) {
+                d = i;
+                b = run;
+                n = c[i];
+                break;
+            }
+            run += c[i];
+        }
+        d += lane * 8;
+    }
+    digit = __shfl_sync(0xffffffffu, d, src);
+    before = __shfl_sync(0xffffffffu, b, src);
+    cnt = __shfl_sync(0xffffffffu, n, src);
+}
+
+// MSB-first radix select over keys[0..n) held in shared memory by ONE warp; NaN keys are skipped.
+// kmin/kmax bound the valid keys, so the digits above their first difference are skipped.
+__device__ unsigned long long warp_radix_select(const unsigned long long* keys, int n, unsigned rho,
+                                                unsigned long long kmin, unsigned long long kmax,
+                                                unsigned* hist, int lane) {
+    unsigned long long diff = kmin ^ kmax;
+    if (diff == 0) return kmin;
+    int top = 63 - __clzll((long long)diff);
+    int shift = (top >> 3) << 3;
+    unsigned long long mask = (shift + 8 >= 64) ? 0ull : (~0ull << (shift + 8));
+    unsigned long long prefix = kmin & mask;
+    for (;;) {
+        for (int i = lane; i < HBINS; i += 32) hist[i] = 0;
+        __syncwarp();
+        for (int i = lane; i < n; i += 32) {
+            unsigned long long k = keys[i];
+            if (k != KO_KEY_NAN && (k & mask) == prefix) atomicAdd(&hist[(unsigned)(k >> shift) & 255u], 1u);
+        }
+        __syncwarp();
+        int digit;
+        unsigned before, cnt;
+        warp_find_digit(hist, rho, lane, digit, before, cnt);
+        __syncwarp();
+        rho -= before;
+        prefix |= (unsigned long long)digit << shift;
+        mask |= 0xFFull << shift;
+        if (shift == 0) return prefix;
+        shift -= 8;
+    }
+}
+
+__global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_small[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t sid = (int64_t)blockIdx.x * 8 + warp;
+    if (sid >= a.n_series) return;
+    const int64_t off0 = a.offsets[sid];
+    const int64_t Ll = a.offsets[sid + 1] - off0;
+    if (Ll > SMALL_MAX || Ll < 0) return;
+    const int L = (int)Ll;
+    const double* v = a.values + off0;
+    unsigned long long* keys = nullptr;
+    unsigned* hist = nullptr;
+    if (a.nq > 0) {
+        keys = reinterpret_cast<unsigned long long*>(smem_small) + (size_t)warp * SMALL_MAX;
+        hist = reinterpret_cast<unsigned*>(smem_small + (size_t)8 * SMALL_MAX * 8) + warp * HBINS;
+    }
+    double sum = 0.0, mn = INFINITY, mx = -INFINITY;
+    unsigned nv = 0;
+    int last_idx = -1;
+    for (int i = lane; i < L; i += 32) {
+        double x = ko_ld_stream(v + i);
+        bool ok = (x == x);
+        if (ok) {
+            sum += x;
+            nv++;
+            last_idx = i;
+        }
+        mn = fmin(mn, x);
+        mx = fmax(mx, x);
+        if (keys) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
+    }
+    sum = warp_sum(sum);
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    nv = warp_sum_u(nv);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) last_idx = max(last_idx, __shfl_xor_sync(0xffffffffu, last_idx, o));
+    if (lane == 0) {
+        const double nan = __longlong_as_double(0x7FF8000000000000LL);
+        if (a.out_sum) a.out_sum[sid] = sum;
+        if (a.out_mean) a.out_mean[sid] = nv > 0 ? sum / (double)nv : 0.0;
+        if (a.out_min) a.out_min[sid] = nv > 0 ? mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = nv > 0 ? mx + 0.0 : nan;
+        if (a.out_last) a.out_last[sid] = last_idx >= 0 ? v[last_idx] : nan;
+        if (a.out_count) a.out_count[sid] = (int64_t)nv;
+    }
+    if (a.nq > 0 && a.out_quant) {
+        __syncwarp();
+        const unsigned long long kmin = ko_okey(mn + 0.0), kmax = ko_okey(mx + 0.0);
+        for (int j = 0; j < a.nq; ++j) {
+            double r = __longlong_as_double(0x7FF8000000000000LL);
+            if (nv > 0) {
+                unsigned rho = nearest_rank_dev(nv, a.q[j]);
+                r = ko_key2d(warp_radix_select(keys, L, rho, kmin, kmax, hist, lane));
+            }
+            if (lane == 0) a.out_quant[sid * a.nq + a.qcol[j]] = r;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------ CTA path (> 1024)
+struct LongSmem {
+    double* ring;                 // STAGES * TILE
+    unsigned char* pool;          // SLOTS * NCONS * 8 bytes; aliased by the pre-sample keys
+    double* ovq;                  // OVQ
+    unsigned* hist;               // NI_MAX * HBINS
+    unsigned* selhist;            // HBINS
+    double* red;                  // NCWARPS * 4
+    Plan* plan;
+    uint64_t* full;               // STAGES
+    uint64_t* empty;              // STAGES
+};
+
+constexpr size_t LONG_SMEM_BYTES = (size_t)STAGES * TILE * 8 + (size_t)SLOTS * NCONS * 8 + (size_t)OVQ * 8 +
+                                   (size_t)NI_MAX * HBINS * 4 + (size_t)HBINS * 4 + (size_t)NCWARPS * 4 * 8 +
+                                   1024 /* Plan */ + (size_t)2 * STAGES * 8;
+static_assert(sizeof(Plan) <= 1024, "Plan must fit its shared-memory slot");
+
+struct Acc {
+    double sum, mn, mx;
+    unsigned nvalid;
+    unsigned cA[NI_MAX];
+    unsigned cin[NI_MAX];
+    uint32_t p[NI_MAX];     // next free private slot (byte offset into pool)
+    uint32_t pend[NI_MAX];
+};
+
+template <int NI, bool STATS>
+__device__ __forceinline__ void process_elem(double x, Acc& acc, const double (&tA)[NI_MAX],
+                                             const double (&tB)[NI_MAX], const LongSmem& sm) {
+    if (STATS) {
+        if (x == x) {
+            acc.sum += x;
+            acc.nvalid++;
+        }
+        acc.mn = fmin(acc.mn, x);
+        acc.mx = fmax(acc.mx, x);
+    }
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+        const bool lt = x < tA[i];
+        acc.cA[i] += lt ? 1u : 0u;
+        const bool in = !lt && (x < tB[i]);
+        if (in) {
+            const Plan* pl = sm.plan;
+            const int mode = pl->mode[i];
+            const double xc = x + 0.0;
+            if (mode == M_CAPTURE) {
+                if (acc.p[i] != acc.pend[i]) {
+                    *reinterpret_cast<double*>(sm.pool + acc.p[i]) = xc;
+                    acc.p[i] += NCONS * 8;
+                } else {
+                    unsigned pos = atomicAdd(&sm.plan->ovcnt[i], 1u);
+                    if (pos < (unsigned)pl->ovcap[i]) sm.ovq[pl->ov0[i] + pos] = xc;
+                }
+            } else if (mode == M_HIST) {
+                unsigned long long k = ko_okey(xc);
+                unsigned b = (unsigned)((k - pl->kA[i]) >> pl->hshift[i]);
+                atomicAdd(&sm.hist[i * HBINS + b], 1u);
+            } else {
+                acc.cin[i]++;
+            }
+        }
+    }
+}
+
+template <int NI, bool STATS>
+__device__ __forceinline__ void consume_pass(const double* __restrict__ v, int L, int head, int body, int ntiles, uint32_t g,
+                             Acc& acc, const LongSmem& sm, int ctid, int lane) {
+    double tA[NI_MAX], tB[NI_MAX];
+#pragma unroll
+    for (int i = 0; i < NI_MAX; ++i) {
+        tA[i] = (i < NI) ? sm.plan->tA[i] : 0.0;
+        tB[i] = (i < NI) ? sm.plan->tB[i] : 0.0;
+    }
+    // unaligned head / tail element (the TMA body starts 16-byte aligned and has an even length)
+    if (ctid == 0 && head) process_elem<NI, STATS>(v[0], acc, tA, tB, sm);
+    if (ctid == 1 && head + body < L) process_elem<NI, STATS>(v[L - 1], acc, tA, tB, sm);
+    for (int t = 0; t < ntiles; ++t) {
+        const uint32_t gg = g + (uint32_t)t;
+        const int s = (int)(gg % STAGES);
+        mbar_wait(&sm.full[s], (gg / STAGES) & 1u);
+        const double2* st = reinterpret_cast<const double2*>(sm.ring + (size_t)s * TILE);
+        const int n2 = min(TILE, body - t * TILE) >> 1;  // double2 elements in this tile
+#pragma unroll
+        for (int h = 0; h < TILE / 2 / NCONS; ++h) {
+            const int idx = h * NCONS + ctid;
+            if (idx < n2) {
+                const double2 d = st[idx];
+                process_elem<NI, STATS>(d.x, acc, tA, tB, sm);
+                process_elem<NI, STATS>(d.y, acc, tA, tB, sm);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[s]);
+    }
+}
+
+template <bool STATS>
+__device__ __forceinline__ void consume_dispatch(int ni, const double* v, int L, int head, int body, int ntiles,
+                                                 uint32_t g, Acc& acc, const LongSmem& sm, int ctid, int lane) {
+    switch (ni) {
+        case 0: consume_pass<0, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 1: consume_pass<1, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 2: consume_pass<2, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 3: consume_pass<3, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        default: consume_pass<4, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+    }
+}
+
+// Bitonic sort of n (power of two, <= 1024) u64 keys in shared memory by the consumer threads.
+__device__ void bitonic_sort_keys(unsigned long long* keys, int n, int ctid) {
+    for (int k = 2; k <= n; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int t = ctid; t < n / 2; t += NCONS) {
+                // t-th compare-exchange of this stage: insert a zero bit at position log2(j)
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const int ixj = i | j;
+                const unsigned long long x = keys[i], y = keys[ixj];
+                const bool up = ((i & k) == 0);
+                if ((x > y) == up) {
+                    keys[i] = y;
+                    keys[ixj] = x;
+                }
+            }
+            cons_sync();
+        }
+    }
+}
+
+// CTA-wide MSB-first radix select over the captured candidates of interval iv (thread-private slots plus
+// overflow queue).  All candidates have keys in [kA, kB).  Returns the key of local rank rho (1-based).
+__device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsigned rho, uint32_t p0,
+                                               uint32_t pcur, int ctid, int lane) {
+    Plan* pl = sm.plan;
+    const unsigned long long kA = pl->kA[iv], kB = pl->kB[iv];
+    const unsigned long long diff = kA ^ (kB - 1);
+    if (diff == 0) return kA;
+    const int top = 63 - __clzll((long long)diff);
+    int shift = (top >> 3) << 3;
+    unsigned long long mask = (shift + 8 >= 64) ? 0ull : (~0ull << (shift + 8));
+    unsigned long long prefix = kA & mask;
+    const int ovn = (int)min(pl->ovcnt[iv], (unsigned)pl->ovcap[iv]);
+    const double* ovq = sm.ovq + pl->ov0[iv];
+    for (;;) {
+        sm.selhist[ctid] = 0;
+        cons_sync();
+        for (uint32_t p = p0; p != pcur; p += NCONS * 8) {
+            unsigned long long k = ko_okey(*reinterpret_cast<const double*>(sm.pool + p));
+            if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+        }
+        for (int i = ctid; i < ovn; i += NCONS) {
+            unsigned long long k = ko_okey(ovq[i]);
+            if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+        }
+        cons_sync();
+        if (ctid < 32) {
+            int digit;
+            unsigned before, cnt;
+            warp_find_digit(sm.selhist, rho, lane, digit, before, cnt);
+            if (lane == 0) {
+                pl->sel_digit = digit;
+                pl->sel_cum = before;
+                pl->sel_cnt = cnt;
+            }
+        }
+        cons_sync();
+        rho -= pl->sel_cum;
+        prefix |= (unsigned long long)pl->sel_digit << shift;
+        mask |= 0xFFull << shift;
+        const unsigned cnt = pl->sel_cnt;
+        if (shift == 0) return prefix;
+        if (cnt == 1) {  // a single candidate carries this prefix: fetch it
+            for (uint32_t p = p0; p != pcur; p += NCONS * 8) {
+                unsigned long long k = ko_okey(*reinterpret_cast<const double*>(sm.pool + p));
+                if ((k & mask) == prefix) pl->sel_key = k;
+            }
+            for (int i = ctid; i < ovn; i += NCONS) {
+                unsigned long long k = ko_okey(ovq[i]);
+                if ((k & mask) == prefix) pl->sel_key = k;
+            }
+            cons_sync();
+            return pl->sel_key;
+        }
+        shift -= 8;
+    }
+}
+
+__device__ __forceinline__ int hist_shift(unsigned long long kA, unsigned long long kB) {
+    unsigned long long span = kB - kA - 1;  // kB > kA
+    if (span < 256) return 0;
+    int top = 63 - __clzll((long long)span);
+    return top - 7;
+}
+
+// Thread 0: derive the brackets of the first pass from the sorted pre-sample.
+__device__ void build_first_plan(Plan* pl, const unsigned long long* skeys, int s, int valid_s, int L,
+                                 const SeriesArgs& a) {
+    const int nq = a.nq;
+    int lo[NI_MAX], hi[NI_MAX];
+    int ni = 0;
+    for (int j = 0; j < nq; ++j) {
+        int aj = -1, bj = valid_s;
+        if (valid_s > 0) {
+            const double q = a.q[j];
+            const double pos = q * (double)valid_s;
+            const double sig = sqrt(fmax(q * (1.0 - q), 0.0) * (double)valid_s);
+            const int m = (int)ceil(CSIG * sig) + 2;
+            aj = (int)floor(pos) - m - 1;
+            bj = (int)ceil(pos) + m;
+            if (aj < 0) aj = -1;
+            if (bj > valid_s) bj = valid_s;
+        }
+        const int gap = valid_s / 32;
+        if (ni > 0 && aj <= hi[ni - 1] + gap) {  // merge with the previous bracket
+            if (bj > hi[ni - 1]) hi[ni - 1] = bj;
+            if (aj < lo[ni - 1]) lo[ni - 1] = aj;
+        } else {
+            lo[ni] = aj;
+            hi[ni] = bj;
+            ni++;
+        }
+        pl->q_iv[j] = ni - 1;
+        pl->q_done[j] = 0;
+        pl->q_act[j] = A_NONE;
+    }
+    if (nq == 0) {
+        pl->ni = 0;
+        return;
+    }
+    pl->ni = ni;
+    int need[NI_MAX];
+    int total = 0;
+    for (int i = 0; i < ni; ++i) {
+        const bool lower_open = lo[i] < 0, upper_open = hi[i] >= valid_s;
+        unsigned long long kA = lower_open ? KO_KEY_NINF : skeys[lo[i]];
+        unsigned long long kB;
+        if (upper_open) kB = KO_KEY_PINF;
+        else {
+            unsigned long long kh = skeys[hi[i]];
+            kB = (kh >= KO_KEY_PINF) ? KO_KEY_PINF : kh + 1;
+        }
+        int mode = M_CAPTURE;
+        if (!lower_open && !upper_open && skeys[lo[i]] == skeys[hi[i]]) mode = M_COUNT;  // one tie group
+        if (kB <= kA) {  // degenerate (only +inf above): count only
+            kB = kA + 1;
+            mode = M_COUNT;
+            if (kA >= KO_KEY_PINF) { kA = KO_KEY_PINF - 1; kB = KO_KEY_PINF; }
+        }
+        pl->kA[i] = kA;
+        pl->kB[i] = kB;
+        pl->tA[i] = ko_key2d(kA);
+        pl->tB[i] = ko_key2d(kB);
+        pl->hshift[i] = hist_shift(kA, kB);
+        pl->mode[i] = mode;
+        need[i] = 0;
+        if (mode == M_CAPTURE) {
+            const int a0 = lower_open ? 0 : lo[i], b0 = upper_open ? valid_s - 1 : hi[i];
+            const double mass = valid_s > 0 ? (double)(b0 - a0 + 3) / (double)valid_s : 1.0;
+            const double per_thread = fmin(mass, 1.0) * (double)L / (double)NCONS;
+            need[i] = (int)ceil(per_thread) + 1;
+            total += need[i];
+        }
+    }
+    // intervals that cannot be captured in shared memory get a key-space histogram instead
+    while (total > SLOTS) {
+        int big = -1;
+        for (int i = 0; i < ni; ++i)
+            if (pl->mode[i] == M_CAPTURE && (big < 0 || need[i] > need[big])) big = i;
+        if (big < 0) break;
+        pl->mode[big] = M_HIST;
+        total -= need[big];
+        need[big] = 0;
+    }
+    int ncap = 0;
+    for (int i = 0; i < ni; ++i) ncap += (pl->mode[i] == M_CAPTURE);
+    int slot = 0, spare = SLOTS - total, k = 0;
+    for (int i = 0; i < ni; ++i) {
+        pl->slot0[i] = slot;
+        pl->nslots[i] = 0;
+        pl->ov0[i] = 0;
+        pl->ovcap[i] = 0;
+        if (pl->mode[i] == M_CAPTURE) {
+            int extra = spare / ncap;
+            pl->nslots[i] = need[i] + extra;
+            slot += pl->nslots[i];
+            pl->ov0[i] = k * (OVQ / ncap);
+            pl->ovcap[i] = OVQ / ncap;
+            k++;
+        }
+    }
+}
+
+// Thread 0: brackets of a refinement pass — one interval per unresolved quantile.
+// nkA/nkB/npop hold the new key range and its known population per quantile.
+__device__ void build_refine_plan(Plan* pl, int nq, const unsigned long long* nkA, const unsigned long long* nkB,
+                                  const unsigned* npop) {
+    int ni = 0, ncap = 0;
+    int need[NI_MAX];
+    for (int j = 0; j < nq; ++j) {
+        if (pl->q_done[j]) continue;
+        const int i = ni++;
+        pl->q_iv[j] = i;
+        pl->kA[i] = nkA[j];
+        pl->kB[i] = nkB[j];
+        pl->tA[i] = ko_key2d(nkA[j]);
+        pl->tB[i] = ko_key2d(nkB[j]);
+        pl->hshift[i] = hist_shift(nkA[j], nkB[j]);
+        need[i] = (int)((npop[j] + NCONS - 1) / NCONS);
+        need[i] = need[i] + need[i] / 2 + 3;
+        pl->mode[i] = M_CAPTURE;
+    }
+    pl->ni = ni;
+    // share the private slots evenly; what does not fit is histogrammed
+    for (int i = 0; i < ni; ++i) {
+        if (need[i] > SLOTS / ni) pl->mode[i] = M_HIST;
+        else ncap++;
+    }
+    int k = 0;
+    for (int i = 0; i < ni; ++i) {
+        pl->slot0[i] = i * (SLOTS / ni);
+        pl->nslots[i] = (pl->mode[i] == M_CAPTURE) ? SLOTS / ni : 0;
+        pl->ov0[i] = 0;
+        pl->ovcap[i] = 0;
+        if (pl->mode[i] == M_CAPTURE) {
+            pl->ov0[i] = k * (OVQ / ncap);
+            pl->ovcap[i] = OVQ / ncap;
+            k++;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    LongSmem sm;
+    {
+        unsigned char* p = smem_raw;
+        sm.ring = reinterpret_cast<double*>(p);            p += (size_t)STAGES * TILE * 8;
+        sm.pool = p;                                       p += (size_t)SLOTS * NCONS * 8;
+        sm.ovq = reinterpret_cast<double*>(p);             p += (size_t)OVQ * 8;
+        sm.hist = reinterpret_cast<unsigned*>(p);          p += (size_t)NI_MAX * HBINS * 4;
+        sm.selhist = reinterpret_cast<unsigned*>(p);       p += (size_t)HBINS * 4;
+        sm.red = reinterpret_cast<double*>(p);             p += (size_t)NCWARPS * 4 * 8;
+        sm.plan = reinterpret_cast<Plan*>(p);              p += 1024;
+        sm.full = reinterpret_cast<uint64_t*>(p);          p += (size_t)STAGES * 8;
+        sm.empty = reinterpret_cast<uint64_t*>(p);
+    }
+    Plan* pl = sm.plan;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const bool producer = (warp == NCWARPS);
+    const int ctid = tid;  // consumer thread index (valid when !producer)
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], NCWARPS);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int n_long = a.counters[0];
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    uint32_t g = 0;  // running ring tile index, identical in all threads
+
+    for (;;) {
+        if (tid == 0) pl->work = atomicAdd(&a.counters[1], 1);
+        __syncthreads();
+        const int w = pl->work;
+        if (w >= n_long) break;
+        const int sid = a.long_list[w];
+        const int64_t off0 = a.offsets[sid];
+        const int L = (int)(a.offsets[sid + 1] - off0);
+        const double* v = a.values + off0;
+        const int head = (int)((reinterpret_cast<uintptr_t>(v) >> 3) & 1);
+        const int body = (L - head) & ~1;
+        const int ntiles = (body + TILE - 1) / TILE;
+        const double* vbody = v + head;
+        const int nq = a.nq;
+
+        // ---------------- pre-sample, sort, first plan (consumers); last valid sample (thread 255)
+        if (!producer) {
+            if (nq > 0) {
+                const int s = (L >= 8192) ? SAMPLE_BIG : SAMPLE_SMALL;
+                unsigned long long* skeys = reinterpret_cast<unsigned long long*>(sm.pool);
+                if (ctid == 0) pl->sample_valid = 0;
+                cons_sync();
+                int nv = 0;
+                for (int i = ctid; i < s; i += NCONS) {
+                    const long long idx = ((2LL * i + 1) * (long long)L) / (2LL * s);
+                    const double x = v[idx];
+                    const bool ok = (x == x);
+                    skeys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
+                    nv += ok;
+                }
+                if (nv) atomicAdd(&pl->sample_valid, nv);
+                cons_sync();
+                bitonic_sort_keys(skeys, s, ctid);
+                if (ctid == 0) build_first_plan(pl, skeys, s, pl->sample_valid, L, a);
+            } else if (ctid == 0) {
+                pl->ni = 0;
+            }
+            if (ctid == NCONS - 1) {
+                double lastv = nan;
+                for (int i = L - 1; i >= 0; --i) {
+                    const double x = v[i];
+                    if (x == x) {
+                        lastv = x;
+                        break;
+                    }
+                }
+                pl->last = lastv;
+            }
+            if (ctid == 0) {
+                pl->passes = 0;
+                pl->more = 0;
+            }
+        }
+
+        // ---------------- streaming passes
+        bool first = true;
+        for (;;) {
+            __syncthreads();  // plan visible to everyone; previous pass fully consumed
+            const int ni = pl->ni;
+            if (producer) {
+                if (lane == 0) {
+                    for (int t = 0; t < ntiles; ++t) {
+                        const uint32_t gg = g + (uint32_t)t;
+                        const int s = (int)(gg % STAGES);
+                        mbar_wait(&sm.empty[s], ((gg / STAGES) & 1u) ^ 1u);
+                        const uint32_t bytes = (uint32_t)min(TILE, body - t * TILE) * 8u;
+                        mbar_expect_tx(&sm.full[s], bytes);
+                        tma_bulk_g2s(sm.ring + (size_t)s * TILE, vbody + (size_t)t * TILE, bytes, &sm.full[s]);
+                    }
+                }
+            } else {
+                Acc acc;
+                acc.sum = 0.0;
+                acc.mn = INFINITY;
+                acc.mx = -INFINITY;
+                acc.nvalid = 0;
+                uint32_t p0[NI_MAX];
+#pragma unroll
+                for (int i = 0; i < NI_MAX; ++i) {
+                    acc.cA[i] = 0;
+                    acc.cin[i] = 0;
+                    p0[i] = (i < ni) ? (uint32_t)(((size_t)pl->slot0[i] * NCONS + ctid) * 8) : 0u;
+                    acc.p[i] = p0[i];
+                    acc.pend[i] = (i < ni) ? p0[i] + (uint32_t)pl->nslots[i] * NCONS * 8 : 0u;
+                }
+                if (ctid < NI_MAX) {
+                    pl->cA[ctid] = 0;
+                    pl->nin[ctid] = 0;
+                    pl->ovcnt[ctid] = 0;
+                }
+                for (int i = ctid; i < NI_MAX * HBINS; i += NCONS) sm.hist[i] = 0;
+                cons_sync();
+                if (first) consume_dispatch<true>(ni, v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                else consume_dispatch<false>(ni, v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+
+                // ---- reduce
+                if (first) {
+                    const double ws = warp_sum(acc.sum), wmn = warp_min(acc.mn), wmx = warp_max(acc.mx);
+                    const unsigned wn = warp_sum_u(acc.nvalid);
+                    if (lane == 0) {
+                        sm.red[warp * 4 + 0] = ws;
+                        sm.red[warp * 4 + 1] = wmn;
+                        sm.red[warp * 4 + 2] = wmx;
+                        sm.red[warp * 4 + 3] = (double)wn;
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < NI_MAX; ++i) {
+                    if (i < ni) {
+                        const unsigned ca = warp_sum_u(acc.cA[i]);
+                        const unsigned ci = warp_sum_u(acc.cin[i] + (acc.p[i] - p0[i]) / (NCONS * 8));
+                        if (lane == 0) {
+                            atomicAdd(&pl->cA[i], ca);
+                            atomicAdd(&pl->nin[i], ci);
+                        }
+                    }
+                }
+                cons_sync();
+
+                // ---- thread 0: decide per quantile
+                unsigned long long nkA[NI_MAX], nkB[NI_MAX];
+                unsigned npop[NI_MAX];
+                if (ctid == 0) {
+                    if (first) {
+                        double s = 0.0, mn = INFINITY, mx = -INFINITY, n = 0.0;
+                        for (int wq = 0; wq < NCWARPS; ++wq) {
+                            s += sm.red[wq * 4 + 0];
+                            mn = fmin(mn, sm.red[wq * 4 + 1]);
+                            mx = fmax(mx, sm.red[wq * 4 + 2]);
+                            n += sm.red[wq * 4 + 3];
+                        }
+                        pl->sum = s;
+                        pl->mn = mn;
+                        pl->mx = mx;
+                        pl->nvalid = (unsigned)n;
+                    }
+                    const unsigned n = pl->nvalid;
+                    for (int j = 0; j < nq; ++j) {
+                        pl->q_act[j] = A_NONE;
+                        if (pl->q_done[j]) continue;
+                        if (n == 0) {
+                            pl->q_val[j] = nan;
+                            pl->q_done[j] = 1;
+                            continue;
+                        }
+                        const int i = pl->q_iv[j];
+                        const unsigned r = nearest_rank_dev(n, a.q[j]);
+                        const unsigned cA = pl->cA[i];
+                        unsigned nb = pl->nin[i] + pl->ovcnt[i];
+                        if (pl->mode[i] == M_HIST) {
+                            nb = 0;
+                            for (int b = 0; b < HBINS; ++b) nb += sm.hist[i * HBINS + b];
+                            pl->nin[i] = nb;
+                            pl->ovcnt[i] = 0;
+                        }
+                        const unsigned long long kA = pl->kA[i], kB = pl->kB[i];
+                        if (r <= cA) {  // below the bracket
+                            nkA[j] = KO_KEY_NINF;
+                            nkB[j] = kA;
+                            npop[j] = cA;
+                            if (nkB[j] <= nkA[j]) {  // cannot happen (cA would be 0); be safe
+                                pl->q_val[j] = ko_key2d(KO_KEY_NINF);
+                                pl->q_done[j] = 1;
+                            }
+                        } else if (r > cA + nb) {  // above the bracket
+                            if (kB >= KO_KEY_PINF) {
+                                pl->q_val[j] = ko_key2d(KO_KEY_PINF);
+                                pl->q_done[j] = 1;
+                            } else {
+                                nkA[j] = kB;
+                                nkB[j] = KO_KEY_PINF;
+                                npop[j] = n - cA - nb;
+                            }
+                        } else {
+                            const unsigned rho = r - cA;
+                            if (kB - kA == 1 || pl->mode[i] == M_COUNT) {
+                                pl->q_val[j] = ko_key2d(kA);
+                                pl->q_done[j] = 1;
+                            } else if (pl->mode[i] == M_CAPTURE) {
+                                if (pl->ovcnt[i] <= (unsigned)pl->ovcap[i]) {
+                                    pl->q_act[j] = A_SELECT;
+                                    pl->q_rho[j] = rho;
+                                } else {  // overflowed: histogram the same bracket next
+                                    nkA[j] = kA;
+                                    nkB[j] = kB;
+                                    npop[j] = 0xFFFFFFFFu;
+                                }
+                            } else {  // M_HIST: narrow to the bin holding the rank
+                                unsigned cum = 0;
+                                int b = 0;
+                                for (; b < HBINS - 1; ++b) {
+                                    const unsigned h = sm.hist[i * HBINS + b];
+                                    if (cum + h >= rho) break;
+                                    cum += h;
+                                }
+                                const int sh = pl->hshift[i];
+                                const unsigned long long na = kA + ((unsigned long long)b << sh);
+                                unsigned long long nb2 = na + (1ull << sh);
+                                if (nb2 > kB || nb2 < na) nb2 = kB;
+                                if (nb2 - na == 1) {
+                                    pl->q_val[j] = ko_key2d(na);
+                                    pl->q_done[j] = 1;
+                                } else {
+                                    nkA[j] = na;
+                                    nkB[j] = nb2;
+                                    npop[j] = sm.hist[i * HBINS + b];
+                                }
+                            }
+                        }
+                    }
+                }
+                cons_sync();
+                // ---- selects over captured candidates (all consumers)
+                for (int j = 0; j < nq; ++j) {
+                    if (pl->q_act[j] == A_SELECT) {
+                        const int i = pl->q_iv[j];
+                        uint32_t pp0 = 0, pcur = 0;
+#pragma unroll
+                        for (int ii = 0; ii < NI_MAX; ++ii)
+                            if (ii == i) {
+                                pp0 = p0[ii];
+                                pcur = acc.p[ii];
+                            }
+                        const unsigned long long k = cta_radix_select(sm, i, pl->q_rho[j], pp0, pcur, ctid, lane);
+                        if (ctid == 0) {
+                            pl->q_val[j] = ko_key2d(k);
+                            pl->q_done[j] = 1;
+                        }
+                        cons_sync();
+                    }
+                }
+                if (ctid == 0) {
+                    int more = 0;
+                    for (int j = 0; j < nq; ++j) more |= !pl->q_done[j];
+                    pl->passes += 1;
+                    if (more && pl->passes > 12) {  // cannot happen: every pass shrinks the key range
+                        for (int j = 0; j < nq; ++j)
+                            if (!pl->q_done[j]) {
+                                pl->q_val[j] = nan;
+                                pl->q_done[j] = 1;
+                            }
+                        atomicExch(&a.counters[2], 2);
+                        more = 0;
+                    }
+                    if (more) build_refine_plan(pl, nq, nkA, nkB, npop);
+                    pl->more = more;
+                }
+            }
+            g += (uint32_t)ntiles;
+            first = false;
+            __syncthreads();
+            if (!pl->more) break;
+        }
+
+        // ---------------- outputs
+        if (tid == 0) {
+            const unsigned n = pl->nvalid;
+            if (a.out_sum) a.out_sum[sid] = pl->sum;
+            if (a.out_mean) a.out_mean[sid] = n > 0 ? pl->sum / (double)n : 0.0;
+            if (a.out_min) a.out_min[sid] = n > 0 ? pl->mn + 0.0 : nan;
+            if (a.out_max) a.out_max[sid] = n > 0 ? pl->mx + 0.0 : nan;
+            if (a.out_last) a.out_last[sid] = pl->last;
+            if (a.out_count) a.out_count[sid] = (int64_t)n;
+            if (a.out_quant)
+                for (int j = 0; j < nq; ++j) a.out_quant[(int64_t)sid * nq + a.qcol[j]] = pl->q_val[j];
+            if (pl->passes > 1) atomicAdd(&a.counters[3], 1);
+        }
+        __syncthreads();
+    }
+}
+
+bool g_attr_done = false;
+
+}  // namespace
+
+// Enqueue the three kernels on `stream`.  scratch must hold 8 ints + n_series ints.
+int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offsets, int64_t n_series,
+                     const double* q, int nq, double* d_sum, double* d_mean, double* d_min, double* d_max,
+                     double* d_last, int64_t* d_count, double* d_quant, int* d_scratch, cudaStream_t stream) {
+    KO_REQUIRE(nq >= 0 && nq <= KO_MAX_QUANTILES, "series rollup: nq must be 0..KO_MAX_QUANTILES");
+    KO_REQUIRE(n_series < 2147483647LL, "series rollup: too many series in one call");
+    SeriesArgs a;
+    a.values = d_values;
+    a.offsets = d_offsets;
+    a.n_series = n_series;
+    a.out_sum = d_sum;
+    a.out_mean = d_mean;
+    a.out_min = d_min;
+    a.out_max = d_max;
+    a.out_last = d_last;
+    a.out_count = d_count;
+    a.out_quant = d_quant;
+    a.counters = d_scratch;
+    a.long_list = d_scratch + 8;
+    a.nq = nq;
+    // quantiles ascending (stable insertion sort), remembering the caller's column
+    for (int j = 0; j < NI_MAX; ++j) {
+        a.q[j] = 0.0;
+        a.qcol[j] = 0;
+    }
+    for (int j = 0; j < nq; ++j) {
+        KO_REQUIRE(q[j] >= 0.0 && q[j] <= 1.0, "series rollup: quantile outside [0,1]");
+        int k = j;
+        while (k > 0 && a.q[k - 1] > q[j]) {
+            a.q[k] = a.q[k - 1];
+            a.qcol[k] = a.qcol[k - 1];
+            --k;
+        }
+        a.q[k] = q[j];
+        a.qcol[k] = j;
+    }
+    if (!g_attr_done) {
+        KO_CUDA(cudaFuncSetAttribute(series_long, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)LONG_SMEM_BYTES));
+        KO_CUDA(cudaFuncSetAttribute(series_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     8 * SMALL_MAX * 8 + 8 * HBINS * 4));
+        g_attr_done = true;
+    }
+    KO_CUDA(cudaMemsetAsync(d_scratch, 0, 8 * sizeof(int), stream));
+    const int cb = 256;
+    classify_series<<<(unsigned)((n_series + cb - 1) / cb), cb, 0, stream>>>(a);
+    const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
+    series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, stream>>>(a);
+    int grid = 2 * ctx->num_sms;
+    if ((int64_t)grid > n_series) grid = (int)n_series;
+    KO_CUDA(cudaEventRecord(ctx->ev_k0, stream));
+    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, stream>>>(a);
+    KO_CUDA(cudaEventRecord(ctx->ev_k1, stream));
+    ctx->k_timed = true;
+    KO_CUDA(cudaGetLastError());
+    ctx->counters.kernel_launches += 3;
+    return KO_OK;
+}
+
+size_t ko_series_scratch_bytes(int64_t n_series) { return (size_t)(8 + n_series) * sizeof(int); }
+
+extern "C" int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_offsets,
+                                    int64_t n_series, const double* q, int nq, double* d_out_sum,
+                                    double* d_out_mean, double* d_out_min, double* d_out_max,
+                                    double* d_out_last, int64_t* d_out_count, double* d_out_quantiles,
+                                    void* stream) {
+    KO_REQUIRE(ctx && ctx->alive, "ko_series_rollup_dev: ctx not initialised");
+    KO_REQUIRE(n_series >= 0, "ko_series_rollup_dev: negative n_series");
+    if (n_series == 0) return KO_OK;
+    KO_REQUIRE(d_values && d_offsets, "ko_series_rollup_dev: NULL input");
+    KO_REQUIRE(nq == 0 || q, "ko_series_rollup_dev: q is NULL");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_CUDA(cudaSetDevice(ctx->device));
+    int rc = ko_buf_reserve(&ctx->scratch, ko_series_scratch_bytes(n_series));
+    if (rc) return rc;
+    return ko_series_launch(ctx, d_values, d_offsets, n_series, q, nq, d_out_sum, d_out_mean, d_out_min,
+                            d_out_max, d_out_last, d_out_count, d_out_quantiles, (int*)ctx->scratch.p,
+                            (cudaStream_t)stream);
+}
+
+// Host-pointer entry point: chunked, double-buffered H2D of the sample column overlapped with the kernels.
+extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t* offsets, int64_t n_series,
+                                const double* q, int nq, double* out_sum, double* out_mean, double* out_min,
+                                double* out_max, double* out_last, int64_t* out_count, double* out_quantiles) {
+    KO_REQUIRE(ctx && ctx->alive, "ko_series_rollup: ctx not initialised");
+    KO_REQUIRE(n_series >= 0, "ko_series_rollup: negative n_series");
+    if (n_series == 0) return KO_OK;
+    KO_REQUIRE(offsets, "ko_series_rollup: offsets is NULL");
+    KO_REQUIRE(nq >= 0 && nq <= KO_MAX_QUANTILES, "ko_series_rollup: nq must be 0..KO_MAX_QUANTILES");
+    KO_REQUIRE(nq == 0 || q, "ko_series_rollup: q is NULL");
+    for (int64_t i = 0; i < n_series; ++i)
+        KO_REQUIRE(offsets[i + 1] >= offsets[i] && offsets[i + 1] - offsets[i] < 2147483647LL,
+                   "ko_series_rollup: offsets must be non-decreasing with series shorter than 2^31");
+    KO_REQUIRE(values || offsets[n_series] == offsets[0], "ko_series_rollup: values is NULL");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_CUDA(cudaSetDevice(ctx->device));
+
+    const size_t off_bytes = (size_t)(n_series + 1) * 8;
+    const int ncols = 6 + nq;  // sum mean min max last count quant[nq]
+    const size_t col = ko_align_up((size_t)n_series * 8, 256);
+    int rc;
+    if ((rc = ko_buf_reserve(&ctx->in_small, off_bytes))) return rc;
+    if ((rc = ko_buf_reserve(&ctx->out_small, col * 6 + ko_align_up((size_t)n_series * 8 * (nq ? nq : 1), 256))))
+        return rc;
+    if ((rc = ko_buf_reserve(&ctx->scratch, ko_series_scratch_bytes(n_series)))) return rc;
+    (void)ncols;
+    int64_t* d_off = (int64_t*)ctx->in_small.p;
+    unsigned char* ob = (unsigned char*)ctx->out_small.p;
+    double* d_sum = (double*)(ob + 0 * col);
+    double* d_mean = (double*)(ob + 1 * col);
+    double* d_min = (double*)(ob + 2 * col);
+    double* d_max = (double*)(ob + 3 * col);
+    double* d_last = (double*)(ob + 4 * col);
+    int64_t* d_cnt = (int64_t*)(ob + 5 * col);
+    double* d_q = (double*)(ob + 6 * col);
+
+    // chunk plan: whole series per chunk, about 256 MB each
+    const size_t target = (size_t)256 << 20;
+    size_t max_chunk = 0;
+    {
+        int64_t s0 = 0;
+        while (s0 < n_series) {
+            int64_t s1 = s0;
+            size_t bytes = 0;
+            while (s1 < n_series && (bytes == 0 || bytes < target)) {
+                bytes += (size_t)(offsets[s1 + 1] - offsets[s1]) * 8;
+                ++s1;
+            }
+            if (bytes > max_chunk) max_chunk = bytes;
+            s0 = s1;
+        }
+    }
+    const bool multi = max_chunk < (size_t)(offsets[n_series] - offsets[0]) * 8;
+    if ((rc = ko_buf_reserve(&ctx->stage[0], max_chunk + 256))) return rc;
+    if (multi && (rc = ko_buf_reserve(&ctx->stage[1], max_chunk + 256))) return rc;
+
+    KO_CUDA(cudaMemcpyAsync(d_off, offsets, off_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->counters.h2d_bytes += (int64_t)off_bytes;
+    int64_t s0 = 0;
+    int c = 0;
+    while (s0 < n_series) {
+        int64_t s1 = s0;
+        size_t bytes = 0;
+        while (s1 < n_series && (bytes == 0 || bytes < target)) {
+            bytes += (size_t)(offsets[s1 + 1] - offsets[s1]) * 8;
+            ++s1;
+        }
+        const int b = c & 1;
+        if (c >= 2) KO_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_done[b], 0));
+        if (bytes)
+            KO_CUDA(cudaMemcpyAsync(ctx->stage[b].p, values + offsets[s0], bytes, cudaMemcpyHostToDevice,
+                                    ctx->copy_stream));
+        ctx->counters.h2d_bytes += (int64_t)bytes;
+        KO_CUDA(cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream));
+        KO_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0));
+        // the kernels index values with absolute offsets: bias the base pointer by the chunk start
+        const double* base = reinterpret_cast<const double*>(reinterpret_cast<uintptr_t>(ctx->stage[b].p) -
+                                                              (uintptr_t)offsets[s0] * 8u);
+        const int64_t ns = s1 - s0;
+        rc = ko_series_launch(ctx, base, d_off + s0, ns, q, nq, out_sum ? d_sum + s0 : nullptr,
+                              out_mean ? d_mean + s0 : nullptr, out_min ? d_min + s0 : nullptr,
+                              out_max ? d_max + s0 : nullptr, out_last ? d_last + s0 : nullptr,
+                              out_count ? d_cnt + s0 : nullptr,
+                              (out_quantiles && nq) ? d_q + s0 * nq : nullptr, (int*)ctx->scratch.p, ctx->stream);
+        if (rc) {
+            cudaStreamSynchronize(ctx->stream);
+            cudaStreamSynchronize(ctx->copy_stream);
+            return rc;
+        }
+        KO_CUDA(cudaEventRecord(ctx->ev_done[b], ctx->stream));
+        // the scratch (work list / counters) is shared by consecutive chunks: they run in stream order
+        s0 = s1;
+        ++c;
+    }
+    const size_t nb = (size_t)n_series * 8;
+    if (out_sum) KO_CUDA(cudaMemcpyAsync(out_sum, d_sum, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_mean) KO_CUDA(cudaMemcpyAsync(out_mean, d_mean, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_min) KO_CUDA(cudaMemcpyAsync(out_min, d_min, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_max) KO_CUDA(cudaMemcpyAsync(out_max, d_max, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_last) KO_CUDA(cudaMemcpyAsync(out_last, d_last, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_count) KO_CUDA(cudaMemcpyAsync(out_count, d_cnt, nb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_quantiles && nq)
+        KO_CUDA(cudaMemcpyAsync(out_quantiles, d_q, nb * nq, cudaMemcpyDeviceToHost, ctx->stream));
+    int flags[4] = {0, 0, 0, 0};
+    KO_CUDA(cudaMemcpyAsync(flags, (int*)ctx->scratch.p, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
+    KO_CUDA(cudaStreamSynchronize(ctx->stream));
+    int nout = (out_sum != 0) + (out_mean != 0) + (out_min != 0) + (out_max != 0) + (out_last != 0) +
+               (out_count != 0) + ((out_quantiles && nq) ? nq : 0);
+    ctx->counters.d2h_bytes += (int64_t)nb * nout + (int64_t)sizeof(flags);
+    ctx->counters.series_fallback = flags[3];
+    if (flags[2]) {
+        ko_set_error("ko_series_rollup: device reported error flag %d", flags[2]);
+        return KO_ECUDA;
+    }
+    return KO_OK;
+}

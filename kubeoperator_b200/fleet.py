@@ -1,0 +1,107 @@
+"""Fleet-wide merges across series shards (one process per GPU).  BUILD-DEFINED: the
+reference has no multi-process rollup; its fleet merge is the serial concat + re-sort of DashBoardView.get
+(core/apps/kubeops_api/api.py:495-501) and the browser sums of dashboard.component.ts:117-153.
+
+Per-series statistics need no communication (series are sharded by ID).  Collectives — NCCL on GPUs, gloo
+in the CPU tests — are used only for the small fleet-level exchange:
+* ``fleet_quantile``: exact nearest-rank quantile of the pooled per-shard values by all-gathering 65 536-bin
+  key histograms and refining 16 bits per round (4 rounds for a 64-bit key);
+* ``fleet_topk``: all-gather of every shard's top-k (key, global index) and a merge that keeps the
+  reference's stable descending order (ties by global index);
+* ``fleet_scalars``: all-reduce of the additive fleet scalars.
+
+``hist_fn(shift, prefix_mask, prefix) -> int64[65536]`` supplies the local histogram: on a GPU it is
+``Rollup.key_histogram`` / ``key_histogram_dev`` (the CUDA kernel); the CPU tests pass a NumPy stand-in.
+"""
+import math
+
+import numpy as np
+
+HIST_BINS = 65536
+
+
+def shard_range(n_items, rank, world):
+    """Contiguous balanced shard [lo, hi) of n_items for ``rank``."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_by_weight(weights, world):
+    """Contiguous series ranges balanced by sample count (prefix sum over series lengths)."""
+    w = np.asarray(weights, np.int64)
+    csum = np.concatenate([[0], np.cumsum(w)])
+    total = int(csum[-1])
+    cuts = [int(np.searchsorted(csum, total * r / world, side="left")) for r in range(world + 1)]
+    cuts[0], cuts[-1] = 0, len(w)
+    return [(cuts[r], max(cuts[r], cuts[r + 1])) for r in range(world)]
+
+
+def _all_gather_sum(t, dist):
+    if dist is None or not dist.is_initialized() or dist.get_world_size() == 1:
+        return t
+    import torch
+    bufs = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(bufs, t)                      # per north_star: allgather of per-shard histograms
+    return torch.stack(bufs).sum(dim=0)
+
+
+def key_to_double(key):
+    k = np.uint64(key)
+    u = (k & np.uint64(0x7FFFFFFFFFFFFFFF)) if (int(k) >> 63) else ~k
+    return float(np.array([u], np.uint64).view(np.float64)[0])
+
+
+def fleet_quantile(hist_fn, n_valid_local, q, dist=None, device="cpu"):
+    """Exact nearest-rank quantile over all shards.  Returns NaN when the fleet has no valid value."""
+    import torch
+    n = torch.tensor([int(n_valid_local)], dtype=torch.int64, device=device)
+    n_total = int(_all_gather_sum(n, dist).item())
+    if n_total == 0:
+        return float("nan")
+    r = max(1, min(n_total, int(math.ceil(q * n_total))))
+    prefix, mask = 0, 0
+    for shift in (48, 32, 16, 0):
+        h = hist_fn(shift, mask, prefix)
+        if not torch.is_tensor(h):
+            h = torch.from_numpy(np.ascontiguousarray(h, np.int64)).to(device)
+        h = _all_gather_sum(h, dist)
+        c = torch.cumsum(h, 0)
+        d = int(torch.searchsorted(c, torch.tensor([r], dtype=torch.int64, device=c.device)).item())
+        if d > 0:
+            r -= int(c[d - 1].item())
+        prefix |= d << shift
+        mask |= 0xFFFF << shift
+    return key_to_double(prefix) + 0.0
+
+
+def fleet_topk(local_keys, local_global_idx, k, dist=None, device="cpu"):
+    """Global indices of the fleet's top-k by (key descending, global index ascending) — the order
+    quick_sort_pods gives on the concatenated list (api.py:495-500), truncated to k.  ``local_keys`` /
+    ``local_global_idx`` are this shard's top-k already in that order."""
+    import torch
+    keys = torch.full((k,), torch.iinfo(torch.int64).min, dtype=torch.int64, device=device)
+    gidx = torch.full((k,), torch.iinfo(torch.int64).max, dtype=torch.int64, device=device)
+    m = min(k, len(local_keys))
+    if m:
+        keys[:m] = torch.as_tensor(np.asarray(local_keys[:m], np.int64), device=device)
+        gidx[:m] = torch.as_tensor(np.asarray(local_global_idx[:m], np.int64), device=device)
+    pair = torch.stack([keys, gidx])
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        bufs = [torch.empty_like(pair) for _ in range(dist.get_world_size())]
+        dist.all_gather(bufs, pair)
+        pair = torch.cat(bufs, dim=1)
+    ks, gs = pair[0].cpu().numpy(), pair[1].cpu().numpy()
+    keep = gs != np.iinfo(np.int64).max
+    ks, gs = ks[keep], gs[keep]
+    order = np.lexsort((gs, -ks))
+    return gs[order][:k].tolist()
+
+
+def fleet_scalars(values, dist=None, device="cpu"):
+    """All-reduce(sum) of a small vector of additive fleet scalars (f64)."""
+    import torch
+    t = torch.as_tensor(np.asarray(values, np.float64), device=device)
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t)
+    return t.cpu().numpy()

@@ -1,0 +1,155 @@
+"""Deterministic synthetic Prometheus dumps for the BASELINE.json configs, columnar:
+``values`` f64[] (all series back to back), ``offsets`` i64[n_series+1], ``kind`` per series.
+
+NumPy generation (``make_series``) is used by tests, smoke and the bounded CPU sample; bench.py builds the
+full-size column on the GPU with torch from the same distributions (``make_series_torch``) because drawing
+4e8 Beta variates on the host would take longer than the whole bench.
+"""
+import numpy as np
+
+STEP_SECONDS = 15
+KIND_GAUGE, KIND_CONST, KIND_COUNTER, KIND_DISCRETE = 0, 1, 2, 3
+
+# name -> (nodes, gpus per node, pods, samples per series)
+CONFIGS = {
+    "c1": dict(nodes=4, gpus=0, pods=120, L=5760),          # 1 master + 3 workers, 24 h
+    "c2": dict(nodes=100, gpus=8, pods=3000, L=40320),      # 100 nodes incl. DCGM series, 7 d
+    "c3": dict(nodes=1000, gpus=0, pods=30000, L=172800),   # 1000 nodes x 30 pods, 30 d
+}
+
+
+def series_layout(cfg):
+    """Kinds of the series of a config: per node cpu_usage(gauge) cpu(const) mem(const) mem_usage(gauge);
+    per GPU util(discrete %) fb_used(gauge) fb_free(gauge) temp(discrete) power(gauge);
+    per pod cpu(counter) mem(gauge)."""
+    kinds = []
+    kinds += [KIND_GAUGE, KIND_CONST, KIND_CONST, KIND_GAUGE] * cfg["nodes"]
+    kinds += [KIND_DISCRETE, KIND_GAUGE, KIND_GAUGE, KIND_DISCRETE, KIND_GAUGE] * (cfg["nodes"] * cfg["gpus"])
+    kinds += [KIND_COUNTER, KIND_GAUGE] * cfg["pods"]
+    return np.array(kinds, np.int8)
+
+
+def n_series(cfg):
+    return 4 * cfg["nodes"] + 5 * cfg["nodes"] * cfg["gpus"] + 2 * cfg["pods"]
+
+
+def _one_series(rng, kind, L):
+    if kind == KIND_GAUGE:
+        v = rng.beta(2.0, 5.0, L)
+        hot = rng.random(L) < 0.01
+        v = np.where(hot, 0.8 + 0.2 * v, v)              # 1 % of usage samples above the 0.8 band
+    elif kind == KIND_CONST:
+        v = np.full(L, float(rng.choice([4, 8, 16, 64])))
+    elif kind == KIND_COUNTER:
+        inc = rng.gamma(2.0, 0.05, L)
+        reset = rng.random(L) < 1e-5
+        v = np.empty(L)
+        acc = 0.0
+        start = 0
+        for r in list(np.flatnonzero(reset)) + [L]:
+            seg = np.cumsum(inc[start:r])
+            v[start:r] = seg
+            start = r
+        del acc
+    else:
+        v = np.floor(40.0 + 40.0 * rng.beta(2.0, 2.0, L))  # integer-valued (temperature / util style)
+    v = v.astype(np.float64)
+    v[rng.random(L) < 1e-3] = np.nan                      # staleness markers
+    return v
+
+
+def make_series(config="c1", seed=1, L=None, max_series=None, all_zero_frac=0.02):
+    """Columnar dump of a config (optionally truncated to ``max_series`` series / ``L`` samples)."""
+    cfg = dict(CONFIGS[config]) if isinstance(config, str) else dict(config)
+    if L is not None:
+        cfg["L"] = L
+    kinds = series_layout(cfg)
+    if max_series is not None:
+        kinds = kinds[:max_series]
+    rng = np.random.default_rng(seed)
+    n = len(kinds)
+    L = cfg["L"]
+    values = np.empty(n * L, np.float64)
+    for i, k in enumerate(kinds):
+        values[i * L:(i + 1) * L] = _one_series(rng, int(k), L)
+    # 2 % of nodes all-zero (exercises cluster_monitor.py:174): zero both usage series of the node
+    for node in range(min(cfg["nodes"], n // 4)):
+        if rng.random() < all_zero_frac:
+            for s in (4 * node, 4 * node + 3):
+                values[s * L:(s + 1) * L] = 0.0
+    offsets = np.arange(n + 1, dtype=np.int64) * L
+    return dict(values=values, offsets=offsets, kinds=kinds, cfg=cfg)
+
+
+def make_ragged(seed, lengths):
+    """Ragged batch for edge-case tests: one series per entry of ``lengths``, kinds cycling."""
+    rng = np.random.default_rng(seed)
+    parts = [_one_series(rng, i % 4, int(L)) if L > 0 else np.zeros(0) for i, L in enumerate(lengths)]
+    offsets = np.concatenate([[0], np.cumsum([len(p) for p in parts])]).astype(np.int64)
+    values = np.concatenate(parts) if parts else np.zeros(0)
+    return dict(values=values, offsets=offsets)
+
+
+def make_pods(seed, n_pods):
+    """Columnar pod list: Poisson(0.3) restarts per container, 3 % not ready, 2 % pods not Running."""
+    rng = np.random.default_rng(seed)
+    n_cont = rng.choice([1, 1, 2, 2, 3], n_pods)
+    offsets = np.concatenate([[0], np.cumsum(n_cont)]).astype(np.int64)
+    c = int(offsets[-1])
+    return dict(container_restart=rng.poisson(0.3, c).astype(np.int32),
+                container_ready=(rng.random(c) >= 0.03).astype(np.uint8),
+                pod_offsets=offsets, pod_phase_ok=(rng.random(n_pods) >= 0.02).astype(np.uint8))
+
+
+def make_nodes(seed, n_nodes, n_clusters=1, zero_frac=0.02, hot_frac=0.0):
+    """Instant node columns as ClusterMonitor.list_nodes delivers them (floats)."""
+    rng = np.random.default_rng(seed)
+    cu, mu = rng.beta(2, 5, n_nodes), rng.beta(2, 5, n_nodes)
+    zero = rng.random(n_nodes) < zero_frac
+    cu[zero] = 0.0
+    mu[zero] = 0.0
+    hot = rng.random(n_nodes) < hot_frac
+    cu[hot & ~zero] = 80.0 + 20.0 * rng.random(int((hot & ~zero).sum()))
+    cpu = rng.choice([4.0, 8.0, 16.0, 64.0], n_nodes)
+    mem = np.floor(rng.uniform(8, 512, n_nodes) * 2 ** 30) / 1024 / 1024 / 1024
+    cluster = np.sort(rng.integers(0, n_clusters, n_nodes)).astype(np.int32)
+    return dict(cpu=cpu, mem=mem, cpu_usage=cu, mem_usage=mu, cluster_of_node=cluster)
+
+
+def make_series_torch(config, seed, device, L=None, n_series_override=None):
+    """Full-size column generated ON THE GPU (torch) from the same distributions as make_series.
+    Returns (values tensor f64 [n*L], offsets tensor i64 [n+1], kinds ndarray)."""
+    import torch
+    cfg = dict(CONFIGS[config])
+    if L is not None:
+        cfg["L"] = L
+    kinds = series_layout(cfg)
+    if n_series_override is not None:
+        kinds = np.resize(kinds, n_series_override)
+    n, L = len(kinds), cfg["L"]
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    values = torch.empty(n * L, dtype=torch.float64, device=device)
+    kt = torch.from_numpy(kinds.astype(np.int64)).to(device)
+    rows = 512                                             # generate in row blocks to bound temporaries
+    for r0 in range(0, n, rows):
+        r1 = min(n, r0 + rows)
+        m = r1 - r0
+        k = kt[r0:r1].unsqueeze(1)
+        # Beta(2,5) as an order statistic: 2nd smallest of 6 uniforms; Beta(2,2): 2nd smallest of 3
+        u = torch.rand((m, L, 6), generator=g, device=device, dtype=torch.float32)
+        b25 = torch.kthvalue(u, 2, dim=2).values.double()
+        b22 = torch.kthvalue(u[:, :, :3], 2, dim=2).values.double()
+        w = torch.rand((m, L), generator=g, device=device, dtype=torch.float64)
+        gauge = torch.where(w < 0.01, 0.8 + 0.2 * b25, b25)
+        const = torch.tensor([4.0, 8.0, 16.0, 64.0], device=device, dtype=torch.float64)[
+            torch.randint(0, 4, (m, 1), generator=g, device=device)].expand(m, L)
+        counter = torch.cumsum(0.05 * (-torch.log1p(-u[:, :, 3].double()) - torch.log1p(-u[:, :, 4].double())), dim=1)
+        disc = torch.floor(40.0 + 40.0 * b22)
+        blk = torch.where(k == KIND_GAUGE, gauge, torch.where(k == KIND_CONST, const,
+                          torch.where(k == KIND_COUNTER, counter, disc)))
+        blk = torch.where(w > 0.999, torch.full_like(blk, float("nan")), blk)
+        values[r0 * L:r1 * L] = blk.reshape(-1)
+        del u, b25, b22, w, gauge, counter, disc, blk
+    offsets = torch.arange(n + 1, dtype=torch.int64, device=device) * L
+    return values, offsets, kinds

@@ -62,7 +62,7 @@ def gen_set_cluster_data():
         nodes, pods = _nodes(rng, n_nodes, zf, ints, hot), _pods(rng, n_pods)
         blob, flagged = rh.run_set_cluster_data("c", nodes, pods, flag_mode=hot)
         cases.append(dict(
-            nodes=nodes, pods=pods, flag_mode=hot,
+            nodes=nodes, pods=pods, flag_mode=hot, blob=blob,
             expect=dict(cpu_usage=blob["cpu_usage"], cpu_total=blob["cpu_total"],
                         mem_usage=blob["mem_usage"], mem_total=blob["mem_total"],
                         flagged=flagged,

@@ -1,0 +1,209 @@
+"""GPU parity of the window-statistics path (ko_series_rollup through the C ABI) against the oracle.
+
+Bar (north_star): counts, min/max, last, order statistics bit-exact; sums and means within 1e-12 relative
+(relative to sum|x|, the condition the left-to-right oracle sum itself satisfies)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import c_oracle, rollup_oracle as ro
+from kubeoperator_b200 import synth
+
+pytestmark = pytest.mark.gpu
+QS = [0.5, 0.95, 0.99]
+SUM_RTOL = 1e-12
+
+
+@pytest.fixture(scope="module")
+def rollup():
+    from kubeoperator_b200 import Rollup
+    r = Rollup(0)
+    yield r
+    r.close()
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, np.float64).view(np.uint64)
+
+
+def assert_series_parity(got, exp, values, offsets, qs):
+    n = len(offsets) - 1
+    assert np.array_equal(got["count"], exp["count"])
+    for k in ("min", "max", "last"):
+        both_nan = np.isnan(got[k]) & np.isnan(exp[k])
+        assert np.array_equal(_bits(got[k])[~both_nan], _bits(exp[k])[~both_nan]), k
+        assert np.array_equal(np.isnan(got[k]), np.isnan(exp[k])), k
+    if len(qs):
+        g, e = got["quantiles"], exp["quantiles"]
+        assert g.shape == e.shape
+        both_nan = np.isnan(g) & np.isnan(e)
+        bad = (_bits(g) != _bits(e)) & ~both_nan
+        assert not bad.any(), "quantile mismatch at %s: got %s expected %s" % (
+            np.argwhere(bad)[:5].tolist(), g[bad][:5], e[bad][:5])
+    absum = np.array([np.nansum(np.abs(values[offsets[i]:offsets[i + 1]])) for i in range(n)])
+    with np.errstate(invalid="ignore"):
+        finite = np.isfinite(exp["sum"])
+        assert np.all(np.abs(got["sum"] - exp["sum"])[finite] <= SUM_RTOL * absum[finite] + 0.0)
+        assert np.array_equal(np.isnan(got["sum"][~finite]), np.isnan(exp["sum"][~finite]))
+        assert np.array_equal(got["sum"][~finite & ~np.isnan(exp["sum"])], exp["sum"][~finite & ~np.isnan(exp["sum"])])
+        cnt = np.maximum(exp["count"], 1)
+        assert np.all(np.abs(got["mean"] - exp["mean"])[finite] <= SUM_RTOL * absum[finite] / cnt[finite])
+
+
+def test_golden_vectors(rollup, golden_dir):
+    g = json.load(open(os.path.join(golden_dir, "builddefined_series.json")))
+    dec = lambda v: float("nan") if v is None else float(v)
+    vals, offs = [], [0]
+    for s in g["series"]:
+        vals += [dec(x) for x in s["values"]]
+        offs.append(len(vals))
+    values, offsets = np.array(vals), np.array(offs, np.int64)
+    got = rollup.series_rollup(values, offsets, g["qs"])
+    exp = ro.series_rollup_np(values, offsets, g["qs"])
+    assert_series_parity(got, exp, values, offsets, g["qs"])
+    for i, s in enumerate(g["series"]):
+        for j in range(len(g["qs"])):
+            a, b = got["quantiles"][i, j], dec(s["quantiles"][j])
+            assert (a != a and b != b) or _bits([a])[0] == _bits([b])[0]
+        assert int(got["count"][i]) == s["expect"]["count"]
+
+
+def test_config1_full(rollup):
+    d = synth.make_series("c1", seed=1)
+    got = rollup.series_rollup(d["values"], d["offsets"], QS)
+    exp = c_oracle.series_rollup(d["values"], d["offsets"], QS, nthreads=8)
+    assert_series_parity(got, exp, d["values"], d["offsets"], QS)
+
+
+def test_config2_slice_long_series(rollup):
+    # 48 series of the 100-node config at its full length (40 320 samples): every kind incl. DCGM-like
+    d = synth.make_series("c2", seed=2, max_series=16)
+    cfg = dict(nodes=0, gpus=0, pods=0, L=40320)
+    cfg.update(nodes=2, gpus=2, pods=6)
+    e = synth.make_series(cfg, seed=3)
+    values = np.concatenate([d["values"], e["values"]])
+    offsets = np.concatenate([d["offsets"], d["offsets"][-1] + e["offsets"][1:]])
+    got = rollup.series_rollup(values, offsets, QS)
+    exp = c_oracle.series_rollup(values, offsets, QS, nthreads=8)
+    assert_series_parity(got, exp, values, offsets, QS)
+
+
+def test_ragged_and_edge_lengths(rollup):
+    lengths = [0, 1, 2, 3, 31, 32, 33, 20, 240, 1023, 1024, 1025, 1026, 2047, 2048, 2049, 4097, 8191, 8192, 8193,
+               0, 5, 12345, 40321, 7]
+    d = synth.make_ragged(4, lengths)
+    got = rollup.series_rollup(d["values"], d["offsets"], QS)
+    exp = ro.series_rollup_np(d["values"], d["offsets"], QS)
+    assert_series_parity(got, exp, d["values"], d["offsets"], QS)
+    # odd start offsets: the same batch behind one leading sample shifts every 16-byte alignment
+    v2 = np.concatenate([[1.5], d["values"]])
+    o2 = np.concatenate([[0], d["offsets"] + 1])
+    got = rollup.series_rollup(v2, o2, QS)
+    exp = ro.series_rollup_np(v2, o2, QS)
+    assert_series_parity(got, exp, v2, o2, QS)
+
+
+def test_ties_constants_nan_inf(rollup):
+    rng = np.random.default_rng(5)
+    L = 20000
+    series = [
+        np.full(L, 16.0),                                          # constant
+        np.where(rng.random(L) < 0.5, 0.0, rng.random(L)),         # half the mass on one value
+        np.where(rng.random(L) < 0.6, 100.0, 100 * rng.random(L)),  # saturated upper tie group
+        np.floor(rng.normal(60, 3, L)),                            # few distinct integers
+        np.full(L, np.nan),                                        # all stale
+        np.where(rng.random(L) < 0.9, np.nan, rng.random(L)),      # mostly stale
+        np.concatenate([np.full(L // 2, -0.0), np.full(L - L // 2, 0.0)]),
+        np.where(rng.random(L) < 0.02, np.inf, rng.random(L)),     # +inf above the p99 rank
+        np.where(rng.random(L) < 0.6, -np.inf, rng.random(L)),
+        np.sort(rng.random(L)),                                    # monotone (counter-like)
+        np.sort(rng.random(L))[::-1].copy(),
+        rng.normal(0, 1, L) * 10.0 ** rng.integers(-300, 300, L),  # huge dynamic range, mixed sign
+        np.concatenate([np.zeros(L - 3), [1.0, 2.0, 3.0]]),        # the sample never sees the tail
+    ]
+    offsets = np.arange(len(series) + 1, dtype=np.int64) * L
+    values = np.concatenate(series)
+    for qs in (QS, [0.0, 1.0, 0.001, 0.999]):
+        got = rollup.series_rollup(values, offsets, qs)
+        exp = ro.series_rollup_np(values, offsets, qs)
+        assert_series_parity(got, exp, values, offsets, qs)
+
+
+def test_very_long_series_refinement_passes(rollup):
+    # 30 days at 15 s (config 3/4 length): the brackets do not fit shared memory -> histogram refinement
+    d = synth.make_series(dict(nodes=1, gpus=1, pods=1, L=172800), seed=6)
+    got = rollup.series_rollup(d["values"], d["offsets"], QS)
+    exp = c_oracle.series_rollup(d["values"], d["offsets"], QS, nthreads=8)
+    assert_series_parity(got, exp, d["values"], d["offsets"], QS)
+    assert rollup.counters()["series_fallback"] > 0
+
+
+def test_short_windows_config5(rollup):
+    rng = np.random.default_rng(7)
+    for L in (20, 240):
+        n = 20000
+        values = rng.beta(2, 5, n * L)
+        values[rng.random(n * L) < 1e-3] = np.nan
+        offsets = np.arange(n + 1, dtype=np.int64) * L
+        got = rollup.series_rollup(values, offsets, QS)
+        exp = c_oracle.series_rollup(values, offsets, QS, nthreads=8)
+        assert_series_parity(got, exp, values, offsets, QS)
+        got = rollup.series_rollup(values, offsets, ())        # statistics only
+        assert_series_parity(got, exp, values, offsets, ())
+
+
+def test_quantile_order_and_subsets(rollup):
+    d = synth.make_series("c1", seed=8, max_series=12)
+    for qs in ([0.99, 0.5], [0.5], [0.25, 0.25, 0.75, 0.1]):
+        got = rollup.series_rollup(d["values"], d["offsets"], qs)
+        exp = ro.series_rollup_np(d["values"], d["offsets"], qs)
+        assert_series_parity(got, exp, d["values"], d["offsets"], qs)
+    got = rollup.series_rollup(d["values"], d["offsets"], QS, want=("count",))
+    assert set(got) == {"count", "quantiles"}
+
+
+def test_chunked_host_pipeline_matches_device_path(rollup):
+    """> 256 MB of samples exercises the double-buffered H2D pipeline; properties at full length:
+    count/min/max/quantile invariants instead of a CPU oracle over the whole batch."""
+    import torch
+    n, L = 1100, 40320                                   # 355 MB
+    vals, offs, _ = synth.make_series_torch("c2", 9, "cuda", n_series_override=n)
+    host = vals.cpu().numpy()
+    offsets = offs.cpu().numpy()
+    got = rollup.series_rollup(host, offsets, QS)
+    # device-pointer entry point on the same data
+    outs = {k: torch.zeros(n, dtype=torch.float64, device="cuda") for k in ("sum", "mean", "min", "max", "last")}
+    cnt = torch.zeros(n, dtype=torch.int64, device="cuda")
+    qt = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
+    rollup.series_rollup_dev(vals.data_ptr(), offs.data_ptr(), n, QS, outs["sum"].data_ptr(), outs["mean"].data_ptr(),
+                             outs["min"].data_ptr(), outs["max"].data_ptr(), outs["last"].data_ptr(), cnt.data_ptr(),
+                             qt.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    for k in outs:
+        assert np.array_equal(_bits(got[k]), _bits(outs[k].cpu().numpy())), k
+    assert np.array_equal(got["count"], cnt.cpu().numpy())
+    assert np.array_equal(_bits(got["quantiles"]), _bits(qt.cpu().numpy()))
+    # oracle on a sample of the series, properties on all
+    pick = np.arange(0, n, 37)
+    sub_off = np.concatenate([[0], np.cumsum(np.full(len(pick), L))]).astype(np.int64)
+    sub_val = np.concatenate([host[offsets[i]:offsets[i + 1]] for i in pick])
+    exp = c_oracle.series_rollup(sub_val, sub_off, QS, nthreads=8)
+    sub = {k: (v[pick] if k != "quantiles" else v[pick]) for k, v in got.items()}
+    assert_series_parity(sub, exp, sub_val, sub_off, QS)
+    q = got["quantiles"]
+    assert np.all(got["min"] <= q[:, 0]) and np.all(q[:, 0] <= q[:, 1]) and np.all(q[:, 1] <= q[:, 2])
+    assert np.all(q[:, 2] <= got["max"])
+
+
+def test_errors_are_loud(rollup):
+    from kubeoperator_b200 import KoRollupError
+    with pytest.raises(KoRollupError):
+        rollup.series_rollup(np.zeros(4), np.array([0, 3, 2, 4]), QS)          # decreasing offsets
+    with pytest.raises(KoRollupError):
+        rollup.series_rollup(np.zeros(4), np.array([0, 4]), [0.1, 0.2, 0.3, 0.4, 0.5])   # too many quantiles
+    with pytest.raises(KoRollupError):
+        rollup.series_rollup(np.zeros(4), np.array([0, 4]), [1.5])
+    out = rollup.series_rollup(np.zeros(0), np.array([0]), QS)                 # zero series is fine
+    assert len(out["count"]) == 0
