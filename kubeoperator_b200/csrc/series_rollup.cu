@@ -537,20 +537,22 @@ __device__ void build_first_plan(Plan* pl, const unsigned long long* skeys, int 
     int need[NI_MAX];
     int total = 0;
     for (int i = 0; i < ni; ++i) {
-        const bool lower_open = lo[i] < 0, upper_open = hi[i] >= valid_s;
-        unsigned long long kA = lower_open ? KO_KEY_NINF : skeys[lo[i]];
-        unsigned long long kB;
-        if (upper_open) kB = KO_KEY_PINF;
-        else {
-            unsigned long long kh = skeys[hi[i]];
+        // Brackets are clamped to the sample's own extremes (a target beyond them is a rare miss that the
+        // refinement passes catch); with no valid sample the bracket is everything.
+        const bool any = valid_s > 0;
+        const int a0 = lo[i] < 0 ? 0 : lo[i], b0 = hi[i] >= valid_s ? valid_s - 1 : hi[i];
+        unsigned long long kA = any ? skeys[a0] : KO_KEY_NINF;
+        unsigned long long kB = KO_KEY_PINF;
+        if (any) {
+            const unsigned long long kh = skeys[b0];
             kB = (kh >= KO_KEY_PINF) ? KO_KEY_PINF : kh + 1;
         }
         int mode = M_CAPTURE;
-        if (!lower_open && !upper_open && skeys[lo[i]] == skeys[hi[i]]) mode = M_COUNT;  // one tie group
-        if (kB <= kA) {  // degenerate (only +inf above): count only
-            kB = kA + 1;
+        if (any && skeys[a0] == skeys[b0]) mode = M_COUNT;  // the sample sees one tie group here
+        if (kB <= kA) {  // only +inf in range: count it
+            kA = KO_KEY_PINF - 1;
+            kB = KO_KEY_PINF;
             mode = M_COUNT;
-            if (kA >= KO_KEY_PINF) { kA = KO_KEY_PINF - 1; kB = KO_KEY_PINF; }
         }
         pl->kA[i] = kA;
         pl->kB[i] = kB;
@@ -560,7 +562,6 @@ __device__ void build_first_plan(Plan* pl, const unsigned long long* skeys, int 
         pl->mode[i] = mode;
         need[i] = 0;
         if (mode == M_CAPTURE) {
-            const int a0 = lower_open ? 0 : lo[i], b0 = upper_open ? valid_s - 1 : hi[i];
             const double mass = valid_s > 0 ? (double)(b0 - a0 + 3) / (double)valid_s : 1.0;
             const double per_thread = fmin(mass, 1.0) * (double)L / (double)NCONS;
             need[i] = (int)ceil(per_thread) + 1;
@@ -611,7 +612,8 @@ __device__ void build_refine_plan(Plan* pl, int nq, const unsigned long long* nk
         pl->tA[i] = ko_key2d(nkA[j]);
         pl->tB[i] = ko_key2d(nkB[j]);
         pl->hshift[i] = hist_shift(nkA[j], nkB[j]);
-        need[i] = (int)((npop[j] + NCONS - 1) / NCONS);
+        const unsigned long long per = ((unsigned long long)npop[j] + NCONS - 1) / NCONS;
+        need[i] = (int)(per > 100000ull ? 100000ull : per);
         need[i] = need[i] + need[i] / 2 + 3;
         pl->mode[i] = M_CAPTURE;
     }
