@@ -38,6 +38,7 @@ extern "C" {
 #define KO_BAND_YELLOW 1       /* (60, 80]                                                             */
 #define KO_BAND_RED 2          /* > 80                                                                 */
 #define KO_HIST_BINS 65536     /* bins of one fleet-quantile refinement round                          */
+#define KO_STATIC_MAX_SERIES 65536 /* largest batch of ko_series_rollup_static                         */
 
 typedef struct ko_ctx ko_ctx;
 
@@ -110,6 +111,26 @@ int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_o
                          int64_t n_series, const double* q, int nq, double* d_out_sum,
                          double* d_out_mean, double* d_out_min, double* d_out_max, double* d_out_last,
                          int64_t* d_out_count, double* d_out_quantiles, void* stream);
+
+/* Same kernels and results as ko_series_rollup_dev, for callers that must not allocate device memory when
+ * they ask for a rollup: a worker whose GPU memory belongs entirely to another component's pool, a request
+ * thread that cannot afford the device-wide synchronisation hidden in cudaMalloc / cudaFree, or any section of
+ * a program in which the CUDA allocator is off limits.  This entry point has NO COUNTERPART IN THE REFERENCE
+ * (and needs no ko_ctx): the work list and counters that ko_series_rollup_dev keeps in memory it cudaMallocs on
+ * demand live here in a fixed array inside the library image, 4*(8+KO_STATIC_MAX_SERIES) bytes = 256 KiB,
+ * which every GPU that loads the library holds until the process exits.  It calls no cudaMalloc, cudaFree or
+ * other allocating routine.  Limits and rules:
+ *   - n_series > KO_STATIC_MAX_SERIES is refused with KO_EINVAL (split the batch);
+ *   - the first call on a device looks up the array's device address and sets the kernels' shared-memory
+ *     attributes; make that first call before any stream capture begins;
+ *   - all calls on a device share the array, which keeps the previous call's contents (its counters are
+ *     cleared on `stream` at the start of each call): calls whose kernels could overlap on the GPU race on it,
+ *     so issue them on one stream or otherwise serialise them.
+ * `device` is the CUDA ordinal; it is made current.  Pointers are device pointers as in ko_series_rollup_dev. */
+int ko_series_rollup_static(int device, const double* d_values, const int64_t* d_offsets, int64_t n_series,
+                            const double* q, int nq, double* d_out_sum, double* d_out_mean, double* d_out_min,
+                            double* d_out_max, double* d_out_last, int64_t* d_out_count, double* d_out_quantiles,
+                            void* stream);
 
 /* ---- a7: scrape-target availability rate --------------------------------------------------------------
  * Replaces PrometheusClient.calculate_available_rate, core/apps/kubeops_api/prometheus_client.py:75-85, for

@@ -1139,3 +1139,118 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
     }
     return KO_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// ko_series_rollup_static — the same three kernels with their scratch (work cursor, flags, list of long
+// series) in a fixed array that lives in the library image instead of in memory obtained at run time.
+//
+// Who needs this: a caller that may not allocate device memory at the moment it wants a rollup.  Examples are
+// a process whose GPU memory has been handed over completely to another component's pool (a trainer or an
+// inference server sharing the GPU with the monitoring worker), a request thread that must not run into the
+// device-wide synchronisation that cudaMalloc / cudaFree imply, and code running between two points where the
+// CUDA allocator is off limits.  ko_series_rollup_dev grows ctx->scratch with cudaMalloc when a bigger batch
+// arrives; this entry point never does: no cudaMalloc, no cudaFree, no ctx (ko_init creates streams/events).
+//
+// Price: every GPU that loads libkorollup.so holds the array until the process exits
+// (4 * (8 + KO_STATIC_MAX_SERIES) bytes = 256 KiB), batches above KO_STATIC_MAX_SERIES series are refused, and
+// all calls on one device share the array: it keeps the previous call's contents (the counters are cleared on
+// the caller's stream at the start of every call), so two calls whose kernels may overlap on the GPU — different
+// streams, or threads launching concurrently — race on it.  Serialise them on one stream.
+namespace {
+
+static __device__ __align__(256) int g_static_scratch[8 + KO_STATIC_MAX_SERIES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+struct StaticDevice {
+    int* scratch = nullptr;  // DEVICE address of g_static_scratch on that GPU
+    int num_sms = 0;
+    bool ready = false;
+};
+StaticDevice g_static_dev[STATIC_MAX_DEVICES];
+std::mutex g_static_mu;
+
+// Once per device, with that device current: g_static_scratch as written in host code is only a host-side
+// handle of the symbol, not an address a kernel can use, so the device address is looked up here.
+int static_setup(int device, StaticDevice** out) {
+    KO_REQUIRE(device >= 0 && device < STATIC_MAX_DEVICES, "ko_series_rollup_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    KO_CUDA(cudaSetDevice(device));
+    StaticDevice* sd = &g_static_dev[device];
+    if (!sd->ready) {
+        int* ptr = nullptr;
+        KO_CUDA(cudaGetSymbolAddress((void**)&ptr, g_static_scratch));
+        KO_REQUIRE(ptr != nullptr, "ko_series_rollup_static: cudaGetSymbolAddress returned NULL");
+        int sms = 0;
+        KO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        KO_CUDA(cudaFuncSetAttribute(series_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LONG_SMEM_BYTES));
+        KO_CUDA(cudaFuncSetAttribute(series_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     8 * SMALL_MAX * 8 + 8 * HBINS * 4));
+        sd->scratch = ptr;
+        sd->num_sms = sms;
+        sd->ready = true;
+    }
+    *out = sd;
+    return KO_OK;
+}
+
+}  // namespace
+
+extern "C" int ko_series_rollup_static(int device, const double* d_values, const int64_t* d_offsets,
+                                       int64_t n_series, const double* q, int nq, double* d_out_sum,
+                                       double* d_out_mean, double* d_out_min, double* d_out_max, double* d_out_last,
+                                       int64_t* d_out_count, double* d_out_quantiles, void* stream) {
+    KO_REQUIRE(n_series >= 0, "ko_series_rollup_static: negative n_series");
+    if (n_series > KO_STATIC_MAX_SERIES) {
+        ko_set_error("ko_series_rollup_static: %lld series exceed the fixed scratch of KO_STATIC_MAX_SERIES=%d; "
+                     "split the batch or use ko_series_rollup_dev",
+                     (long long)n_series, KO_STATIC_MAX_SERIES);
+        return KO_EINVAL;
+    }
+    KO_REQUIRE(nq >= 0 && nq <= KO_MAX_QUANTILES, "ko_series_rollup_static: nq must be 0..KO_MAX_QUANTILES");
+    KO_REQUIRE(nq == 0 || q, "ko_series_rollup_static: q is NULL");
+    StaticDevice* sd = nullptr;
+    int rc = static_setup(device, &sd);  // first call on a device: symbol lookup + kernel attributes
+    if (rc) return rc;
+    if (n_series == 0) return KO_OK;
+    KO_REQUIRE(d_values && d_offsets, "ko_series_rollup_static: NULL input");
+    SeriesArgs a;
+    a.values = d_values;
+    a.offsets = d_offsets;
+    a.n_series = n_series;
+    a.out_sum = d_out_sum;
+    a.out_mean = d_out_mean;
+    a.out_min = d_out_min;
+    a.out_max = d_out_max;
+    a.out_last = d_out_last;
+    a.out_count = d_out_count;
+    a.out_quant = d_out_quantiles;
+    a.counters = sd->scratch;
+    a.long_list = sd->scratch + 8;
+    a.nq = nq;
+    for (int j = 0; j < NI_MAX; ++j) {
+        a.q[j] = 0.0;
+        a.qcol[j] = 0;
+    }
+    for (int j = 0; j < nq; ++j) {  // ascending quantiles, remembering the caller's column
+        KO_REQUIRE(q[j] >= 0.0 && q[j] <= 1.0, "ko_series_rollup_static: quantile outside [0,1]");
+        int k = j;
+        while (k > 0 && a.q[k - 1] > q[j]) {
+            a.q[k] = a.q[k - 1];
+            a.qcol[k] = a.qcol[k - 1];
+            --k;
+        }
+        a.q[k] = q[j];
+        a.qcol[k] = j;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array still holds the last call's cursor / flags / list: the eight counters must start at zero
+    KO_CUDA(cudaMemsetAsync(sd->scratch, 0, 8 * sizeof(int), st));
+    classify_series<<<(unsigned)((n_series + 255) / 256), 256, 0, st>>>(a);
+    const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
+    series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, st>>>(a);
+    int grid = 2 * sd->num_sms;
+    if ((int64_t)grid > n_series) grid = (int)n_series;
+    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
+    KO_CUDA(cudaGetLastError());
+    return KO_OK;
+}

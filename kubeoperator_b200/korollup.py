@@ -38,6 +38,7 @@ ABI = {
     "ko_stable_desc_order": [_c_vp, _c_vp, _c_i64, _c_vp],
     "ko_series_rollup": [_c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_int] + [_c_vp] * 7,
     "ko_series_rollup_dev": [_c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_int] + [_c_vp] * 7 + [_c_vp],
+    "ko_series_rollup_static": [_c_int, _c_vp, _c_vp, _c_i64, _c_vp, _c_int] + [_c_vp] * 7 + [_c_vp],
     "ko_available_rate": [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_vp],
     "ko_fleet_rollup": [_c_vp] + [_c_vp] * 6 + [_c_i64, _c_vp],
     "ko_key_histogram": [_c_vp, _c_vp, _c_i64, _c_int, ctypes.c_uint64, ctypes.c_uint64, _c_vp],
@@ -91,6 +92,24 @@ def _ptr(a):
 
 def _arr(a, dtype):
     return np.ascontiguousarray(a, dtype=dtype)
+
+
+STATIC_MAX_SERIES = 65536
+
+
+def series_rollup_static(device, d_values, d_offsets, n_series, qs, d_sum=0, d_mean=0, d_min=0, d_max=0, d_last=0,
+                         d_count=0, d_quant=0, stream=0):
+    """``ko_series_rollup_static``: the device-pointer series rollup for callers that must not allocate GPU
+    memory (no ``Rollup`` / ko_ctx needed, nothing is cudaMalloc'ed; scratch is a fixed 256 KiB array inside the
+    library).  At most ``STATIC_MAX_SERIES`` series per call; calls on one device must not overlap on the GPU;
+    make the first call on a device before any stream capture.  Arguments as ``Rollup.series_rollup_dev``."""
+    lib = load_library()
+    q = _arr(qs, np.float64)
+    rc = lib.ko_series_rollup_static(int(device), d_values, d_offsets, int(n_series), _ptr(q) if len(q) else None,
+                                     len(q), d_sum or None, d_mean or None, d_min or None, d_max or None,
+                                     d_last or None, d_count or None, d_quant or None, stream or None)
+    if rc != 0:
+        raise KoRollupError(rc, lib.ko_last_error().decode())
 
 
 class Rollup:
