@@ -286,7 +286,7 @@ def run_ours(args, rank, world, local_rank):
                     "includes": "ko_series_rollup (pinned host -> H2D -> kernels -> D2H) + ko_cluster_rollup + "
                                 "ko_pod_rollup through the C ABI"},
             "gpu_launches": int(launches), "clocks": clocks,
-            "series_needing_extra_pass": int(c1["series_fallback"]),
+            "series_needing_extra_pass": int(c1e["series_fallback"]),
         }
         if world > 1:
             line["fleet_p95_node_cpu_mean"] = fleet_q[0]

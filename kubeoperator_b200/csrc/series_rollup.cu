@@ -9,7 +9,7 @@
 //   series_long       — persistent CTAs, one series at a time per CTA: a producer warp streams the series
 //                       through a 4-stage TMA ring (cp.async.bulk + mbarrier) while 8 consumer warps
 //                       fuse the statistics with a bracketed selection: a strided pre-sample (sorted in
-//                       shared memory) gives a value bracket per quantile; the single streaming pass counts
+//                       registers / shuffles) gives a value bracket per quantile; the single streaming pass counts
 //                       samples below each bracket and captures the few inside it into shared memory,
 //                       where a shared-memory radix select finds the exact order statistic.  Brackets
 //                       that miss or overflow are refined by further passes (histogram in key space),
@@ -29,6 +29,7 @@ constexpr int STAGES = 4;
 constexpr int SAMPLE_BIG = 1024;     // pre-sample size for L >= 8192
 constexpr int SAMPLE_SMALL = 256;    // pre-sample size for shorter long series
 constexpr int SLOTS = 32;            // thread-private candidate slots per consumer thread
+constexpr int SLOTS_H = 24;          // ... when a histogram interval is active (its per-bin min/max keys use the rest)
 constexpr int OVQ = 1024;            // shared overflow queue entries
 constexpr int NI_MAX = KO_MAX_QUANTILES;
 constexpr int HBINS = 256;
@@ -75,6 +76,10 @@ struct Plan {
     unsigned ovcnt[NI_MAX];
     int more;
     int passes;
+    int fast;       // first pass can use the specialised loop (capture / count-only brackets + upper tail)
+    int tail_iv;    // index of the upper-tail interval of the fast pass, or -1
+    unsigned cmp_cnt;
+    double trash;   // sink of captures that find both the private slots and the overflow queue full
     unsigned nvalid;
     int sample_valid;
     double sum, mn, mx, last;
@@ -122,6 +127,25 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
             smem_u32(dst)),
         "l"(src), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
+}
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "KO_WAITA:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra KO_DONEA;\n"
+        "bra KO_WAITA;\n"
+        "KO_DONEA:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void lds_v2f64(uint32_t addr, double& x, double& y) {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr));
 }
 __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NCONS) : "memory"); }
 
@@ -316,10 +340,12 @@ struct LongSmem {
     uint64_t* empty;              // STAGES
 };
 
+constexpr int CMP_MAX = NI_MAX * HBINS * 4 / 8;  // compacted keys of the radix select alias the histograms
 constexpr size_t LONG_SMEM_BYTES = (size_t)STAGES * TILE * 8 + (size_t)SLOTS * NCONS * 8 + (size_t)OVQ * 8 +
-                                   (size_t)NI_MAX * HBINS * 4 + (size_t)HBINS * 4 + (size_t)NCWARPS * 4 * 8 +
-                                   1024 /* Plan */ + (size_t)2 * STAGES * 8;
+                                   (size_t)NI_MAX * HBINS * 4 + (size_t)HBINS * 4 +
+                                   (size_t)NCWARPS * 4 * 8 + 1024 /* Plan */ + (size_t)2 * STAGES * 8;
 static_assert(sizeof(Plan) <= 1024, "Plan must fit its shared-memory slot");
+static_assert(LONG_SMEM_BYTES <= 115712, "two CTAs per SM need <= 113 KB each");
 
 struct Acc {
     double sum, mn, mx;
@@ -330,16 +356,165 @@ struct Acc {
     uint32_t pend[NI_MAX];
 };
 
-template <int NI, bool STATS>
-__device__ __forceinline__ void process_elem(double x, Acc& acc, const double (&tA)[NI_MAX],
-                                             const double (&tB)[NI_MAX], const LongSmem& sm) {
-    if (STATS) {
-        if (x == x) {
-            acc.sum += x;
-            acc.nvalid++;
+// Rare: the thread's private slots are full — claim an entry of the interval's shared overflow queue and return
+// its shared-memory address (a scratch word when the queue is full too; the attempt is still counted).
+__device__ __noinline__ uint32_t overflow_addr(Plan* pl, double* ovq, int i) {
+    const unsigned pos = atomicAdd(&pl->ovcnt[i], 1u);
+    if (pos < (unsigned)pl->ovcap[i]) return smem_u32(ovq + pl->ov0[i] + pos);
+    return smem_u32(&pl->trash);
+}
+__device__ __forceinline__ void sts_f64(uint32_t addr, double x) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(x) : "memory");
+}
+// Store x into the thread's next private slot of interval i (or the overflow queue when they are full).
+__device__ __forceinline__ void capture(uint32_t pool32, uint32_t& p, uint32_t pend, const LongSmem& sm, int i,
+                                        double x) {
+    uint32_t addr = pool32 + p;
+    if (p == pend) addr = overflow_addr(sm.plan, sm.ovq, i);
+    else p += NCONS * 8;
+    sts_f64(addr, x);
+}
+
+// Histogram mode (series with heavy ties, brackets too wide for shared memory, refinement passes): 256 bins
+// linear in key space over the bracket, plus the smallest and largest key seen per bin — a bin that holds a
+// single distinct value (the usual case for integer-valued series) settles its quantile without another pass.
+__device__ __forceinline__ unsigned long long* hist_bmin(unsigned char* pool) {
+    return reinterpret_cast<unsigned long long*>(pool + (size_t)SLOTS_H * NCONS * 8);
+}
+__device__ __forceinline__ unsigned long long* hist_bmax(unsigned char* pool) {
+    return hist_bmin(pool) + NI_MAX * HBINS;
+}
+__device__ __noinline__ void hist_add(const Plan* pl, unsigned* hist, unsigned char* pool, int i, double x) {
+    const unsigned long long k = ko_okey(x + 0.0);
+    const unsigned b = (unsigned)((k - pl->kA[i]) >> pl->hshift[i]);
+    atomicAdd(&hist[i * HBINS + b], 1u);
+    atomicMin(&hist_bmin(pool)[i * HBINS + b], k);
+    atomicMax(&hist_bmax(pool)[i * HBINS + b], k);
+}
+
+// sum += x, nvalid += 1 unless x is NaN (predicated, no selects)
+__device__ __forceinline__ void acc_valid(double x, double& sum, unsigned& nv) {
+    asm("{\n.reg .pred p;\nsetp.eq.f64 p, %2, %2;\n@p add.f64 %0, %0, %2;\n@p add.u32 %1, %1, 1;\n}"
+        : "+d"(sum), "+r"(nv)
+        : "d"(x));
+}
+
+// ---- fast first pass: NB value brackets [tA, tB) (capture or count-only) + an optional upper tail x >= tT.
+template <int NB, bool TAIL>
+struct FastRegs {
+    double tA[NB > 0 ? NB : 1], tB[NB > 0 ? NB : 1];
+    bool cap[NB > 0 ? NB : 1];
+    double tT;
+};
+
+template <int NB, bool TAIL>
+__device__ __forceinline__ void fast_elems4(const double (&x)[4], Acc& acc, const FastRegs<NB, TAIL>& fr,
+                                            const LongSmem& sm, uint32_t pool32) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        acc_valid(x[e], acc.sum, acc.nvalid);
+        if (x[e] < acc.mn) acc.mn = x[e];
+        if (x[e] > acc.mx) acc.mx = x[e];
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+        bool in[4];
+        bool any = false;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const bool lt = x[e] < fr.tA[i];
+            acc.cA[i] += lt ? 1u : 0u;
+            in[e] = !lt && (x[e] < fr.tB[i]);
+            any = any || in[e];
         }
-        acc.mn = fmin(acc.mn, x);
-        acc.mx = fmax(acc.mx, x);
+        if (any) {
+            if (fr.cap[i]) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (in[e]) capture(pool32, acc.p[i], acc.pend[i], sm, i, x[e]);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc.cin[i] += in[e] ? 1u : 0u;
+            }
+        }
+    }
+    if (TAIL) {
+        constexpr int i = NB;
+        bool in[4];
+        bool any = false;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            in[e] = x[e] >= fr.tT;
+            any = any || in[e];
+        }
+        if (any) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (in[e]) capture(pool32, acc.p[i], acc.pend[i], sm, i, x[e]);
+            }
+        }
+    }
+}
+
+template <int NB, bool TAIL>
+__device__ __forceinline__ void fast_elem1(double x, Acc& acc, const FastRegs<NB, TAIL>& fr, const LongSmem& sm) {
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    const double v[4] = {x, nan, nan, nan};  // NaN is neither valid nor inside any bracket
+    fast_elems4<NB, TAIL>(v, acc, fr, sm, smem_u32(sm.pool));
+}
+
+template <int NB, bool TAIL>
+__device__ __forceinline__ void consume_fast(const double* __restrict__ v, int L, int head, int body, int ntiles,
+                                             uint32_t g, Acc& acc, const LongSmem& sm, int ctid, int lane) {
+    FastRegs<NB, TAIL> fr;
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+        fr.tA[i] = sm.plan->tA[i];
+        fr.tB[i] = sm.plan->tB[i];
+        fr.cap[i] = sm.plan->mode[i] == M_CAPTURE;
+    }
+    fr.tT = TAIL ? sm.plan->tA[NB] : 0.0;
+    if (ctid == 0 && head) fast_elem1<NB, TAIL>(v[0], acc, fr, sm);
+    if (ctid == 1 && head + body < L) fast_elem1<NB, TAIL>(v[L - 1], acc, fr, sm);
+    const uint32_t full0 = smem_u32(sm.full), empty0 = smem_u32(sm.empty);
+    const uint32_t ring0 = smem_u32(sm.ring) + (uint32_t)ctid * 16u;
+    const uint32_t pool32 = smem_u32(sm.pool);
+    uint32_t s = g % STAGES, par = (g / STAGES) & 1u;
+    int rem2 = body >> 1;  // double2 elements left
+    for (int t = 0; t < ntiles; ++t) {
+        mbar_wait_addr(full0 + s * 8u, par);
+        const uint32_t base = ring0 + s * (uint32_t)(TILE * 8);
+        double x[4];
+        if (rem2 >= TILE / 2) {
+            lds_v2f64(base, x[0], x[1]);
+            lds_v2f64(base + NCONS * 16, x[2], x[3]);
+        } else {
+            const double nan = __longlong_as_double(0x7FF8000000000000LL);
+            x[0] = x[1] = x[2] = x[3] = nan;
+            if (ctid < rem2) lds_v2f64(base, x[0], x[1]);
+            if (ctid + NCONS < rem2) lds_v2f64(base + NCONS * 16, x[2], x[3]);
+        }
+        fast_elems4<NB, TAIL>(x, acc, fr, sm, pool32);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        rem2 -= TILE / 2;
+        if (++s == STAGES) {
+            s = 0;
+            par ^= 1u;
+        }
+    }
+}
+
+// ---- generic pass (refinement passes, histogram first passes): NI intervals of any mode.
+template <int NI, bool STATS>
+__device__ __forceinline__ void generic_elem(double x, Acc& acc, const double (&tA)[NI_MAX],
+                                             const double (&tB)[NI_MAX], const int (&mode)[NI_MAX],
+                                             const LongSmem& sm, uint32_t pool32) {
+    if (STATS) {
+        acc_valid(x, acc.sum, acc.nvalid);
+        if (x < acc.mn) acc.mn = x;
+        if (x > acc.mx) acc.mx = x;
     }
 #pragma unroll
     for (int i = 0; i < NI; ++i) {
@@ -347,94 +522,138 @@ __device__ __forceinline__ void process_elem(double x, Acc& acc, const double (&
         acc.cA[i] += lt ? 1u : 0u;
         const bool in = !lt && (x < tB[i]);
         if (in) {
-            const Plan* pl = sm.plan;
-            const int mode = pl->mode[i];
-            const double xc = x + 0.0;
-            if (mode == M_CAPTURE) {
-                if (acc.p[i] != acc.pend[i]) {
-                    *reinterpret_cast<double*>(sm.pool + acc.p[i]) = xc;
-                    acc.p[i] += NCONS * 8;
-                } else {
-                    unsigned pos = atomicAdd(&sm.plan->ovcnt[i], 1u);
-                    if (pos < (unsigned)pl->ovcap[i]) sm.ovq[pl->ov0[i] + pos] = xc;
-                }
-            } else if (mode == M_HIST) {
-                unsigned long long k = ko_okey(xc);
-                unsigned b = (unsigned)((k - pl->kA[i]) >> pl->hshift[i]);
-                atomicAdd(&sm.hist[i * HBINS + b], 1u);
-            } else {
-                acc.cin[i]++;
-            }
+            if (mode[i] == M_CAPTURE) capture(pool32, acc.p[i], acc.pend[i], sm, i, x);
+            else if (mode[i] == M_HIST) hist_add(sm.plan, sm.hist, sm.pool, i, x);
+            else acc.cin[i]++;
         }
     }
 }
 
 template <int NI, bool STATS>
-__device__ __forceinline__ void consume_pass(const double* __restrict__ v, int L, int head, int body, int ntiles, uint32_t g,
-                             Acc& acc, const LongSmem& sm, int ctid, int lane) {
+__device__ __noinline__ void consume_generic(const double* __restrict__ v, int L, int head, int body, int ntiles,
+                                             uint32_t g, Acc* accp, const LongSmem* smp, int ctid, int lane) {
+    const LongSmem& sm = *smp;
+    Acc acc = *accp;
     double tA[NI_MAX], tB[NI_MAX];
+    int mode[NI_MAX];
 #pragma unroll
     for (int i = 0; i < NI_MAX; ++i) {
         tA[i] = (i < NI) ? sm.plan->tA[i] : 0.0;
         tB[i] = (i < NI) ? sm.plan->tB[i] : 0.0;
+        mode[i] = (i < NI) ? sm.plan->mode[i] : M_COUNT;
     }
-    // unaligned head / tail element (the TMA body starts 16-byte aligned and has an even length)
-    if (ctid == 0 && head) process_elem<NI, STATS>(v[0], acc, tA, tB, sm);
-    if (ctid == 1 && head + body < L) process_elem<NI, STATS>(v[L - 1], acc, tA, tB, sm);
+    const uint32_t pool32 = smem_u32(sm.pool);
+    if (ctid == 0 && head) generic_elem<NI, STATS>(v[0], acc, tA, tB, mode, sm, pool32);
+    if (ctid == 1 && head + body < L) generic_elem<NI, STATS>(v[L - 1], acc, tA, tB, mode, sm, pool32);
+    const uint32_t full0 = smem_u32(sm.full), empty0 = smem_u32(sm.empty);
+    const uint32_t ring0 = smem_u32(sm.ring) + (uint32_t)ctid * 16u;
+    uint32_t s = g % STAGES, par = (g / STAGES) & 1u;
+    int rem2 = body >> 1;
     for (int t = 0; t < ntiles; ++t) {
-        const uint32_t gg = g + (uint32_t)t;
-        const int s = (int)(gg % STAGES);
-        mbar_wait(&sm.full[s], (gg / STAGES) & 1u);
-        const double2* st = reinterpret_cast<const double2*>(sm.ring + (size_t)s * TILE);
-        const int n2 = min(TILE, body - t * TILE) >> 1;  // double2 elements in this tile
+        mbar_wait_addr(full0 + s * 8u, par);
+        const uint32_t base = ring0 + s * (uint32_t)(TILE * 8);
 #pragma unroll
-        for (int h = 0; h < TILE / 2 / NCONS; ++h) {
-            const int idx = h * NCONS + ctid;
-            if (idx < n2) {
-                const double2 d = st[idx];
-                process_elem<NI, STATS>(d.x, acc, tA, tB, sm);
-                process_elem<NI, STATS>(d.y, acc, tA, tB, sm);
+        for (int h = 0; h < 2; ++h) {
+            if (ctid + h * NCONS < rem2) {
+                double x0, x1;
+                lds_v2f64(base + h * NCONS * 16, x0, x1);
+                generic_elem<NI, STATS>(x0, acc, tA, tB, mode, sm, pool32);
+                generic_elem<NI, STATS>(x1, acc, tA, tB, mode, sm, pool32);
             }
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[s]);
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        rem2 -= TILE / 2;
+        if (++s == STAGES) {
+            s = 0;
+            par ^= 1u;
+        }
     }
+    *accp = acc;
 }
 
 template <bool STATS>
-__device__ __forceinline__ void consume_dispatch(int ni, const double* v, int L, int head, int body, int ntiles,
-                                                 uint32_t g, Acc& acc, const LongSmem& sm, int ctid, int lane) {
+__device__ __forceinline__ void consume_generic_dispatch(int ni, const double* v, int L, int head, int body,
+                                                         int ntiles, uint32_t g, Acc* acc, const LongSmem* sm,
+                                                         int ctid, int lane) {
     switch (ni) {
-        case 0: consume_pass<0, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
-        case 1: consume_pass<1, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
-        case 2: consume_pass<2, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
-        case 3: consume_pass<3, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
-        default: consume_pass<4, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 0: consume_generic<0, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 1: consume_generic<1, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 2: consume_generic<2, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        case 3: consume_generic<3, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
+        default: consume_generic<4, STATS>(v, L, head, body, ntiles, g, acc, sm, ctid, lane); break;
     }
 }
 
-// Bitonic sort of n (power of two, <= 1024) u64 keys in shared memory by the consumer threads.
-__device__ void bitonic_sort_keys(unsigned long long* keys, int n, int ctid) {
-    for (int k = 2; k <= n; k <<= 1) {
+// ---- pre-sample sort: 64-bit packed keys (top 54 key bits | 10-bit sample index), KPT keys per thread held in
+// registers.  Compare-exchange partners inside a thread are swapped in registers, partners inside the warp by
+// shuffles, the few remaining stages through shared memory.  n = KPT * NCONS keys, element index = tid*KPT + e.
+template <int KPT>
+__device__ __forceinline__ void sort_sample_regs(unsigned long long (&r)[KPT], unsigned long long* buf, int ctid) {
+    constexpr int N = KPT * NCONS;
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = ctid; t < n / 2; t += NCONS) {
-                // t-th compare-exchange of this stage: insert a zero bit at position log2(j)
-                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-                const int ixj = i | j;
-                const unsigned long long x = keys[i], y = keys[ixj];
-                const bool up = ((i & k) == 0);
-                if ((x > y) == up) {
-                    keys[i] = y;
-                    keys[ixj] = x;
+            if (j < KPT) {  // partner in the same thread
+#pragma unroll
+                for (int e = 0; e < KPT; ++e) {
+                    if ((e & j) == 0) {
+                        const int i = ctid * KPT + e;
+                        const bool up = (i & k) == 0;
+                        const unsigned long long a = r[e], b = r[e | j];
+                        const bool sw = (a > b) == up;
+                        r[e] = sw ? b : a;
+                        r[e | j] = sw ? a : b;
+                    }
+                }
+            } else if (j / KPT < 32) {  // partner in the same warp
+                const int m = j / KPT;
+                const bool lower = (ctid & m) == 0;
+#pragma unroll
+                for (int e = 0; e < KPT; ++e) {
+                    const int i = ctid * KPT + e;
+                    const bool up = (i & k) == 0;
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, r[e], m);
+                    const bool take_min = (lower == up);
+                    const bool o_less = o < r[e];
+                    r[e] = (o_less == take_min) ? o : r[e];
+                }
+            } else {  // partner in another warp: exchange through shared memory
+                const int m = j / KPT;
+                cons_sync();
+#pragma unroll
+                for (int e = 0; e < KPT; ++e) buf[ctid * KPT + e] = r[e];
+                cons_sync();
+                const bool lower = (ctid & m) == 0;
+#pragma unroll
+                for (int e = 0; e < KPT; ++e) {
+                    const int i = ctid * KPT + e;
+                    const bool up = (i & k) == 0;
+                    const unsigned long long o = buf[(ctid ^ m) * KPT + e];
+                    const bool take_min = (lower == up);
+                    const bool o_less = o < r[e];
+                    r[e] = (o_less == take_min) ? o : r[e];
                 }
             }
-            cons_sync();
         }
     }
+    cons_sync();
+#pragma unroll
+    for (int e = 0; e < KPT; ++e) buf[ctid * KPT + e] = r[e];
+    cons_sync();
 }
 
-// CTA-wide MSB-first radix select over the captured candidates of interval iv (thread-private slots plus
-// overflow queue).  All candidates have keys in [kA, kB).  Returns the key of local rank rho (1-based).
+// ---- CTA-wide MSB-first radix select over the captured candidates of interval iv (thread-private slots plus
+// overflow queue).  All candidate keys lie in [kA, kB).  Returns the key of local rank rho (1-based).  After the
+// first pass the few candidates that carry the chosen digit are compacted into a list, so later passes are short.
+template <typename F>
+__device__ __forceinline__ void for_each_candidate(const LongSmem& sm, const double* ovq, int ovn, uint32_t p0,
+                                                   uint32_t pcur, int ctid, F f) {
+    for (uint32_t p = p0; p != pcur; p += NCONS * 8) f(ko_okey(*reinterpret_cast<const double*>(sm.pool + p) + 0.0));
+    for (int i = ctid; i < ovn; i += NCONS) f(ko_okey(ovq[i] + 0.0));
+}
+
 __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsigned rho, uint32_t p0,
                                                uint32_t pcur, int ctid, int lane) {
     Plan* pl = sm.plan;
@@ -447,16 +666,21 @@ __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsig
     unsigned long long prefix = kA & mask;
     const int ovn = (int)min(pl->ovcnt[iv], (unsigned)pl->ovcap[iv]);
     const double* ovq = sm.ovq + pl->ov0[iv];
+    unsigned long long* cmp = reinterpret_cast<unsigned long long*>(sm.hist);  // free once the pass was decided
+    bool use_list = false;
+    int nlist = 0;
     for (;;) {
         sm.selhist[ctid] = 0;
         cons_sync();
-        for (uint32_t p = p0; p != pcur; p += NCONS * 8) {
-            unsigned long long k = ko_okey(*reinterpret_cast<const double*>(sm.pool + p));
-            if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
-        }
-        for (int i = ctid; i < ovn; i += NCONS) {
-            unsigned long long k = ko_okey(ovq[i]);
-            if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+        if (use_list) {
+            for (int i = ctid; i < nlist; i += NCONS) {
+                const unsigned long long k = cmp[i];
+                if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+            }
+        } else {
+            for_each_candidate(sm, ovq, ovn, p0, pcur, ctid, [&](unsigned long long k) {
+                if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+            });
         }
         cons_sync();
         if (ctid < 32) {
@@ -467,6 +691,7 @@ __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsig
                 pl->sel_digit = digit;
                 pl->sel_cum = before;
                 pl->sel_cnt = cnt;
+                pl->cmp_cnt = 0;
             }
         }
         cons_sync();
@@ -475,17 +700,25 @@ __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsig
         mask |= 0xFFull << shift;
         const unsigned cnt = pl->sel_cnt;
         if (shift == 0) return prefix;
-        if (cnt == 1) {  // a single candidate carries this prefix: fetch it
-            for (uint32_t p = p0; p != pcur; p += NCONS * 8) {
-                unsigned long long k = ko_okey(*reinterpret_cast<const double*>(sm.pool + p));
-                if ((k & mask) == prefix) pl->sel_key = k;
-            }
-            for (int i = ctid; i < ovn; i += NCONS) {
-                unsigned long long k = ko_okey(ovq[i]);
-                if ((k & mask) == prefix) pl->sel_key = k;
+        if (cnt == 1) {  // one candidate carries this prefix: fetch it
+            if (use_list) {
+                for (int i = ctid; i < nlist; i += NCONS)
+                    if ((cmp[i] & mask) == prefix) pl->sel_key = cmp[i];
+            } else {
+                for_each_candidate(sm, ovq, ovn, p0, pcur, ctid, [&](unsigned long long k) {
+                    if ((k & mask) == prefix) pl->sel_key = k;
+                });
             }
             cons_sync();
             return pl->sel_key;
+        }
+        if (!use_list && cnt <= (unsigned)CMP_MAX) {
+            for_each_candidate(sm, ovq, ovn, p0, pcur, ctid, [&](unsigned long long k) {
+                if ((k & mask) == prefix) cmp[atomicAdd(&pl->cmp_cnt, 1u)] = k;
+            });
+            cons_sync();
+            use_list = true;
+            nlist = (int)cnt;
         }
         shift -= 8;
     }
@@ -498,9 +731,10 @@ __device__ __forceinline__ int hist_shift(unsigned long long kA, unsigned long l
     return top - 7;
 }
 
-// Thread 0: derive the brackets of the first pass from the sorted pre-sample.
-__device__ void build_first_plan(Plan* pl, const unsigned long long* skeys, int s, int valid_s, int L,
-                                 const SeriesArgs& a) {
+// Thread 0: derive the intervals of the first pass from the sorted pre-sample.
+// spk: sorted packed keys (54 key bits | 10-bit index into ukeys); ukeys: the full keys in sample order.
+__device__ void build_first_plan(Plan* pl, const unsigned long long* spk, const unsigned long long* ukeys,
+                                 int valid_s, int L, const SeriesArgs& a) {
     const int nq = a.nq;
     int lo[NI_MAX], hi[NI_MAX];
     int ni = 0;
@@ -529,65 +763,95 @@ __device__ void build_first_plan(Plan* pl, const unsigned long long* skeys, int 
         pl->q_done[j] = 0;
         pl->q_act[j] = A_NONE;
     }
-    if (nq == 0) {
-        pl->ni = 0;
-        return;
-    }
     pl->ni = ni;
+    pl->fast = 1;
+    pl->tail_iv = -1;
+    if (nq == 0) return;
     int need[NI_MAX];
+    bool tail[NI_MAX];
     int total = 0;
     for (int i = 0; i < ni; ++i) {
         // Brackets are clamped to the sample's own extremes (a target beyond them is a rare miss that the
         // refinement passes catch); with no valid sample the bracket is everything.
         const bool any = valid_s > 0;
         const int a0 = lo[i] < 0 ? 0 : lo[i], b0 = hi[i] >= valid_s ? valid_s - 1 : hi[i];
-        unsigned long long kA = any ? skeys[a0] : KO_KEY_NINF;
-        unsigned long long kB = KO_KEY_PINF;
-        if (any) {
-            const unsigned long long kh = skeys[b0];
-            kB = (kh >= KO_KEY_PINF) ? KO_KEY_PINF : kh + 1;
-        }
+        unsigned long long kA = KO_KEY_NINF, kB = KO_KEY_PINF;
         int mode = M_CAPTURE;
-        if (any && skeys[a0] == skeys[b0]) mode = M_COUNT;  // the sample sees one tie group here
-        if (kB <= kA) {  // only +inf in range: count it
+        tail[i] = false;
+        if (any) {
+            unsigned long long ka = ukeys[spk[a0] & 1023ull], kb = ukeys[spk[b0] & 1023ull];
+            if (ka > kb) {  // both in one 54-bit bucket: order inside it is arbitrary
+                const unsigned long long t = ka;
+                ka = kb;
+                kb = t;
+            }
+            kA = ka;
+            if (ka == kb) {  // the sample sees a single value here: count its tie group
+                mode = M_COUNT;
+                kB = ka + 1;
+            } else if (hi[i] >= valid_s) {  // reaches beyond the sample maximum: everything >= kA
+                tail[i] = true;
+                kB = KO_KEY_PINF + 1;
+            } else {
+                kB = (kb >= KO_KEY_PINF) ? KO_KEY_PINF : kb + 1;
+            }
+        }
+        if (kB <= kA || (mode == M_COUNT && kA >= KO_KEY_PINF)) {  // only +inf in range
             kA = KO_KEY_PINF - 1;
             kB = KO_KEY_PINF;
             mode = M_COUNT;
+            tail[i] = false;
         }
         pl->kA[i] = kA;
         pl->kB[i] = kB;
-        pl->tA[i] = ko_key2d(kA);
-        pl->tB[i] = ko_key2d(kB);
-        pl->hshift[i] = hist_shift(kA, kB);
         pl->mode[i] = mode;
         need[i] = 0;
         if (mode == M_CAPTURE) {
-            const double mass = valid_s > 0 ? (double)(b0 - a0 + 3) / (double)valid_s : 1.0;
+            // the closed bracket holds the whole tie groups of its end values: widen the sample range over them
+            int ea = a0, eb = b0;
+            if (any) {
+                const unsigned long long ta = spk[a0] >> 10, tb = spk[b0] >> 10;
+                while (ea > 0 && (spk[ea - 1] >> 10) == ta) --ea;
+                while (eb < valid_s - 1 && (spk[eb + 1] >> 10) == tb) ++eb;
+                if (tail[i]) eb = valid_s - 1;
+            }
+            const double mass = valid_s > 0 ? (double)(eb - ea + 3) / (double)valid_s : 1.0;
             const double per_thread = fmin(mass, 1.0) * (double)L / (double)NCONS;
             need[i] = (int)ceil(per_thread) + 1;
             total += need[i];
         }
     }
+    int nbr = 0;
+    for (int i = 0; i < ni; ++i) nbr += tail[i] ? 0 : 1;
+    if (nbr > 2) pl->fast = 0;
     // intervals that cannot be captured in shared memory get a key-space histogram instead
-    while (total > SLOTS) {
+    while (total > (pl->fast ? SLOTS : SLOTS_H)) {
         int big = -1;
         for (int i = 0; i < ni; ++i)
             if (pl->mode[i] == M_CAPTURE && (big < 0 || need[i] > need[big])) big = i;
         if (big < 0) break;
         pl->mode[big] = M_HIST;
+        pl->fast = 0;
         total -= need[big];
         need[big] = 0;
     }
     int ncap = 0;
     for (int i = 0; i < ni; ++i) ncap += (pl->mode[i] == M_CAPTURE);
-    int slot = 0, spare = SLOTS - total, k = 0;
+    int slot = 0, spare = (pl->fast ? SLOTS : SLOTS_H) - total, k = 0;
     for (int i = 0; i < ni; ++i) {
+        if (tail[i]) {
+            if (pl->fast) pl->tail_iv = i;
+            else pl->kB[i] = KO_KEY_PINF;  // the generic pass compares against tB; +inf is settled by rank
+        }
+        pl->tA[i] = ko_key2d(pl->kA[i]);
+        pl->tB[i] = ko_key2d(pl->kB[i] > KO_KEY_PINF ? KO_KEY_PINF : pl->kB[i]);
+        pl->hshift[i] = hist_shift(pl->kA[i], pl->kB[i]);
         pl->slot0[i] = slot;
         pl->nslots[i] = 0;
         pl->ov0[i] = 0;
         pl->ovcap[i] = 0;
         if (pl->mode[i] == M_CAPTURE) {
-            int extra = spare / ncap;
+            const int extra = spare / ncap;
             pl->nslots[i] = need[i] + extra;
             slot += pl->nslots[i];
             pl->ov0[i] = k * (OVQ / ncap);
@@ -618,15 +882,17 @@ __device__ void build_refine_plan(Plan* pl, int nq, const unsigned long long* nk
         pl->mode[i] = M_CAPTURE;
     }
     pl->ni = ni;
+    pl->fast = 0;
+    pl->tail_iv = -1;
     // share the private slots evenly; what does not fit is histogrammed
     for (int i = 0; i < ni; ++i) {
-        if (need[i] > SLOTS / ni) pl->mode[i] = M_HIST;
+        if (need[i] > SLOTS_H / ni) pl->mode[i] = M_HIST;
         else ncap++;
     }
     int k = 0;
     for (int i = 0; i < ni; ++i) {
-        pl->slot0[i] = i * (SLOTS / ni);
-        pl->nslots[i] = (pl->mode[i] == M_CAPTURE) ? SLOTS / ni : 0;
+        pl->slot0[i] = i * (SLOTS_H / ni);
+        pl->nslots[i] = (pl->mode[i] == M_CAPTURE) ? SLOTS_H / ni : 0;
         pl->ov0[i] = 0;
         pl->ovcap[i] = 0;
         if (pl->mode[i] == M_CAPTURE) {
@@ -635,6 +901,45 @@ __device__ void build_refine_plan(Plan* pl, int nq, const unsigned long long* nk
             k++;
         }
     }
+}
+
+#ifdef KO_PHASE_TIMING
+__device__ unsigned long long g_phase[16];
+#define KO_TICK(slot)                                                   \
+    do {                                                                \
+        if (blockIdx.x == 0 && threadIdx.x == 0) {                      \
+            const unsigned long long _t = clock64();                    \
+            g_phase[slot] += _t - _tick;                                \
+            _tick = _t;                                                 \
+        }                                                               \
+    } while (0)
+#else
+#define KO_TICK(slot) do { } while (0)
+#endif
+
+template <int KPT>
+__device__ __forceinline__ void presample(const double* __restrict__ v, int L, const LongSmem& sm, int ctid) {
+    constexpr int S = KPT * NCONS;
+    Plan* pl = sm.plan;
+    unsigned long long* ukeys = reinterpret_cast<unsigned long long*>(sm.pool);        // full keys, sample order
+    unsigned long long* spk = ukeys + SAMPLE_BIG;                                      // sorted packed keys
+    unsigned long long r[KPT];
+    int nv = 0;
+#pragma unroll
+    for (int e = 0; e < KPT; ++e) {
+        const int i = ctid * KPT + e;
+        const long long idx = ((2LL * i + 1) * (long long)L) / (2LL * S);
+        const double x = v[idx];
+        const bool ok = (x == x);
+        const unsigned long long k = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
+        ukeys[i] = k;
+        r[e] = (k & ~1023ull) | (unsigned long long)i;
+        nv += ok;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nv += __shfl_xor_sync(0xffffffffu, nv, o);
+    if ((ctid & 31) == 0 && nv) atomicAdd(&pl->sample_valid, nv);
+    sort_sample_regs<KPT>(r, spk, ctid);  // ends with a consumer barrier: ukeys, spk, sample_valid visible
 }
 
 __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
@@ -667,12 +972,16 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
     const int n_long = a.counters[0];
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
     uint32_t g = 0;  // running ring tile index, identical in all threads
+#ifdef KO_PHASE_TIMING
+    unsigned long long _tick = clock64();
+#endif
 
     for (;;) {
         if (tid == 0) pl->work = atomicAdd(&a.counters[1], 1);
         __syncthreads();
         const int w = pl->work;
         if (w >= n_long) break;
+        KO_TICK(0);
         const int sid = a.long_list[w];
         const int64_t off0 = a.offsets[sid];
         const int L = (int)(a.offsets[sid + 1] - off0);
@@ -685,25 +994,13 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
 
         // ---------------- pre-sample, sort, first plan (consumers); last valid sample (thread 255)
         if (!producer) {
-            if (nq > 0) {
-                const int s = (L >= 8192) ? SAMPLE_BIG : SAMPLE_SMALL;
-                unsigned long long* skeys = reinterpret_cast<unsigned long long*>(sm.pool);
-                if (ctid == 0) pl->sample_valid = 0;
-                cons_sync();
-                int nv = 0;
-                for (int i = ctid; i < s; i += NCONS) {
-                    const long long idx = ((2LL * i + 1) * (long long)L) / (2LL * s);
-                    const double x = v[idx];
-                    const bool ok = (x == x);
-                    skeys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
-                    nv += ok;
-                }
-                if (nv) atomicAdd(&pl->sample_valid, nv);
-                cons_sync();
-                bitonic_sort_keys(skeys, s, ctid);
-                if (ctid == 0) build_first_plan(pl, skeys, s, pl->sample_valid, L, a);
-            } else if (ctid == 0) {
+            if (ctid == 0) {
+                pl->sample_valid = 0;
+                pl->passes = 0;
+                pl->more = 0;
                 pl->ni = 0;
+                pl->fast = 1;
+                pl->tail_iv = -1;
             }
             if (ctid == NCONS - 1) {
                 double lastv = nan;
@@ -716,9 +1013,16 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                 }
                 pl->last = lastv;
             }
-            if (ctid == 0) {
-                pl->passes = 0;
-                pl->more = 0;
+            if (nq > 0) {
+                cons_sync();
+                if (L >= 8192) presample<SAMPLE_BIG / NCONS>(v, L, sm, ctid);
+                else presample<SAMPLE_SMALL / NCONS>(v, L, sm, ctid);
+                KO_TICK(1);
+                if (ctid == 0) {
+                    const unsigned long long* ukeys = reinterpret_cast<const unsigned long long*>(sm.pool);
+                    build_first_plan(pl, ukeys + SAMPLE_BIG, ukeys, pl->sample_valid, L, a);
+                }
+                KO_TICK(2);
             }
         }
 
@@ -758,11 +1062,33 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                     pl->nin[ctid] = 0;
                     pl->ovcnt[ctid] = 0;
                 }
-                for (int i = ctid; i < NI_MAX * HBINS; i += NCONS) sm.hist[i] = 0;
+                if (!pl->fast) {
+                    for (int i = ctid; i < NI_MAX * HBINS; i += NCONS) {
+                        sm.hist[i] = 0;
+                        hist_bmin(sm.pool)[i] = ~0ull;
+                        hist_bmax(sm.pool)[i] = 0ull;
+                    }
+                }
                 cons_sync();
-                if (first) consume_dispatch<true>(ni, v, L, head, body, ntiles, g, acc, sm, ctid, lane);
-                else consume_dispatch<false>(ni, v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                if (first && pl->fast) {
+                    const int tl = pl->tail_iv >= 0 ? 1 : 0;
+                    const int nb = ni - tl;
+                    if (tl) {
+                        if (nb == 0) consume_fast<0, true>(v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                        else if (nb == 1) consume_fast<1, true>(v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                        else consume_fast<2, true>(v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                    } else {
+                        if (nb == 0) consume_fast<0, false>(v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                        else if (nb == 1) consume_fast<1, false>(v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                        else consume_fast<2, false>(v, L, head, body, ntiles, g, acc, sm, ctid, lane);
+                    }
+                } else if (first) {
+                    consume_generic_dispatch<true>(ni, v, L, head, body, ntiles, g, &acc, &sm, ctid, lane);
+                } else {
+                    consume_generic_dispatch<false>(ni, v, L, head, body, ntiles, g, &acc, &sm, ctid, lane);
+                }
 
+                KO_TICK(3);
                 // ---- reduce
                 if (first) {
                     const double ws = warp_sum(acc.sum), wmn = warp_min(acc.mn), wmx = warp_max(acc.mx);
@@ -805,6 +1131,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                         pl->nvalid = (unsigned)n;
                     }
                     const unsigned n = pl->nvalid;
+                    if (pl->tail_iv >= 0) {  // upper tail: everything not inside it is below it
+                        const int ti = pl->tail_iv;
+                        pl->cA[ti] = n - (pl->nin[ti] + pl->ovcnt[ti]);
+                    }
                     for (int j = 0; j < nq; ++j) {
                         pl->q_act[j] = A_NONE;
                         if (pl->q_done[j]) continue;
@@ -820,12 +1150,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                         if (pl->mode[i] == M_HIST) {
                             nb = 0;
                             for (int b = 0; b < HBINS; ++b) nb += sm.hist[i * HBINS + b];
-                            pl->nin[i] = nb;
-                            pl->ovcnt[i] = 0;
                         }
                         const unsigned long long kA = pl->kA[i], kB = pl->kB[i];
                         if (r <= cA) {  // below the bracket
-                            nkA[j] = KO_KEY_NINF;
+                            nkA[j] = ko_okey(pl->mn + 0.0);   // series minimum (known since the first pass)
                             nkB[j] = kA;
                             npop[j] = cA;
                             if (nkB[j] <= nkA[j]) {  // cannot happen (cA would be 0); be safe
@@ -838,8 +1166,13 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                                 pl->q_done[j] = 1;
                             } else {
                                 nkA[j] = kB;
-                                nkB[j] = KO_KEY_PINF;
+                                nkB[j] = ko_okey(pl->mx + 0.0);    // series maximum; +inf is settled by rank
+                                nkB[j] = nkB[j] >= KO_KEY_PINF ? KO_KEY_PINF : nkB[j] + 1;
                                 npop[j] = n - cA - nb;
+                                if (nkB[j] <= nkA[j]) {  // nothing finite above the bracket: it is +inf
+                                    pl->q_val[j] = ko_key2d(KO_KEY_PINF);
+                                    pl->q_done[j] = 1;
+                                }
                             }
                         } else {
                             const unsigned rho = r - cA;
@@ -852,7 +1185,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                                     pl->q_rho[j] = rho;
                                 } else {  // overflowed: histogram the same bracket next
                                     nkA[j] = kA;
-                                    nkB[j] = kB;
+                                    nkB[j] = kB > KO_KEY_PINF ? KO_KEY_PINF : kB;
                                     npop[j] = 0xFFFFFFFFu;
                                 }
                             } else {  // M_HIST: narrow to the bin holding the rank
@@ -867,8 +1200,12 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                                 const unsigned long long na = kA + ((unsigned long long)b << sh);
                                 unsigned long long nb2 = na + (1ull << sh);
                                 if (nb2 > kB || nb2 < na) nb2 = kB;
+                                const unsigned long long bmn = hist_bmin(sm.pool)[i * HBINS + b];
                                 if (nb2 - na == 1) {
                                     pl->q_val[j] = ko_key2d(na);
+                                    pl->q_done[j] = 1;
+                                } else if (bmn == hist_bmax(sm.pool)[i * HBINS + b]) {  // one distinct value
+                                    pl->q_val[j] = ko_key2d(bmn);
                                     pl->q_done[j] = 1;
                                 } else {
                                     nkA[j] = na;
@@ -879,6 +1216,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                         }
                     }
                 }
+                KO_TICK(4);
                 cons_sync();
                 // ---- selects over captured candidates (all consumers)
                 for (int j = 0; j < nq; ++j) {
@@ -899,11 +1237,12 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                         cons_sync();
                     }
                 }
+                KO_TICK(5);
                 if (ctid == 0) {
                     int more = 0;
                     for (int j = 0; j < nq; ++j) more |= !pl->q_done[j];
                     pl->passes += 1;
-                    if (more && pl->passes > 12) {  // cannot happen: every pass shrinks the key range
+                    if (more && pl->passes > 14) {  // cannot happen: every pass shrinks the key range 256-fold
                         for (int j = 0; j < nq; ++j)
                             if (!pl->q_done[j]) {
                                 pl->q_val[j] = nan;
@@ -936,6 +1275,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
             if (pl->passes > 1) atomicAdd(&a.counters[3], 1);
         }
         __syncthreads();
+        KO_TICK(6);
     }
 }
 
@@ -1254,3 +1594,14 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     KO_CUDA(cudaGetLastError());
     return KO_OK;
 }
+
+#ifdef KO_PHASE_TIMING
+extern "C" int ko_debug_phases(unsigned long long* out16, int reset) {
+    KO_CUDA(cudaMemcpyFromSymbol(out16, g_phase, sizeof(unsigned long long) * 16));
+    if (reset) {
+        unsigned long long z[16] = {0};
+        KO_CUDA(cudaMemcpyToSymbol(g_phase, z, sizeof(z)));
+    }
+    return KO_OK;
+}
+#endif
