@@ -46,7 +46,7 @@ typedef struct ko_counters {
     int64_t kernel_launches; /* kernels of this library launched through the ctx since ko_init       */
     int64_t h2d_bytes;       /* bytes copied host->device by host-pointer entry points               */
     int64_t d2h_bytes;       /* bytes copied device->host by host-pointer entry points               */
-    int64_t series_fallback; /* long series that needed an extra refinement pass in the last call    */
+    int64_t series_fallback; /* long series the pipelined fast path deferred to the slow path (last call) */
 } ko_counters;
 
 /* ---- life cycle (no reference counterpart: the reference is pure Python) ------------------------- */
@@ -117,7 +117,7 @@ int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_o
  * thread that cannot afford the device-wide synchronisation hidden in cudaMalloc / cudaFree, or any section of
  * a program in which the CUDA allocator is off limits.  This entry point has NO COUNTERPART IN THE REFERENCE
  * (and needs no ko_ctx): the work list and counters that ko_series_rollup_dev keeps in memory it cudaMallocs on
- * demand live here in a fixed array inside the library image, 4*(8+KO_STATIC_MAX_SERIES) bytes = 256 KiB,
+ * demand live here in a fixed array inside the library image, 4*(8+2*KO_STATIC_MAX_SERIES) bytes = 512 KiB,
  * which every GPU that loads the library holds until the process exits.  It calls no cudaMalloc, cudaFree or
  * other allocating routine.  Limits and rules:
  *   - n_series > KO_STATIC_MAX_SERIES is refused with KO_EINVAL (split the batch);

@@ -49,8 +49,10 @@ struct SeriesArgs {
     double* out_last;
     int64_t* out_count;
     double* out_quant;
-    int* counters;  // [0] n_long  [1] work cursor  [2] error flag  [3] series needing extra passes
+    int* counters;  // [0] n_long  [1] work cursor  [2] error flag  [3] series needing extra passes  [4] deferred  [5] cursor
     int* long_list;
+    int* defer_list;  // series the pipelined fast path hands to series_long (counters[4] entries, cursor counters[5])
+    int fb;           // series_long works on the deferred list
     int nq;
     double q[NI_MAX];   // ascending
     int qcol[NI_MAX];   // output column of q[j]
@@ -120,6 +122,25 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
+// Wait for roles that may idle for microseconds: suspend inside try_wait (time hint) and back off with
+// nanosleep, so that waiting warps do not steal issue slots from the warps that do the work.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    for (;;) {
+        uint32_t done;
+        asm volatile(
+            "{\n"
+            ".reg .pred P1;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n"
+            "selp.u32 %0, 1, 0, P1;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(addr), "r"(parity), "r"(2000u)
+            : "memory");
+        if (done) break;
+        __nanosleep(400);
+    }
+}
 // TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
 __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile(
@@ -143,6 +164,27 @@ __device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_arrive_addr(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Shared-memory atomics by explicit state space: through a generic pointer the compiler emits the slow generic
+// ATOM path instead of ATOMS/REDS.
+__device__ __forceinline__ void red_shared_add(const void* p, unsigned v) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned atom_shared_add(const void* p, unsigned v) {
+    unsigned r;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(smem_u32(p)), "r"(v) : "memory");
+    return r;
+}
+__device__ __forceinline__ void red_shared_min64(const void* p, unsigned long long v) {
+    asm volatile("red.shared.min.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_shared_max64(const void* p, unsigned long long v) {
+    asm volatile("red.shared.max.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
+}
+__device__ __forceinline__ double lds_f64(uint32_t addr) {
+    double x;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(x) : "r"(addr));
+    return x;
 }
 __device__ __forceinline__ void lds_v2f64(uint32_t addr, double& x, double& y) {
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(x), "=d"(y) : "r"(addr));
@@ -252,7 +294,7 @@ __device__ unsigned long long warp_radix_select(const unsigned long long* keys, 
         __syncwarp();
         for (int i = lane; i < n; i += 32) {
             unsigned long long k = keys[i];
-            if (k != KO_KEY_NAN && (k & mask) == prefix) atomicAdd(&hist[(unsigned)(k >> shift) & 255u], 1u);
+            if (k != KO_KEY_NAN && (k & mask) == prefix) red_shared_add(&hist[(unsigned)(k >> shift) & 255u], 1u);
         }
         __syncwarp();
         int digit;
@@ -329,15 +371,24 @@ __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
 
 // ------------------------------------------------------------------------------ CTA path (> 1024)
 struct LongSmem {
-    double* ring;                 // STAGES * TILE
-    unsigned char* pool;          // SLOTS * NCONS * 8 bytes; aliased by the pre-sample keys
-    double* ovq;                  // OVQ
-    unsigned* hist;               // NI_MAX * HBINS
-    unsigned* selhist;            // HBINS
-    double* red;                  // NCWARPS * 4
-    Plan* plan;
-    uint64_t* full;               // STAGES
-    uint64_t* empty;              // STAGES
+    // Fixed offsets from the dynamic shared-memory base (no pointer table: it would live in local memory and turn
+    // every access into a generic load).
+    unsigned char* base;
+    __device__ __forceinline__ double* ring_() const { return reinterpret_cast<double*>(base); }
+    __device__ __forceinline__ unsigned char* pool_() const { return base + (size_t)STAGES * TILE * 8; }
+    __device__ __forceinline__ double* ovq_() const {
+        return reinterpret_cast<double*>(base + (size_t)STAGES * TILE * 8 + (size_t)SLOTS * NCONS * 8);
+    }
+    __device__ __forceinline__ unsigned* hist_() const {
+        return reinterpret_cast<unsigned*>(base + (size_t)STAGES * TILE * 8 + (size_t)SLOTS * NCONS * 8 + (size_t)OVQ * 8);
+    }
+    __device__ __forceinline__ unsigned* selhist_() const { return hist_() + NI_MAX * HBINS; }
+    __device__ __forceinline__ double* red_() const { return reinterpret_cast<double*>(selhist_() + HBINS); }
+    __device__ __forceinline__ Plan* plan_() const { return reinterpret_cast<Plan*>(red_() + NCWARPS * 4); }
+    __device__ __forceinline__ uint64_t* full_() const {
+        return reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(plan_()) + 1024);
+    }
+    __device__ __forceinline__ uint64_t* empty_() const { return full_() + STAGES; }
 };
 
 constexpr int CMP_MAX = NI_MAX * HBINS * 4 / 8;  // compacted keys of the radix select alias the histograms
@@ -359,7 +410,7 @@ struct Acc {
 // Rare: the thread's private slots are full — claim an entry of the interval's shared overflow queue and return
 // its shared-memory address (a scratch word when the queue is full too; the attempt is still counted).
 __device__ __noinline__ uint32_t overflow_addr(Plan* pl, double* ovq, int i) {
-    const unsigned pos = atomicAdd(&pl->ovcnt[i], 1u);
+    const unsigned pos = atom_shared_add(&pl->ovcnt[i], 1u);
     if (pos < (unsigned)pl->ovcap[i]) return smem_u32(ovq + pl->ov0[i] + pos);
     return smem_u32(&pl->trash);
 }
@@ -370,7 +421,7 @@ __device__ __forceinline__ void sts_f64(uint32_t addr, double x) {
 __device__ __forceinline__ void capture(uint32_t pool32, uint32_t& p, uint32_t pend, const LongSmem& sm, int i,
                                         double x) {
     uint32_t addr = pool32 + p;
-    if (p == pend) addr = overflow_addr(sm.plan, sm.ovq, i);
+    if (p == pend) addr = overflow_addr(sm.plan_(), sm.ovq_(), i);
     else p += NCONS * 8;
     sts_f64(addr, x);
 }
@@ -387,9 +438,9 @@ __device__ __forceinline__ unsigned long long* hist_bmax(unsigned char* pool) {
 __device__ __noinline__ void hist_add(const Plan* pl, unsigned* hist, unsigned char* pool, int i, double x) {
     const unsigned long long k = ko_okey(x + 0.0);
     const unsigned b = (unsigned)((k - pl->kA[i]) >> pl->hshift[i]);
-    atomicAdd(&hist[i * HBINS + b], 1u);
-    atomicMin(&hist_bmin(pool)[i * HBINS + b], k);
-    atomicMax(&hist_bmax(pool)[i * HBINS + b], k);
+    red_shared_add(&hist[i * HBINS + b], 1u);
+    red_shared_min64(&hist_bmin(pool)[i * HBINS + b], k);
+    red_shared_max64(&hist_bmax(pool)[i * HBINS + b], k);
 }
 
 // sum += x, nvalid += 1 unless x is NaN (predicated, no selects)
@@ -461,7 +512,7 @@ template <int NB, bool TAIL>
 __device__ __forceinline__ void fast_elem1(double x, Acc& acc, const FastRegs<NB, TAIL>& fr, const LongSmem& sm) {
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
     const double v[4] = {x, nan, nan, nan};  // NaN is neither valid nor inside any bracket
-    fast_elems4<NB, TAIL>(v, acc, fr, sm, smem_u32(sm.pool));
+    fast_elems4<NB, TAIL>(v, acc, fr, sm, smem_u32(sm.pool_()));
 }
 
 template <int NB, bool TAIL>
@@ -470,16 +521,16 @@ __device__ __forceinline__ void consume_fast(const double* __restrict__ v, int L
     FastRegs<NB, TAIL> fr;
 #pragma unroll
     for (int i = 0; i < NB; ++i) {
-        fr.tA[i] = sm.plan->tA[i];
-        fr.tB[i] = sm.plan->tB[i];
-        fr.cap[i] = sm.plan->mode[i] == M_CAPTURE;
+        fr.tA[i] = sm.plan_()->tA[i];
+        fr.tB[i] = sm.plan_()->tB[i];
+        fr.cap[i] = sm.plan_()->mode[i] == M_CAPTURE;
     }
-    fr.tT = TAIL ? sm.plan->tA[NB] : 0.0;
+    fr.tT = TAIL ? sm.plan_()->tA[NB] : 0.0;
     if (ctid == 0 && head) fast_elem1<NB, TAIL>(v[0], acc, fr, sm);
     if (ctid == 1 && head + body < L) fast_elem1<NB, TAIL>(v[L - 1], acc, fr, sm);
-    const uint32_t full0 = smem_u32(sm.full), empty0 = smem_u32(sm.empty);
-    const uint32_t ring0 = smem_u32(sm.ring) + (uint32_t)ctid * 16u;
-    const uint32_t pool32 = smem_u32(sm.pool);
+    const uint32_t full0 = smem_u32(sm.full_()), empty0 = smem_u32(sm.empty_());
+    const uint32_t ring0 = smem_u32(sm.ring_()) + (uint32_t)ctid * 16u;
+    const uint32_t pool32 = smem_u32(sm.pool_());
     uint32_t s = g % STAGES, par = (g / STAGES) & 1u;
     int rem2 = body >> 1;  // double2 elements left
     for (int t = 0; t < ntiles; ++t) {
@@ -523,7 +574,7 @@ __device__ __forceinline__ void generic_elem(double x, Acc& acc, const double (&
         const bool in = !lt && (x < tB[i]);
         if (in) {
             if (mode[i] == M_CAPTURE) capture(pool32, acc.p[i], acc.pend[i], sm, i, x);
-            else if (mode[i] == M_HIST) hist_add(sm.plan, sm.hist, sm.pool, i, x);
+            else if (mode[i] == M_HIST) hist_add(sm.plan_(), sm.hist_(), sm.pool_(), i, x);
             else acc.cin[i]++;
         }
     }
@@ -538,15 +589,15 @@ __device__ __noinline__ void consume_generic(const double* __restrict__ v, int L
     int mode[NI_MAX];
 #pragma unroll
     for (int i = 0; i < NI_MAX; ++i) {
-        tA[i] = (i < NI) ? sm.plan->tA[i] : 0.0;
-        tB[i] = (i < NI) ? sm.plan->tB[i] : 0.0;
-        mode[i] = (i < NI) ? sm.plan->mode[i] : M_COUNT;
+        tA[i] = (i < NI) ? sm.plan_()->tA[i] : 0.0;
+        tB[i] = (i < NI) ? sm.plan_()->tB[i] : 0.0;
+        mode[i] = (i < NI) ? sm.plan_()->mode[i] : M_COUNT;
     }
-    const uint32_t pool32 = smem_u32(sm.pool);
+    const uint32_t pool32 = smem_u32(sm.pool_());
     if (ctid == 0 && head) generic_elem<NI, STATS>(v[0], acc, tA, tB, mode, sm, pool32);
     if (ctid == 1 && head + body < L) generic_elem<NI, STATS>(v[L - 1], acc, tA, tB, mode, sm, pool32);
-    const uint32_t full0 = smem_u32(sm.full), empty0 = smem_u32(sm.empty);
-    const uint32_t ring0 = smem_u32(sm.ring) + (uint32_t)ctid * 16u;
+    const uint32_t full0 = smem_u32(sm.full_()), empty0 = smem_u32(sm.empty_());
+    const uint32_t ring0 = smem_u32(sm.ring_()) + (uint32_t)ctid * 16u;
     uint32_t s = g % STAGES, par = (g / STAGES) & 1u;
     int rem2 = body >> 1;
     for (int t = 0; t < ntiles; ++t) {
@@ -650,13 +701,13 @@ __device__ __forceinline__ void sort_sample_regs(unsigned long long (&r)[KPT], u
 template <typename F>
 __device__ __forceinline__ void for_each_candidate(const LongSmem& sm, const double* ovq, int ovn, uint32_t p0,
                                                    uint32_t pcur, int ctid, F f) {
-    for (uint32_t p = p0; p != pcur; p += NCONS * 8) f(ko_okey(*reinterpret_cast<const double*>(sm.pool + p) + 0.0));
+    for (uint32_t p = p0; p != pcur; p += NCONS * 8) f(ko_okey(*reinterpret_cast<const double*>(sm.pool_() + p) + 0.0));
     for (int i = ctid; i < ovn; i += NCONS) f(ko_okey(ovq[i] + 0.0));
 }
 
 __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsigned rho, uint32_t p0,
                                                uint32_t pcur, int ctid, int lane) {
-    Plan* pl = sm.plan;
+    Plan* pl = sm.plan_();
     const unsigned long long kA = pl->kA[iv], kB = pl->kB[iv];
     const unsigned long long diff = kA ^ (kB - 1);
     if (diff == 0) return kA;
@@ -665,28 +716,28 @@ __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsig
     unsigned long long mask = (shift + 8 >= 64) ? 0ull : (~0ull << (shift + 8));
     unsigned long long prefix = kA & mask;
     const int ovn = (int)min(pl->ovcnt[iv], (unsigned)pl->ovcap[iv]);
-    const double* ovq = sm.ovq + pl->ov0[iv];
-    unsigned long long* cmp = reinterpret_cast<unsigned long long*>(sm.hist);  // free once the pass was decided
+    const double* ovq = sm.ovq_() + pl->ov0[iv];
+    unsigned long long* cmp = reinterpret_cast<unsigned long long*>(sm.hist_());  // free once the pass was decided
     bool use_list = false;
     int nlist = 0;
     for (;;) {
-        sm.selhist[ctid] = 0;
+        sm.selhist_()[ctid] = 0;
         cons_sync();
         if (use_list) {
             for (int i = ctid; i < nlist; i += NCONS) {
                 const unsigned long long k = cmp[i];
-                if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+                if ((k & mask) == prefix) red_shared_add(&sm.selhist_()[(unsigned)(k >> shift) & 255u], 1u);
             }
         } else {
             for_each_candidate(sm, ovq, ovn, p0, pcur, ctid, [&](unsigned long long k) {
-                if ((k & mask) == prefix) atomicAdd(&sm.selhist[(unsigned)(k >> shift) & 255u], 1u);
+                if ((k & mask) == prefix) red_shared_add(&sm.selhist_()[(unsigned)(k >> shift) & 255u], 1u);
             });
         }
         cons_sync();
         if (ctid < 32) {
             int digit;
             unsigned before, cnt;
-            warp_find_digit(sm.selhist, rho, lane, digit, before, cnt);
+            warp_find_digit(sm.selhist_(), rho, lane, digit, before, cnt);
             if (lane == 0) {
                 pl->sel_digit = digit;
                 pl->sel_cum = before;
@@ -714,7 +765,7 @@ __device__ unsigned long long cta_radix_select(const LongSmem& sm, int iv, unsig
         }
         if (!use_list && cnt <= (unsigned)CMP_MAX) {
             for_each_candidate(sm, ovq, ovn, p0, pcur, ctid, [&](unsigned long long k) {
-                if ((k & mask) == prefix) cmp[atomicAdd(&pl->cmp_cnt, 1u)] = k;
+                if ((k & mask) == prefix) cmp[atom_shared_add(&pl->cmp_cnt, 1u)] = k;
             });
             cons_sync();
             use_list = true;
@@ -904,7 +955,7 @@ __device__ void build_refine_plan(Plan* pl, int nq, const unsigned long long* nk
 }
 
 #ifdef KO_PHASE_TIMING
-__device__ unsigned long long g_phase[16];
+__device__ unsigned long long g_phase[32];
 #define KO_TICK(slot)                                                   \
     do {                                                                \
         if (blockIdx.x == 0 && threadIdx.x == 0) {                      \
@@ -920,8 +971,8 @@ __device__ unsigned long long g_phase[16];
 template <int KPT>
 __device__ __forceinline__ void presample(const double* __restrict__ v, int L, const LongSmem& sm, int ctid) {
     constexpr int S = KPT * NCONS;
-    Plan* pl = sm.plan;
-    unsigned long long* ukeys = reinterpret_cast<unsigned long long*>(sm.pool);        // full keys, sample order
+    Plan* pl = sm.plan_();
+    unsigned long long* ukeys = reinterpret_cast<unsigned long long*>(sm.pool_());        // full keys, sample order
     unsigned long long* spk = ukeys + SAMPLE_BIG;                                      // sorted packed keys
     unsigned long long r[KPT];
     int nv = 0;
@@ -938,38 +989,29 @@ __device__ __forceinline__ void presample(const double* __restrict__ v, int L, c
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) nv += __shfl_xor_sync(0xffffffffu, nv, o);
-    if ((ctid & 31) == 0 && nv) atomicAdd(&pl->sample_valid, nv);
+    if ((ctid & 31) == 0 && nv) red_shared_add(&pl->sample_valid, (unsigned)nv);
     sort_sample_regs<KPT>(r, spk, ctid);  // ends with a consumer barrier: ukeys, spk, sample_valid visible
 }
 
 __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     LongSmem sm;
-    {
-        unsigned char* p = smem_raw;
-        sm.ring = reinterpret_cast<double*>(p);            p += (size_t)STAGES * TILE * 8;
-        sm.pool = p;                                       p += (size_t)SLOTS * NCONS * 8;
-        sm.ovq = reinterpret_cast<double*>(p);             p += (size_t)OVQ * 8;
-        sm.hist = reinterpret_cast<unsigned*>(p);          p += (size_t)NI_MAX * HBINS * 4;
-        sm.selhist = reinterpret_cast<unsigned*>(p);       p += (size_t)HBINS * 4;
-        sm.red = reinterpret_cast<double*>(p);             p += (size_t)NCWARPS * 4 * 8;
-        sm.plan = reinterpret_cast<Plan*>(p);              p += 1024;
-        sm.full = reinterpret_cast<uint64_t*>(p);          p += (size_t)STAGES * 8;
-        sm.empty = reinterpret_cast<uint64_t*>(p);
-    }
-    Plan* pl = sm.plan;
+    sm.base = smem_raw;
+    Plan* pl = sm.plan_();
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const bool producer = (warp == NCWARPS);
     const int ctid = tid;  // consumer thread index (valid when !producer)
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) {
-            mbar_init(&sm.full[s], 1);
-            mbar_init(&sm.empty[s], NCWARPS);
+            mbar_init(&sm.full_()[s], 1);
+            mbar_init(&sm.empty_()[s], NCWARPS);
         }
         mbar_fence_init();
     }
     __syncthreads();
-    const int n_long = a.counters[0];
+    const int n_long = a.counters[a.fb ? 4 : 0];
+    const int* work_list = a.fb ? a.defer_list : a.long_list;
+    int* cursor = &a.counters[a.fb ? 5 : 1];
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
     uint32_t g = 0;  // running ring tile index, identical in all threads
 #ifdef KO_PHASE_TIMING
@@ -977,12 +1019,12 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
 #endif
 
     for (;;) {
-        if (tid == 0) pl->work = atomicAdd(&a.counters[1], 1);
+        if (tid == 0) pl->work = atomicAdd(cursor, 1);
         __syncthreads();
         const int w = pl->work;
         if (w >= n_long) break;
         KO_TICK(0);
-        const int sid = a.long_list[w];
+        const int sid = work_list[w];
         const int64_t off0 = a.offsets[sid];
         const int L = (int)(a.offsets[sid + 1] - off0);
         const double* v = a.values + off0;
@@ -1019,7 +1061,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                 else presample<SAMPLE_SMALL / NCONS>(v, L, sm, ctid);
                 KO_TICK(1);
                 if (ctid == 0) {
-                    const unsigned long long* ukeys = reinterpret_cast<const unsigned long long*>(sm.pool);
+                    const unsigned long long* ukeys = reinterpret_cast<const unsigned long long*>(sm.pool_());
                     build_first_plan(pl, ukeys + SAMPLE_BIG, ukeys, pl->sample_valid, L, a);
                 }
                 KO_TICK(2);
@@ -1036,10 +1078,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                     for (int t = 0; t < ntiles; ++t) {
                         const uint32_t gg = g + (uint32_t)t;
                         const int s = (int)(gg % STAGES);
-                        mbar_wait(&sm.empty[s], ((gg / STAGES) & 1u) ^ 1u);
+                        mbar_wait(&sm.empty_()[s], ((gg / STAGES) & 1u) ^ 1u);
                         const uint32_t bytes = (uint32_t)min(TILE, body - t * TILE) * 8u;
-                        mbar_expect_tx(&sm.full[s], bytes);
-                        tma_bulk_g2s(sm.ring + (size_t)s * TILE, vbody + (size_t)t * TILE, bytes, &sm.full[s]);
+                        mbar_expect_tx(&sm.full_()[s], bytes);
+                        tma_bulk_g2s(sm.ring_() + (size_t)s * TILE, vbody + (size_t)t * TILE, bytes, &sm.full_()[s]);
                     }
                 }
             } else {
@@ -1064,9 +1106,9 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                 }
                 if (!pl->fast) {
                     for (int i = ctid; i < NI_MAX * HBINS; i += NCONS) {
-                        sm.hist[i] = 0;
-                        hist_bmin(sm.pool)[i] = ~0ull;
-                        hist_bmax(sm.pool)[i] = 0ull;
+                        sm.hist_()[i] = 0;
+                        hist_bmin(sm.pool_())[i] = ~0ull;
+                        hist_bmax(sm.pool_())[i] = 0ull;
                     }
                 }
                 cons_sync();
@@ -1094,10 +1136,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                     const double ws = warp_sum(acc.sum), wmn = warp_min(acc.mn), wmx = warp_max(acc.mx);
                     const unsigned wn = warp_sum_u(acc.nvalid);
                     if (lane == 0) {
-                        sm.red[warp * 4 + 0] = ws;
-                        sm.red[warp * 4 + 1] = wmn;
-                        sm.red[warp * 4 + 2] = wmx;
-                        sm.red[warp * 4 + 3] = (double)wn;
+                        sm.red_()[warp * 4 + 0] = ws;
+                        sm.red_()[warp * 4 + 1] = wmn;
+                        sm.red_()[warp * 4 + 2] = wmx;
+                        sm.red_()[warp * 4 + 3] = (double)wn;
                     }
                 }
 #pragma unroll
@@ -1106,8 +1148,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                         const unsigned ca = warp_sum_u(acc.cA[i]);
                         const unsigned ci = warp_sum_u(acc.cin[i] + (acc.p[i] - p0[i]) / (NCONS * 8));
                         if (lane == 0) {
-                            atomicAdd(&pl->cA[i], ca);
-                            atomicAdd(&pl->nin[i], ci);
+                            red_shared_add(&pl->cA[i], ca);
+                            red_shared_add(&pl->nin[i], ci);
                         }
                     }
                 }
@@ -1120,10 +1162,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                     if (first) {
                         double s = 0.0, mn = INFINITY, mx = -INFINITY, n = 0.0;
                         for (int wq = 0; wq < NCWARPS; ++wq) {
-                            s += sm.red[wq * 4 + 0];
-                            mn = fmin(mn, sm.red[wq * 4 + 1]);
-                            mx = fmax(mx, sm.red[wq * 4 + 2]);
-                            n += sm.red[wq * 4 + 3];
+                            s += sm.red_()[wq * 4 + 0];
+                            mn = fmin(mn, sm.red_()[wq * 4 + 1]);
+                            mx = fmax(mx, sm.red_()[wq * 4 + 2]);
+                            n += sm.red_()[wq * 4 + 3];
                         }
                         pl->sum = s;
                         pl->mn = mn;
@@ -1149,7 +1191,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                         unsigned nb = pl->nin[i] + pl->ovcnt[i];
                         if (pl->mode[i] == M_HIST) {
                             nb = 0;
-                            for (int b = 0; b < HBINS; ++b) nb += sm.hist[i * HBINS + b];
+                            for (int b = 0; b < HBINS; ++b) nb += sm.hist_()[i * HBINS + b];
                         }
                         const unsigned long long kA = pl->kA[i], kB = pl->kB[i];
                         if (r <= cA) {  // below the bracket
@@ -1192,7 +1234,7 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                                 unsigned cum = 0;
                                 int b = 0;
                                 for (; b < HBINS - 1; ++b) {
-                                    const unsigned h = sm.hist[i * HBINS + b];
+                                    const unsigned h = sm.hist_()[i * HBINS + b];
                                     if (cum + h >= rho) break;
                                     cum += h;
                                 }
@@ -1200,17 +1242,17 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
                                 const unsigned long long na = kA + ((unsigned long long)b << sh);
                                 unsigned long long nb2 = na + (1ull << sh);
                                 if (nb2 > kB || nb2 < na) nb2 = kB;
-                                const unsigned long long bmn = hist_bmin(sm.pool)[i * HBINS + b];
+                                const unsigned long long bmn = hist_bmin(sm.pool_())[i * HBINS + b];
                                 if (nb2 - na == 1) {
                                     pl->q_val[j] = ko_key2d(na);
                                     pl->q_done[j] = 1;
-                                } else if (bmn == hist_bmax(sm.pool)[i * HBINS + b]) {  // one distinct value
+                                } else if (bmn == hist_bmax(sm.pool_())[i * HBINS + b]) {  // one distinct value
                                     pl->q_val[j] = ko_key2d(bmn);
                                     pl->q_done[j] = 1;
                                 } else {
                                     nkA[j] = na;
                                     nkB[j] = nb2;
-                                    npop[j] = sm.hist[i * HBINS + b];
+                                    npop[j] = sm.hist_()[i * HBINS + b];
                                 }
                             }
                         }
@@ -1279,6 +1321,1168 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
     }
 }
 
+
+// =========================================================================================================
+// series_pipe — the fast path for long series: one CTA per SM, warp-specialised, three series in flight.
+//
+//   PLANNER  (1 warp)   series k+2: strided pre-sample of 1024 values, sorted in registers (32 keys per lane,
+//                       compare-exchange in registers and by shuffles, no shared memory, no CTA barrier),
+//                       brackets per quantile, capture plan.
+//   PRODUCER (1 warp)   series k+1: TMA bulk copies (cp.async.bulk + mbarrier) into a 5-stage ring.
+//   STREAM   (12 warps) series k+1: fused sum / count / min / max + per-bracket counting and capture of the
+//                       in-bracket samples into thread-private shared-memory slots (pool k+1 mod 2).
+//   FINISH   (4 warps)  series k: combines the partials, radix-selects the exact order statistics among the
+//                       captured samples (pool k mod 2), writes the outputs.
+// Roles hand over through mbarriers only.  Anything unusual — brackets that do not fit shared memory, heavy tie
+// groups, a bracket that missed its rank, an overflowing queue — is not handled here: the series is appended to
+// the deferred list and recomputed exactly by series_long afterwards.
+#ifdef KO_PHASE_TIMING
+#define KO_PT0() const unsigned long long _pt0 = clock64()
+#define KO_PT1(slot, cond)                                                   \
+    do {                                                                     \
+        if (blockIdx.x == 0 && (cond)) g_phase[slot] += clock64() - _pt0;    \
+    } while (0)
+#else
+#define KO_PT0() do { } while (0)
+#define KO_PT1(slot, cond) do { } while (0)
+#endif
+constexpr int P_SW = 12;                       // stream warps
+constexpr int P_FW = 6;                        // finish warps
+constexpr int P_NS = P_SW * 32;                // 384 stream threads
+constexpr int P_NF = P_FW * 32;                // 128 finish threads
+constexpr int P_PW = 2;                        // planner warps (series alternate between them)
+constexpr int P_PLANS = 4;                     // plan slots
+constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW) * 32;   // planners, producer, stream, finish
+constexpr int P_TILE = 4 * P_NS;               // 1536 doubles (12 KB) per ring stage
+constexpr int P_STAGES = 4;
+constexpr int P_SLOTS = 24;                    // thread-private candidate slots per stream thread
+constexpr int P_OVQ = 768;                     // overflow queue entries per pool
+constexpr int P_NI = 3;                        // at most 2 brackets + 1 upper tail
+constexpr int P_COLS = P_NS / P_NF;             // stream-thread columns per finish thread
+static_assert(P_COLS * P_NF == P_NS && (P_COLS == 2 || P_COLS == 3), "finish threads own 2 or 3 whole columns");
+constexpr int P_LIST = 256;                    // candidates of one sub-bracket kept for the final rank counting
+constexpr int P_SAMPLE = 1024;
+
+struct PipePlan {
+    int sid;                 // series index, -1 = no more work
+    int defer;               // not eligible for the fast path
+    int L, head, body, ntiles;
+    const double* v;
+    double last;
+    double smin, smax;       // smallest / largest valid pre-sample value (+inf / -inf without a sample)
+    int ni, nb, tail;        // intervals: nb brackets first, then the optional upper tail
+    int mode[P_NI];
+    int slot0[P_NI], nslots[P_NI];
+    int ov0[P_NI], ovcap[P_NI];
+    unsigned long long kA[P_NI], kB[P_NI];
+    double tA[P_NI], tB[P_NI];
+    int q_iv[NI_MAX];
+};
+
+struct PipeResult {          // what the stream warps hand to the finish warps, one per pool
+    double sum[P_SW], mn[P_SW], mx[P_SW];
+    unsigned nvalid[P_SW];
+    unsigned cA[P_SW][P_NI];
+    unsigned cin[P_SW][P_NI];
+    unsigned ovcnt[P_NI];
+    unsigned short pcount[P_NI][P_NS];   // captured entries per stream thread
+    double trash;                        // sink of captures that find slots and queue full
+};
+
+struct PipeSel {             // scratch of the finish warps
+    union {                                    // the counters are dead once their sums are taken
+        unsigned char cnt8[64][P_NF];          // per-thread byte counters of the 64 sub-brackets (8 KB)
+        unsigned long long list[NI_MAX][P_LIST];   // candidates of the chosen sub-bracket per quantile (8 KB)
+    };
+    unsigned part[P_NF / 64][64];              // sums of the counters
+    unsigned char dummy[3][P_NF];              // counters of absent samples
+    unsigned list_cnt[NI_MAX];
+    unsigned long long lo[NI_MAX], hi[NI_MAX]; // chosen sub-bracket per quantile
+    unsigned rho[NI_MAX];
+    int act[NI_MAX];                           // 1 = needs a select
+    int fail;
+    double val[NI_MAX];
+    unsigned long long ikA[P_NI], ikB[P_NI];   // effective bracket per interval
+    int ish[P_NI], iuse[P_NI];
+    unsigned cAt[P_NI], nin[P_NI];
+    unsigned nvalid;
+    double sum, mn, mx;
+    double wmx[P_FW];
+};
+
+__host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) / 16 * 16; }
+constexpr size_t PO_RING = 0;
+constexpr size_t PO_POOL = PO_RING + (size_t)P_STAGES * P_TILE * 8;
+constexpr size_t P_POOL_BYTES = (size_t)P_SLOTS * P_NS * 8;
+constexpr size_t PO_OVQ = PO_POOL + 2 * P_POOL_BYTES;
+constexpr size_t PO_PLAN = PO_OVQ + 2 * (size_t)P_OVQ * 8;
+constexpr size_t PO_RES = PO_PLAN + align16(P_PLANS * sizeof(PipePlan));
+constexpr size_t PO_SEL = PO_RES + align16(2 * sizeof(PipeResult));
+constexpr size_t PO_BARS = PO_SEL + align16(sizeof(PipeSel));
+constexpr size_t PIPE_SMEM_BYTES = PO_BARS + 32 * 8;
+static_assert(PIPE_SMEM_BYTES <= 232448, "series_pipe must fit the 227 KB of one SM");
+
+// All regions are fixed offsets from the dynamic shared-memory base: nothing here is indexed at run time
+// through a table (a table would be placed in slow local memory).
+struct PipeSmem {
+    unsigned char* base;
+    __device__ __forceinline__ double* ring() const { return reinterpret_cast<double*>(base + PO_RING); }
+    __device__ __forceinline__ unsigned char* pool(uint32_t i) const { return base + PO_POOL + i * P_POOL_BYTES; }
+    __device__ __forceinline__ double* ovq(uint32_t i) const {
+        return reinterpret_cast<double*>(base + PO_OVQ + i * (size_t)P_OVQ * 8);
+    }
+    __device__ __forceinline__ PipePlan* plan(uint32_t i) const {
+        return reinterpret_cast<PipePlan*>(base + PO_PLAN) + i;
+    }
+    __device__ __forceinline__ PipeResult* res(uint32_t i) const {
+        return reinterpret_cast<PipeResult*>(base + PO_RES) + i;
+    }
+    __device__ __forceinline__ PipeSel* sel() const { return reinterpret_cast<PipeSel*>(base + PO_SEL); }
+    __device__ __forceinline__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + PO_BARS); }
+};
+
+enum { B_RING_FULL = 0, B_RING_EMPTY = 5, B_PLAN_FULL = 10, B_PLAN_FREE = 14, B_POOL_FULL = 18, B_POOL_FREE = 20 };
+
+__device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(P_NF) : "memory"); }
+
+// ------------------------------------------------------------------------------------------ planner
+// 1024 packed 32-bit keys, 32 per lane (element index = lane*32 + e), sorted ascending across the warp.
+// A packed key is (22-bit position of the sample's key inside the sample's own key range) << 10 | sample index:
+// fine enough to place the brackets, half the registers and instructions of a 64-bit sort; the exact bracket
+// ends are re-read from the series through the index.
+template <int J>
+__device__ __forceinline__ void planner_stage_regs(unsigned (&r)[32], int k, int lane) {
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+        if ((e & J) == 0) {
+            const bool up = (((lane << 5) | e) & k) == 0;
+            const unsigned lo = min(r[e], r[e | J]), hi = max(r[e], r[e | J]);
+            r[e] = up ? lo : hi;
+            r[e | J] = up ? hi : lo;
+        }
+    }
+}
+__device__ __forceinline__ void planner_sort(unsigned (&r)[32], int lane) {
+#pragma unroll 1
+    for (int k = 2; k <= P_SAMPLE; k <<= 1) {
+#pragma unroll 1
+        for (int j = k >> 1; j >= 32; j >>= 1) {  // partner in another lane
+            const int m = j >> 5;
+            const bool lower = (lane & m) == 0;
+            const bool up = ((lane << 5) & k) == 0;   // k >= 64 here: the bit lies in the lane part
+            const bool take_min = (lower == up);
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+                const unsigned o = __shfl_xor_sync(0xffffffffu, r[e], m);
+                r[e] = take_min ? min(r[e], o) : max(r[e], o);
+            }
+        }
+        if (k > 16) planner_stage_regs<16>(r, k, lane);
+        if (k > 8) planner_stage_regs<8>(r, k, lane);
+        if (k > 4) planner_stage_regs<4>(r, k, lane);
+        if (k > 2) planner_stage_regs<2>(r, k, lane);
+        planner_stage_regs<1>(r, k, lane);
+    }
+}
+
+// sorted key at position p (uniform across the warp)
+__device__ __forceinline__ unsigned planner_at(const unsigned (&r)[32], int p, int lane) {
+    unsigned mine = 0;
+#pragma unroll
+    for (int e = 0; e < 32; ++e)
+        if (e == (p & 31)) mine = r[e];
+    return __shfl_sync(0xffffffffu, mine, p >> 5);
+}
+
+// number of sample keys whose 22-bit position is below t / not above t
+__device__ __forceinline__ void planner_count(const unsigned (&r)[32], unsigned t, int& below, int& notabove) {
+    int b = 0, na = 0;
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+        const unsigned k = r[e] >> 10;
+        b += (k < t) ? 1 : 0;
+        na += (k <= t) ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+        na += __shfl_xor_sync(0xffffffffu, na, o);
+    }
+    below = b;
+    notabove = na;
+}
+
+__device__ __forceinline__ long long sample_pos(int i, int L) {
+    return ((2LL * i + 1) * (long long)L) / (2LL * P_SAMPLE);
+}
+
+// tiny fixed-size arrays kept in registers: every access is unrolled to static indices
+template <typename T, int N>
+struct RegArr {
+    T v[N];
+    __device__ __forceinline__ T get(int i) const {
+        T r = v[0];
+#pragma unroll
+        for (int t = 1; t < N; ++t)
+            if (i == t) r = v[t];
+        return r;
+    }
+    __device__ __forceinline__ void set(int i, T x) {
+#pragma unroll
+        for (int t = 0; t < N; ++t)
+            if (i == t) v[t] = x;
+    }
+};
+
+// Whole warp, every value uniform: build the plan of series `sid` into *pp.
+__device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a, int sid, int lane) {
+    const int64_t off0 = a.offsets[sid];
+    const int L = (int)(a.offsets[sid + 1] - off0);
+    const double* v = a.values + off0;
+    const int head = (int)((reinterpret_cast<uintptr_t>(v) >> 3) & 1);
+    const int body = (L - head) & ~1;
+    const int nq = a.nq;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    // last valid sample: look at the final 32 samples together, walk further back only if all are stale
+    double lastv = nan;
+    {
+        const int i = L - 1 - lane;
+        const double x = (i >= 0) ? v[i] : nan;
+        const unsigned okm = __ballot_sync(0xffffffffu, x == x);
+        if (okm) {
+            lastv = __shfl_sync(0xffffffffu, x, __ffs(okm) - 1);
+        } else {
+            if (lane == 0)
+                for (int t = L - 33; t >= 0; --t) {
+                    const double y = v[t];
+                    if (y == y) {
+                        lastv = y;
+                        break;
+                    }
+                }
+            lastv = __shfl_sync(0xffffffffu, lastv, 0);
+        }
+    }
+    int defer = 0;
+    int ni = 0, nb = 0, tail = 0;
+    double smin = INFINITY, smax = -INFINITY;   // lane 0 only
+    RegArr<int, P_NI> lo, hi;
+    RegArr<int, NI_MAX> q_iv;
+#pragma unroll
+    for (int t = 0; t < P_NI; ++t) lo.v[t] = hi.v[t] = 0;
+#pragma unroll
+    for (int t = 0; t < NI_MAX; ++t) q_iv.v[t] = 0;
+    if (nq > 0) {
+        unsigned r[32];
+        int nv = 0;
+        {
+            unsigned long long kk[32];
+            unsigned long long kmin = KO_KEY_NAN, kmax = 0ull;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+                const double x = v[sample_pos((lane << 5) | e, L)];
+                const bool ok = (x == x);
+                kk[e] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
+                nv += ok;
+                if (ok) {
+                    kmin = kk[e] < kmin ? kk[e] : kmin;
+                    kmax = kk[e] > kmax ? kk[e] : kmax;
+                }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                nv += __shfl_xor_sync(0xffffffffu, nv, o);
+                const unsigned long long a1 = __shfl_xor_sync(0xffffffffu, kmin, o);
+                const unsigned long long a2 = __shfl_xor_sync(0xffffffffu, kmax, o);
+                kmin = a1 < kmin ? a1 : kmin;
+                kmax = a2 > kmax ? a2 : kmax;
+            }
+            const unsigned long long span = kmax > kmin ? kmax - kmin : 0ull;
+            const int bits = span ? 64 - __clzll((long long)span) : 0;
+            const int sh = bits > 22 ? bits - 22 : 0;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+                const unsigned i = (unsigned)((lane << 5) | e);
+                r[e] = (kk[e] == KO_KEY_NAN) ? 0xFFFFFFFFu : ((unsigned)((kk[e] - kmin) >> sh) << 10) | i;
+            }
+        }
+        const int valid_s = nv;
+        planner_sort(r, lane);
+        if (valid_s < 64) defer = 1;  // too few valid samples to bracket: leave it to the exact slow path
+        if (!defer) {   // the sample's extremes seed the running min / max of the stream warps
+            const unsigned p0 = planner_at(r, 0, lane), p1 = planner_at(r, valid_s - 1, lane);
+            if (lane == 0) {
+                smin = v[sample_pos((int)(p0 & 1023u), L)];
+                smax = v[sample_pos((int)(p1 & 1023u), L)];
+            }
+        }
+        int cur_lo = 0, cur_hi = 0;   // the interval being grown
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            if (j < nq && !defer) {
+                const double q = a.q[j];
+                const double pos = q * (double)valid_s;
+                const double sig = sqrt(fmax(q * (1.0 - q), 0.0) * (double)valid_s);
+                const int m = (int)ceil(CSIG * sig) + 2;
+                int aj = (int)floor(pos) - m - 1, bj = (int)ceil(pos) + m;
+                if (aj < 0) aj = -1;
+                if (bj > valid_s) bj = valid_s;
+                const int gap = valid_s / 32;
+                if (ni > 0 && aj <= cur_hi + gap) {
+                    if (bj > cur_hi) cur_hi = bj;
+                    if (aj < cur_lo) cur_lo = aj;
+                } else if (ni < P_NI) {
+                    cur_lo = aj;
+                    cur_hi = bj;
+                    ni++;
+                } else {
+                    defer = 1;
+                }
+                lo.set(ni - 1, cur_lo);
+                hi.set(ni - 1, cur_hi);
+                q_iv.v[j] = ni - 1;
+                if (j >= 2 && q_iv.v[j - 2] == ni - 1) defer = 1;   // three quantiles in one interval: slow path
+            }
+        }
+        int total = 0, ncap = 0;
+        int mode[P_NI], need[P_NI];
+        unsigned long long kA[P_NI], kB[P_NI];
+        bool last_is_tail = false;
+#pragma unroll
+        for (int i = 0; i < P_NI; ++i) {
+            mode[i] = M_COUNT;
+            need[i] = 0;
+            kA[i] = kB[i] = 0;
+            if (i < ni && !defer) {
+                const int lo_i = lo.v[i], hi_i = hi.v[i];
+                const int a0 = lo_i < 0 ? 0 : lo_i, b0 = hi_i >= valid_s ? valid_s - 1 : hi_i;
+                const unsigned pa = planner_at(r, a0, lane), pb = planner_at(r, b0, lane);
+                // exact keys of the two bracket ends (the packed key only carries the top 54 bits)
+                double xa = 0.0, xb = 0.0;
+                if (lane == 0) {
+                    xa = v[sample_pos((int)(pa & 1023u), L)];
+                    xb = v[sample_pos((int)(pb & 1023u), L)];
+                }
+                xa = __shfl_sync(0xffffffffu, xa, 0);
+                xb = __shfl_sync(0xffffffffu, xb, 0);
+                unsigned long long ka = ko_okey(xa + 0.0), kb = ko_okey(xb + 0.0);
+                if (ka > kb) {
+                    const unsigned long long t = ka;
+                    ka = kb;
+                    kb = t;
+                }
+                kA[i] = ka;
+                mode[i] = M_CAPTURE;
+                bool is_tail = false;
+                if (ka == kb) {
+                    mode[i] = M_COUNT;
+                    kB[i] = ka + 1;
+                } else if (hi_i >= valid_s) {
+                    is_tail = true;
+                    kB[i] = KO_KEY_PINF + 1;
+                } else {
+                    kB[i] = (kb >= KO_KEY_PINF) ? KO_KEY_PINF : kb + 1;
+                }
+                if (kB[i] <= kA[i] || (mode[i] == M_COUNT && kA[i] >= KO_KEY_PINF)) defer = 1;  // +inf corner
+                if (mode[i] == M_CAPTURE) {
+                    int below_a, na_a, below_b, na_b;
+                    planner_count(r, pa >> 10, below_a, na_a);
+                    planner_count(r, pb >> 10, below_b, na_b);
+                    const int ea = below_a, eb = is_tail ? valid_s - 1 : na_b - 1;  // whole tie groups at the ends
+                    const double mass = (double)(eb - ea + 3) / (double)valid_s;
+                    const double per_thread = fmin(mass, 1.0) * (double)L / (double)P_NS;
+                    need[i] = (int)ceil(per_thread) + 1;
+                    total += need[i];
+                    ncap++;
+                }
+                if (is_tail) tail = 1; else nb++;
+                last_is_tail = is_tail;
+            }
+        }
+        if (nb > 2 || total > P_SLOTS) defer = 1;
+        if (tail && !last_is_tail) defer = 1;
+        if (!defer && lane == 0) {
+            int slot = 0, k = 0;
+            const int spare = P_SLOTS - total;
+#pragma unroll
+            for (int i = 0; i < P_NI; ++i) {
+                if (i < ni) {
+                    pp->mode[i] = mode[i];
+                    pp->kA[i] = kA[i];
+                    pp->kB[i] = kB[i];
+                    pp->tA[i] = ko_key2d(kA[i]);
+                    pp->tB[i] = ko_key2d(kB[i] > KO_KEY_PINF ? KO_KEY_PINF : kB[i]);
+                    pp->slot0[i] = slot;
+                    pp->nslots[i] = 0;
+                    pp->ov0[i] = 0;
+                    pp->ovcap[i] = 0;
+                    if (mode[i] == M_CAPTURE) {
+                        pp->nslots[i] = need[i] + spare / ncap;
+                        slot += pp->nslots[i];
+                        pp->ov0[i] = k * (P_OVQ / ncap);
+                        pp->ovcap[i] = P_OVQ / ncap;
+                        k++;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        pp->sid = sid;
+        pp->defer = defer;
+        pp->L = L;
+        pp->head = head;
+        pp->body = body;
+        pp->ntiles = (body + P_TILE - 1) / P_TILE;
+        pp->v = v;
+        pp->last = lastv;
+        pp->smin = smin;
+        pp->smax = smax;
+        pp->ni = ni;
+        pp->nb = nb;
+        pp->tail = tail;
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) pp->q_iv[j] = q_iv.v[j];
+    }
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------ stream
+struct PAcc {
+    double sum, mn, mx;
+    unsigned nvalid;
+    unsigned cA[2];
+    unsigned cin[2];
+    uint32_t p[P_NI], pend[P_NI];
+};
+
+struct PStreamCtx {
+    uint32_t pool32;       // shared address of this series' pool
+    uint32_t ovq32;        // shared address of its overflow queue
+    uint32_t ovcnt32;      // shared address of PipeResult::ovcnt
+    uint32_t trash32;
+    int ov0[P_NI], ovcap[P_NI];
+};
+
+// Store x into the thread's next private slot of interval i; when the slots are full (a few per cent of the
+// captures) claim an entry of the overflow queue with a shared-memory atomic.
+__device__ __forceinline__ void pipe_capture(const PStreamCtx& c, uint32_t& p, uint32_t pend, int i, double x,
+                                             int lane) {
+    (void)lane;
+    uint32_t addr = c.pool32 + p;
+    if (p != pend) {
+        p += P_NS * 8;
+    } else {
+        unsigned pos;
+        asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(c.ovcnt32 + 4u * i) : "memory");
+        addr = (pos < (unsigned)c.ovcap[i]) ? c.ovq32 + (uint32_t)(c.ov0[i] + pos) * 8u : c.trash32;
+    }
+    sts_f64(addr, x);
+}
+
+// Helpers of the stream loop.  The compare chains are PTX so that the compiler does not rewrite them into a
+// min/max tree, and the rare updates are out-of-line calls so that they stay behind a real branch instead of
+// being predicated into every iteration.
+__device__ __forceinline__ bool any_lt4(double a, double b, double c, double d, double m) {
+    unsigned r;
+    asm("{\n.reg .pred p;\nsetp.lt.f64 p, %1, %5;\nsetp.lt.or.f64 p, %2, %5, p;\nsetp.lt.or.f64 p, %3, %5, p;\n"
+        "setp.lt.or.f64 p, %4, %5, p;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(r) : "d"(a), "d"(b), "d"(c), "d"(d), "d"(m));
+    return r != 0;
+}
+__device__ __forceinline__ bool any_gt4(double a, double b, double c, double d, double m) {
+    unsigned r;
+    asm("{\n.reg .pred p;\nsetp.gt.f64 p, %1, %5;\nsetp.gt.or.f64 p, %2, %5, p;\nsetp.gt.or.f64 p, %3, %5, p;\n"
+        "setp.gt.or.f64 p, %4, %5, p;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(r) : "d"(a), "d"(b), "d"(c), "d"(d), "d"(m));
+    return r != 0;
+}
+__device__ __noinline__ double rare_min4(double m, double a, double b, double c, double d) {
+    return fmin(fmin(m, fmin(a, b)), fmin(c, d));
+}
+__device__ __noinline__ double rare_max4(double m, double a, double b, double c, double d) {
+    return fmax(fmax(m, fmax(a, b)), fmax(c, d));
+}
+struct Stats4 {
+    double sum, mn, mx;
+    unsigned nv;
+};
+__device__ __noinline__ Stats4 rare_nan4(Stats4 st, double a, double b, double c, double d) {
+    const double v[4] = {a, b, c, d};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        if (v[e] == v[e]) {
+            st.sum += v[e];
+            st.nv++;
+        }
+        st.mn = fmin(st.mn, v[e]);
+        st.mx = fmax(st.mx, v[e]);
+    }
+    return st;
+}
+
+template <int NB, bool TAIL>
+struct PFast {
+    double tA[NB > 0 ? NB : 1], tB[NB > 0 ? NB : 1];
+    bool cap[NB > 0 ? NB : 1];
+    double tT;
+};
+
+template <int NB, bool TAIL>
+__device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, const PFast<NB, TAIL>& fr,
+                                            const PStreamCtx& c, int lane) {
+    // sum / count / min / max, four samples at once.  A NaN among them (staleness marker, rare) takes the
+    // per-sample path.  With a pre-sample the running min / max start at the sample extremes, so an update is
+    // rare and is tested with four compares; with an upper tail every sample >= tT is captured and the finish
+    // warps take the maximum from there.
+    {
+        const double t = (x[0] + x[1]) + (x[2] + x[3]);
+        if (t == t) {
+            acc.sum += t;
+            acc.nvalid += 4;
+            if (NB > 0 || TAIL) {   // seeded
+                if (any_lt4(x[0], x[1], x[2], x[3], acc.mn)) acc.mn = rare_min4(acc.mn, x[0], x[1], x[2], x[3]);
+                if (!TAIL) {
+                    if (any_gt4(x[0], x[1], x[2], x[3], acc.mx)) acc.mx = rare_max4(acc.mx, x[0], x[1], x[2], x[3]);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    if (x[e] < acc.mn) acc.mn = x[e];
+                    if (x[e] > acc.mx) acc.mx = x[e];
+                }
+            }
+        } else {
+            Stats4 st = {acc.sum, acc.mn, acc.mx, acc.nvalid};
+            st = rare_nan4(st, x[0], x[1], x[2], x[3]);
+            acc.sum = st.sum;
+            acc.mn = st.mn;
+            if (!TAIL) acc.mx = st.mx;
+            acc.nvalid = st.nv;
+        }
+    }
+    // Brackets and tail.  Common case: every capturing interval still has four free private slots, so the four
+    // samples are handled by straight-line predicated code (no branches, no overflow test per sample).
+    bool room = true;
+#pragma unroll
+    for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i) room = room && (acc.pend[i] - acc.p[i] >= 4u * P_NS * 8u);
+    if (room) {
+#pragma unroll
+        for (int i = 0; i < NB; ++i) {
+            if (fr.cap[i]) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool lt = x[e] < fr.tA[i];
+                    acc.cA[i] += lt ? 1u : 0u;
+                    if (!lt && (x[e] < fr.tB[i])) {
+                        sts_f64(c.pool32 + acc.p[i], x[e]);
+                        acc.p[i] += P_NS * 8;
+                    }
+                }
+            } else {   // count-only bracket (a tie group)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool lt = x[e] < fr.tA[i];
+                    acc.cA[i] += lt ? 1u : 0u;
+                    acc.cin[i] += (!lt && (x[e] < fr.tB[i])) ? 1u : 0u;
+                }
+            }
+        }
+        if (TAIL) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (x[e] >= fr.tT) {
+                    sts_f64(c.pool32 + acc.p[NB], x[e]);
+                    acc.p[NB] += P_NS * 8;
+                }
+            }
+        }
+        return;
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+        bool in[4];
+        bool any = false;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const bool lt = x[e] < fr.tA[i];
+            acc.cA[i] += lt ? 1u : 0u;
+            in[e] = !lt && (x[e] < fr.tB[i]);
+            any = any || in[e];
+        }
+        if (any) {
+            if (fr.cap[i]) {
+#pragma unroll
+                for (int e = 0; e < 4; ++e)
+                    if (in[e]) pipe_capture(c, acc.p[i], acc.pend[i], i, x[e], lane);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 4; ++e) acc.cin[i] += in[e] ? 1u : 0u;
+            }
+        }
+    }
+    if (TAIL) {
+        constexpr int i = NB;
+        bool in[4];
+        bool any = false;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            in[e] = x[e] >= fr.tT;
+            any = any || in[e];
+        }
+        if (any) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (in[e]) pipe_capture(c, acc.p[i], acc.pend[i], i, x[e], lane);
+        }
+    }
+}
+
+template <int NB, bool TAIL>
+__device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const PStreamCtx& c, const PipeSmem& sm,
+                                            uint32_t& g, int stid, int lane) {
+    PFast<NB, TAIL> fr;
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+        fr.tA[i] = pp->tA[i];
+        fr.tB[i] = pp->tB[i];
+        fr.cap[i] = pp->mode[i] == M_CAPTURE;
+    }
+    fr.tT = TAIL ? pp->tA[NB] : 0.0;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    const int L = pp->L, head = pp->head, body = pp->body, ntiles = pp->ntiles;
+    const double* v = pp->v;
+    if (stid == 0 && head) {
+        const double x[4] = {v[0], nan, nan, nan};
+        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
+    }
+    if (stid == 32 && head + body < L) {   // first lane of another warp, so the two stragglers do not serialise
+        const double x[4] = {v[L - 1], nan, nan, nan};
+        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
+    }
+    const uint32_t full0 = smem_u32(sm.bars() + B_RING_FULL), empty0 = smem_u32(sm.bars() + B_RING_EMPTY);
+    const uint32_t ring0 = smem_u32(sm.ring()) + (uint32_t)stid * 16u;
+    uint32_t s = g % P_STAGES, par = (g / P_STAGES) & 1u;
+    int rem2 = body >> 1;
+    for (int t = 0; t < ntiles; ++t) {
+        mbar_wait_addr(full0 + s * 8u, par);
+        const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
+        double x[4];
+        if (rem2 >= P_TILE / 2) {
+            lds_v2f64(base, x[0], x[1]);
+            lds_v2f64(base + P_NS * 16, x[2], x[3]);
+        } else {
+            x[0] = x[1] = x[2] = x[3] = nan;
+            if (stid < rem2) lds_v2f64(base, x[0], x[1]);
+            if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
+        }
+        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        rem2 -= P_TILE / 2;
+        if (++s == P_STAGES) {
+            s = 0;
+            par ^= 1u;
+        }
+    }
+    g += (uint32_t)ntiles;
+}
+
+// ------------------------------------------------------------------------------------------ finish
+// Explicit shared-memory loads: a generic load would queue behind the planner's outstanding global gathers in
+// the load/store unit and take microseconds.
+template <typename F3, typename F1>
+__device__ __forceinline__ void pipe_for_rows(const unsigned char* pool, const double* ovq, const PipePlan* pp,
+                                              const PipeResult* res, int i, int ftid, F3 frow, F1 fone) {
+    // Each finish thread owns the private slots of P_COLS stream threads.  Shared-memory latency is > 100 cycles
+    // while the stream warps and the TMA engine keep the banks busy, so the next row is fetched before the
+    // current one is processed and frow() handles the samples of a row together.
+    const uint32_t base = smem_u32(pool) + (uint32_t)(((size_t)pp->slot0[i] * P_NS + ftid) * 8);
+    const int n0 = res->pcount[i][ftid], n1 = res->pcount[i][ftid + P_NF];
+    const int n2 = P_COLS == 3 ? res->pcount[i][ftid + 2 * P_NF] : 0;
+    const int nmax = max(n0, max(n1, n2));
+#ifdef KO_PHASE_TIMING
+    const unsigned long long _l0 = clock64();
+#endif
+    double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+    if (0 < n0) y0 = lds_f64(base);
+    if (0 < n1) y1 = lds_f64(base + P_NF * 8);
+    if (P_COLS == 3 && 0 < n2) y2 = lds_f64(base + 2 * P_NF * 8);
+    for (int s = 0; s < nmax; ++s) {
+        const double x0 = y0, x1 = y1, x2 = y2;
+        const uint32_t nrow = base + (uint32_t)(s + 1) * (P_NS * 8);
+        if (s + 1 < n0) y0 = lds_f64(nrow);
+        if (s + 1 < n1) y1 = lds_f64(nrow + P_NF * 8);
+        if (P_COLS == 3 && s + 1 < n2) y2 = lds_f64(nrow + 2 * P_NF * 8);
+        frow(x0, s < n0, x1, s < n1, x2, P_COLS == 3 && s < n2);
+    }
+#ifdef KO_PHASE_TIMING
+    if (blockIdx.x == 0 && ftid == 0) {
+        g_phase[20] += clock64() - _l0;
+        g_phase[21] += (unsigned long long)nmax;
+        g_phase[22] = g_phase[22] > (unsigned long long)nmax ? g_phase[22] : (unsigned long long)nmax;
+        g_phase[23] += 1;
+    }
+#endif
+    const int ovn = (int)min(res->ovcnt[i], (unsigned)pp->ovcap[i]);
+    const uint32_t ov32 = smem_u32(ovq) + (uint32_t)pp->ov0[i] * 8u;
+    for (int q = ftid; q < ovn; q += P_NF) fone(lds_f64(ov32 + (uint32_t)q * 8u));
+}
+
+template <typename F>
+__device__ __forceinline__ void pipe_for_each(const unsigned char* pool, const double* ovq, const PipePlan* pp,
+                                              const PipeResult* res, int i, int ftid, F f) {
+    pipe_for_rows(pool, ovq, pp, res, i, ftid,
+                  [&](double x0, bool v0, double x1, bool v1, double x2, bool v2) {
+                      if (v0) f(x0);
+                      if (v1) f(x1);
+                      if (v2) f(x2);
+                  },
+                  f);
+}
+
+__device__ __forceinline__ unsigned lds_u8(uint32_t addr) {
+    unsigned c;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
+    return c;
+}
+__device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+}
+
+#ifdef KO_PHASE_TIMING
+#define KO_FT(slot)                                                         \
+    do {                                                                    \
+        if (blockIdx.x == 0 && ftid == 0) {                                 \
+            const unsigned long long _t = clock64();                        \
+            g_phase[slot] += _t - _ft;                                      \
+            _ft = _t;                                                       \
+        }                                                                   \
+    } while (0)
+#else
+#define KO_FT(slot) do { } while (0)
+#endif
+// Returns false when the series has to be deferred to the exact slow path.
+//
+// Selection without shared-memory atomics on the hot path (a warp-wide shared atomic costs ~64 cycles): the
+// bracket of an interval is cut into 64 sub-brackets, linear in key space; every finish thread counts its share of
+// the candidates into PRIVATE byte counters (plain load / add / store), the counters are summed with dp4a, the
+// sub-bracket holding the wanted rank is found, its few dozen candidates are collected, and one warp finds the
+// exact order statistic among them by rank counting.
+__device__ __forceinline__ bool pipe_finish(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
+                            const unsigned char* pool, const double* ovq, int ftid, int fwarp, int lane) {
+    const int ni = pp->ni, nq = a.nq;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+#ifdef KO_PHASE_TIMING
+    unsigned long long _ft = clock64();
+#endif
+    if (ftid < P_NI) sel->nin[ftid] = 0;
+    if (ftid == 0) sel->fail = 0;
+    fin_sync();
+    // captured entries per interval
+    for (int i = 0; i < ni; ++i) {
+        unsigned c = (unsigned)res->pcount[i][ftid] + res->pcount[i][ftid + P_NF] +
+                     (P_COLS == 3 ? res->pcount[i][ftid + 2 * P_NF] : 0);
+        c = warp_sum_u(c);
+        if (lane == 0) red_shared_add(&sel->nin[i], c);
+    }
+    if (pp->tail) {   // the stream warps leave the maximum to us: it is among the upper-tail candidates
+        double m = -INFINITY;
+        pipe_for_each(pool, ovq, pp, res, ni - 1, ftid, [&](double xv) { m = fmax(m, xv); });
+        m = warp_max(m);
+        if (lane == 0) sel->wmx[fwarp] = m;
+    }
+    fin_sync();
+    if (ftid == 0) {
+        double s = 0.0, mn = INFINITY, mx = -INFINITY;
+        unsigned n = 0;
+        for (int w = 0; w < P_SW; ++w) {
+            s += res->sum[w];
+            mn = fmin(mn, res->mn[w]);
+            mx = fmax(mx, res->mx[w]);
+            n += res->nvalid[w];
+        }
+        if (pp->tail)
+            for (int w = 0; w < P_FW; ++w) mx = fmax(mx, sel->wmx[w]);
+        sel->sum = s;
+        sel->mn = mn;
+        sel->mx = mx;
+        sel->nvalid = n;
+        for (int i = 0; i < ni; ++i) {
+            unsigned ca = 0, ci = 0;
+            if (i < pp->nb)
+                for (int w = 0; w < P_SW; ++w) {
+                    ca += res->cA[w][i];
+                    ci += res->cin[w][i];
+                }
+            const unsigned nin = sel->nin[i] + res->ovcnt[i] + ci;
+            sel->nin[i] = nin;
+            sel->cAt[i] = (i < pp->nb) ? ca : n - nin;   // upper tail: everything outside is below
+            unsigned long long kB = pp->kB[i];
+            if (kB > KO_KEY_PINF) kB = ko_okey(mx + 0.0) + 1;   // upper tail: nothing lies above the series maximum
+            sel->ikA[i] = pp->kA[i];
+            sel->ikB[i] = kB;
+            const unsigned long long span = kB - pp->kA[i] - 1;   // kB > kA
+            const int bits = span ? 64 - __clzll((long long)span) : 0;
+            sel->ish[i] = bits > 6 ? bits - 6 : 0;               // (key - kA) >> ish is in [0, 64)
+            sel->iuse[i] = 0;
+        }
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            if (j >= nq) continue;
+            sel->act[j] = 0;
+            sel->val[j] = nan;
+            sel->list_cnt[j] = 0;
+            if (n == 0) continue;
+            const int i = pp->q_iv[j];
+            const unsigned r = nearest_rank_dev(n, a.q[j]);
+            const unsigned cA = sel->cAt[i], nb = sel->nin[i];
+            if (r <= cA || r > cA + nb) {
+                sel->fail = 1;  // the bracket missed the rank
+                continue;
+            }
+            if (pp->mode[i] == M_COUNT || sel->ikB[i] - sel->ikA[i] == 1) {
+                sel->val[j] = ko_key2d(sel->ikA[i]);
+                continue;
+            }
+            if (res->ovcnt[i] > (unsigned)pp->ovcap[i]) {
+                sel->fail = 1;  // more candidates than shared memory holds
+                continue;
+            }
+            sel->act[j] = 1;
+            sel->rho[j] = r - cA;
+            sel->iuse[i] = 1;
+        }
+    }
+    fin_sync();
+    KO_FT(13);
+    if (sel->fail) return false;
+    int qiv[NI_MAX];
+#pragma unroll
+    for (int j = 0; j < NI_MAX; ++j) qiv[j] = (j < nq) ? pp->q_iv[j] : -1;
+#pragma unroll 1
+    for (int i = 0; i < ni; ++i) {
+        if (!sel->iuse[i]) continue;   // uniform
+        const unsigned long long kA = sel->ikA[i];
+        const int ish = sel->ish[i];
+        // ---- scan 1: private byte counters per sub-bracket
+        {
+            uint32_t* w = reinterpret_cast<uint32_t*>(&sel->cnt8[0][0]);
+            for (int t = ftid; t < 64 * P_NF / 4; t += P_NF) w[t] = 0;
+        }
+        fin_sync();
+        {
+            // private byte counters: the three samples of a row update three counters; their loads are issued
+            // together unless two of them hit the same counter (then the updates are applied one after another)
+            const uint32_t col = smem_u32(&sel->cnt8[0][0]) + (uint32_t)ftid;
+            const uint32_t dummy = smem_u32(&sel->dummy[0][0]) + (uint32_t)ftid;
+            auto addr_of = [&](double xv, bool valid, int which) -> uint32_t {
+                const unsigned long long k = ko_okey(xv + 0.0);
+                return valid ? col + (uint32_t)((k - kA) >> ish) * (uint32_t)P_NF : dummy + (uint32_t)which * P_NF;
+            };
+            pipe_for_rows(pool, ovq, pp, res, i, ftid,
+                          [&](double x0, bool v0, double x1, bool v1, double x2, bool v2) {
+                              const uint32_t a0 = addr_of(x0, v0, 0), a1 = addr_of(x1, v1, 1), a2 = addr_of(x2, v2, 2);
+                              if (a0 == a1 || a0 == a2 || a1 == a2) {
+                                  sts_u8(a0, lds_u8(a0) + 1);
+                                  sts_u8(a1, lds_u8(a1) + 1);
+                                  sts_u8(a2, lds_u8(a2) + 1);
+                              } else {
+                                  const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1), c2 = lds_u8(a2);
+                                  sts_u8(a0, c0 + 1);
+                                  sts_u8(a1, c1 + 1);
+                                  sts_u8(a2, c2 + 1);
+                              }
+                          },
+                          [&](double xv) {
+                              const uint32_t a0 = addr_of(xv, true, 0);
+                              sts_u8(a0, lds_u8(a0) + 1);
+                          });
+        }
+        fin_sync();
+        KO_FT(14);
+        {   // totals per sub-bracket: thread (bin, half) sums 64 byte counters with dp4a
+            const int bin = ftid & 63, part = ftid >> 6;   // P_NF / 64 parts of 64 byte counters each
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(&sel->cnt8[bin][part * 64]);
+            unsigned t = 0;
+#pragma unroll
+            for (int x = 0; x < 16; ++x) t = __dp4a(w[x], 0x01010101u, t);
+            sel->part[part][bin] = t;
+        }
+        fin_sync();
+        if (fwarp < nq && sel->act[fwarp] == 1 && qiv[fwarp] == i && lane == 0) {
+            const int j = fwarp;   // lane 0 of warp j walks the 64 totals
+            const unsigned rho = sel->rho[j];
+            unsigned cum = 0;
+            int b = 0;
+            for (; b < 63; ++b) {
+                unsigned h = 0;
+#pragma unroll
+                for (int pt = 0; pt < P_NF / 64; ++pt) h += sel->part[pt][b];
+                if (cum + h >= rho) break;
+                cum += h;
+            }
+            unsigned h = 0;
+#pragma unroll
+            for (int pt = 0; pt < P_NF / 64; ++pt) h += sel->part[pt][b];
+            const unsigned long long lo = kA + ((unsigned long long)b << ish);
+            unsigned long long hi = lo + (1ull << ish);
+            if (hi > sel->ikB[i] || hi < lo) hi = sel->ikB[i];
+            sel->lo[j] = lo;
+            sel->hi[j] = hi;
+            sel->rho[j] = rho - cum;
+            if (h > (unsigned)P_LIST) sel->fail = 1;   // a heavy tie group: leave it to the slow path
+        }
+        fin_sync();
+        if (sel->fail) return false;
+        // ---- scan 2: collect the candidates of each quantile's sub-bracket (at most two quantiles per interval
+        // on the fast path; a third one sharing the interval was rejected by the planner)
+        {
+            int j0 = -1, j1 = -1;
+#pragma unroll
+            for (int j = 0; j < NI_MAX; ++j)
+                if ((j < nq) && sel->act[j] == 1 && qiv[j] == i) {
+                    if (j0 < 0) j0 = j; else j1 = j;
+                }
+            const unsigned b0 = (unsigned)((sel->lo[j0 < 0 ? 0 : j0] - kA) >> ish);
+            const unsigned b1 = j1 >= 0 ? (unsigned)((sel->lo[j1] - kA) >> ish) : 0xFFFFFFFFu;
+            const uint32_t cnt0 = smem_u32(&sel->list_cnt[j0 < 0 ? 0 : j0]), cnt1 = smem_u32(&sel->list_cnt[j1 < 0 ? 0 : j1]);
+            const uint32_t l0 = smem_u32(&sel->list[j0 < 0 ? 0 : j0][0]), l1 = smem_u32(&sel->list[j1 < 0 ? 0 : j1][0]);
+            pipe_for_each(pool, ovq, pp, res, i, ftid, [&](double xv) {
+                const unsigned long long k = ko_okey(xv + 0.0);
+                const unsigned b = (unsigned)((k - kA) >> ish);
+                if (b == b0) {
+                    unsigned pos;
+                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt0) : "memory");
+                    if (pos < (unsigned)P_LIST) asm volatile("st.shared.u64 [%0], %1;" ::"r"(l0 + pos * 8u), "l"(k) : "memory");
+                }
+                if (b == b1) {
+                    unsigned pos;
+                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt1) : "memory");
+                    if (pos < (unsigned)P_LIST) asm volatile("st.shared.u64 [%0], %1;" ::"r"(l1 + pos * 8u), "l"(k) : "memory");
+                }
+            });
+        }
+        fin_sync();
+        KO_FT(15);
+        // ---- exact order statistic inside each short list: one warp per quantile, rank counting
+        if (fwarp < nq && sel->act[fwarp] == 1 && qiv[fwarp] == i) {
+            const int j = fwarp;
+            const int n = (int)min(sel->list_cnt[j], (unsigned)P_LIST);
+            const unsigned rho = sel->rho[j];
+            const uint32_t l32 = smem_u32(&sel->list[j][0]);
+            for (int idx = lane; idx < n; idx += 32) {
+                unsigned long long e;
+                asm volatile("ld.shared.u64 %0, [%1];" : "=l"(e) : "r"(l32 + (uint32_t)idx * 8u));
+                unsigned lt = 0, le = 0;
+                for (int m = 0; m < n; ++m) {
+                    unsigned long long v;
+                    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(l32 + (uint32_t)m * 8u));
+                    lt += (v < e) ? 1u : 0u;
+                    le += (v <= e) ? 1u : 0u;
+                }
+                if (lt < rho && rho <= le) sel->val[j] = ko_key2d(e);   // all writers hold the same value
+            }
+        }
+        fin_sync();   // the lists alias the counters of the next interval
+    }
+    fin_sync();
+    KO_FT(7);
+    if (ftid == 0) {
+        const int sid = pp->sid;
+        const unsigned n = sel->nvalid;
+        if (a.out_sum) a.out_sum[sid] = sel->sum;
+        if (a.out_mean) a.out_mean[sid] = n > 0 ? sel->sum / (double)n : 0.0;
+        if (a.out_min) a.out_min[sid] = n > 0 ? sel->mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = n > 0 ? sel->mx + 0.0 : nan;
+        if (a.out_last) a.out_last[sid] = pp->last;
+        if (a.out_count) a.out_count[sid] = (int64_t)n;
+        if (a.out_quant) {
+#pragma unroll
+            for (int j = 0; j < NI_MAX; ++j)
+                if (j < nq) a.out_quant[(int64_t)sid * nq + a.qcol[j]] = sel->val[j];
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------ kernel
+__global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
+    extern __shared__ __align__(128) unsigned char psmem[];
+    PipeSmem sm;
+    sm.base = psmem;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < P_STAGES; ++s) {
+            mbar_init(sm.bars() + B_RING_FULL + s, 1);
+            mbar_init(sm.bars() + B_RING_EMPTY + s, P_SW);
+        }
+        for (int s = 0; s < P_PLANS; ++s) {
+            mbar_init(sm.bars() + B_PLAN_FULL + s, 1);
+            mbar_init(sm.bars() + B_PLAN_FREE + s, P_SW + 2);   // stream warps + finish + producer
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(sm.bars() + B_POOL_FULL + s, P_SW);
+            mbar_init(sm.bars() + B_POOL_FREE + s, 1);
+            for (int i = 0; i < P_NI; ++i) sm.res(s)->ovcnt[i] = 0;
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const int n_long = a.counters[0];
+
+    if (warp < P_PW) {
+        // ================================================================ PLANNERS
+        // Series are dealt to the CTAs round-robin (ordinal k of this CTA is long_list[blockIdx.x + k*gridDim.x]);
+        // planner warp p prepares the ordinals k = p, p + P_PW, ...
+        for (uint32_t k = (uint32_t)warp;; k += P_PW) {
+            const uint32_t slot = k & 3u;
+            mbar_wait_sleep(sm.bars() + B_PLAN_FREE + slot, ((k >> 2) & 1u) ^ 1u);
+            const long long w = (long long)blockIdx.x + (long long)k * gridDim.x;
+            PipePlan* pp = sm.plan(slot);
+            if (w >= n_long) {
+                if (lane == 0) pp->sid = -1;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
+                break;
+            }
+            { KO_PT0(); planner_build(pp, a, a.long_list[w], lane); KO_PT1(8, lane == 0); }
+            if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
+        }
+    } else if (warp == P_PW) {
+        // ================================================================ PRODUCER
+        if (lane == 0) {
+            uint32_t g = 0;
+            for (uint32_t k = 0;; ++k) {
+                const uint32_t slot = k & 3u;
+                mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> 2) & 1u);
+                const PipePlan* pp = sm.plan(slot);
+                if (pp->sid < 0) break;
+                if (!pp->defer) {
+                    const int ntiles = pp->ntiles, body = pp->body;
+                    const double* vbody = pp->v + pp->head;
+                    for (int t = 0; t < ntiles; ++t) {
+                        const uint32_t gg = g + (uint32_t)t;
+                        const uint32_t s = gg % P_STAGES;
+                        mbar_wait(sm.bars() + B_RING_EMPTY + s, ((gg / P_STAGES) & 1u) ^ 1u);
+                        const uint32_t bytes = (uint32_t)min(P_TILE, body - t * P_TILE) * 8u;
+                        mbar_expect_tx(sm.bars() + B_RING_FULL + s, bytes);
+                        tma_bulk_g2s(sm.ring() + (size_t)s * P_TILE, vbody + (size_t)t * P_TILE, bytes,
+                                     sm.bars() + B_RING_FULL + s);
+                    }
+                    g += (uint32_t)ntiles;
+                }
+                mbar_arrive(sm.bars() + B_PLAN_FREE + slot);
+            }
+        }
+    } else if (warp < P_PW + 1 + P_SW) {
+        // ================================================================ STREAM
+        const int stid = tid - (P_PW + 1) * 32;
+        const int swarp = warp - (P_PW + 1);
+        uint32_t g = 0, c = 0;
+        for (uint32_t k = 0;; ++k) {
+            const uint32_t slot = k & 3u;
+            { KO_PT0(); mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> 2) & 1u); KO_PT1(11, stid == 0); }
+            const PipePlan* pp = sm.plan(slot);
+            if (pp->sid < 0) break;
+            if (!pp->defer) {
+                const uint32_t pool = c & 1u;
+                mbar_wait_sleep(sm.bars() + B_POOL_FREE + pool, ((c >> 1) & 1u) ^ 1u);
+                PipeResult* res = sm.res(pool);
+                const int ni = pp->ni;
+                PAcc acc;
+                acc.sum = 0.0;
+                acc.mn = pp->smin;
+                acc.mx = pp->smax;
+                acc.nvalid = 0;
+                acc.cA[0] = acc.cA[1] = 0;
+                acc.cin[0] = acc.cin[1] = 0;
+                uint32_t p0[P_NI];
+                PStreamCtx cx;
+                cx.pool32 = smem_u32(sm.pool(pool));
+                cx.ovq32 = smem_u32(sm.ovq(pool));
+                cx.ovcnt32 = smem_u32(&res->ovcnt[0]);
+                cx.trash32 = smem_u32(&res->trash);
+#pragma unroll
+                for (int i = 0; i < P_NI; ++i) {
+                    const bool on = i < ni;
+                    p0[i] = on ? (uint32_t)(((size_t)pp->slot0[i] * P_NS + stid) * 8) : 0u;
+                    acc.p[i] = p0[i];
+                    acc.pend[i] = on ? p0[i] + (uint32_t)pp->nslots[i] * P_NS * 8 : 0u;
+                    cx.ov0[i] = on ? pp->ov0[i] : 0;
+                    cx.ovcap[i] = on ? pp->ovcap[i] : 0;
+                }
+                const int nb = pp->nb;
+                KO_PT0();
+                if (pp->tail) {
+                    if (nb == 0) pipe_stream<0, true>(pp, acc, cx, sm, g, stid, lane);
+                    else if (nb == 1) pipe_stream<1, true>(pp, acc, cx, sm, g, stid, lane);
+                    else pipe_stream<2, true>(pp, acc, cx, sm, g, stid, lane);
+                } else {
+                    if (nb == 0) pipe_stream<0, false>(pp, acc, cx, sm, g, stid, lane);
+                    else if (nb == 1) pipe_stream<1, false>(pp, acc, cx, sm, g, stid, lane);
+                    else pipe_stream<2, false>(pp, acc, cx, sm, g, stid, lane);
+                }
+                KO_PT1(9, stid == 0);
+                // hand the partials to the finish warps
+                const double ws = warp_sum(acc.sum), wmn = warp_min(acc.mn), wmx = warp_max(acc.mx);
+                const unsigned wn = warp_sum_u(acc.nvalid);
+                const unsigned ca0 = warp_sum_u(acc.cA[0]), ca1 = warp_sum_u(acc.cA[1]);
+                const unsigned ci0 = warp_sum_u(acc.cin[0]), ci1 = warp_sum_u(acc.cin[1]);
+                if (lane == 0) {
+                    res->sum[swarp] = ws;
+                    res->mn[swarp] = wmn;
+                    res->mx[swarp] = wmx;
+                    res->nvalid[swarp] = wn;
+                    res->cA[swarp][0] = ca0;
+                    res->cA[swarp][1] = ca1;
+                    res->cin[swarp][0] = ci0;
+                    res->cin[swarp][1] = ci1;
+                }
+#pragma unroll
+                for (int i = 0; i < P_NI; ++i)
+                    res->pcount[i][stid] = (unsigned short)((acc.p[i] - p0[i]) / (P_NS * 8));
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sm.bars() + B_POOL_FULL + pool);
+                ++c;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FREE + slot);
+        }
+    } else {
+        // ================================================================ FINISH
+        const int ftid = tid - (P_PW + 1) * 32 - P_NS, fwarp = warp - (P_PW + 1) - P_SW;
+        uint32_t c = 0;
+        for (uint32_t k = 0;; ++k) {
+            const uint32_t slot = k & 3u;
+            mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> 2) & 1u);
+            const PipePlan* pp = sm.plan(slot);
+            if (pp->sid < 0) break;
+            bool ok = false;
+            if (!pp->defer) {
+                const uint32_t pool = c & 1u;
+                { KO_PT0(); mbar_wait_sleep(sm.bars() + B_POOL_FULL + pool, (c >> 1) & 1u); KO_PT1(12, ftid == 0); }
+                { KO_PT0(); ok = pipe_finish(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), sm.ovq(pool), ftid, fwarp, lane); KO_PT1(10, ftid == 0); }
+                fin_sync();
+                if (ftid == 0) {
+                    for (int i = 0; i < P_NI; ++i) sm.res(pool)->ovcnt[i] = 0;
+                    mbar_arrive(sm.bars() + B_POOL_FREE + pool);
+                }
+                ++c;
+            }
+            if (ftid == 0) {
+                if (!ok) {  // exact slow path afterwards
+                    const int pos = atomicAdd(&a.counters[4], 1);
+                    a.defer_list[pos] = pp->sid;
+                }
+            }
+            fin_sync();
+            if (ftid == 0) mbar_arrive(sm.bars() + B_PLAN_FREE + slot);
+        }
+    }
+}
+
+
 bool g_attr_done = false;
 
 }  // namespace
@@ -1302,6 +2506,8 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     a.out_quant = d_quant;
     a.counters = d_scratch;
     a.long_list = d_scratch + 8;
+    a.defer_list = d_scratch + 8 + n_series;
+    a.fb = 0;
     a.nq = nq;
     // quantiles ascending (stable insertion sort), remembering the caller's column
     for (int j = 0; j < NI_MAX; ++j) {
@@ -1324,6 +2530,8 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
                                      (int)LONG_SMEM_BYTES));
         KO_CUDA(cudaFuncSetAttribute(series_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      8 * SMALL_MAX * 8 + 8 * HBINS * 4));
+        KO_CUDA(cudaFuncSetAttribute(series_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)PIPE_SMEM_BYTES));
         g_attr_done = true;
     }
     KO_CUDA(cudaMemsetAsync(d_scratch, 0, 8 * sizeof(int), stream));
@@ -1331,18 +2539,22 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     classify_series<<<(unsigned)((n_series + cb - 1) / cb), cb, 0, stream>>>(a);
     const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
     series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, stream>>>(a);
+    int pgrid = ctx->num_sms;
+    if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
     int grid = 2 * ctx->num_sms;
     if ((int64_t)grid > n_series) grid = (int)n_series;
     KO_CUDA(cudaEventRecord(ctx->ev_k0, stream));
-    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, stream>>>(a);
+    series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, stream>>>(a);   // fast path
+    a.fb = 1;
+    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, stream>>>(a);     // exact slow path over the deferred series
     KO_CUDA(cudaEventRecord(ctx->ev_k1, stream));
     ctx->k_timed = true;
     KO_CUDA(cudaGetLastError());
-    ctx->counters.kernel_launches += 3;
+    ctx->counters.kernel_launches += 4;
     return KO_OK;
 }
 
-size_t ko_series_scratch_bytes(int64_t n_series) { return (size_t)(8 + n_series) * sizeof(int); }
+size_t ko_series_scratch_bytes(int64_t n_series) { return (size_t)(8 + 2 * n_series) * sizeof(int); }
 
 extern "C" int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_offsets,
                                     int64_t n_series, const double* q, int nq, double* d_out_sum,
@@ -1466,13 +2678,13 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
     if (out_count) KO_CUDA(cudaMemcpyAsync(out_count, d_cnt, nb, cudaMemcpyDeviceToHost, ctx->stream));
     if (out_quantiles && nq)
         KO_CUDA(cudaMemcpyAsync(out_quantiles, d_q, nb * nq, cudaMemcpyDeviceToHost, ctx->stream));
-    int flags[4] = {0, 0, 0, 0};
+    int flags[6] = {0, 0, 0, 0, 0, 0};
     KO_CUDA(cudaMemcpyAsync(flags, (int*)ctx->scratch.p, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
     KO_CUDA(cudaStreamSynchronize(ctx->stream));
     int nout = (out_sum != 0) + (out_mean != 0) + (out_min != 0) + (out_max != 0) + (out_last != 0) +
                (out_count != 0) + ((out_quantiles && nq) ? nq : 0);
     ctx->counters.d2h_bytes += (int64_t)nb * nout + (int64_t)sizeof(flags);
-    ctx->counters.series_fallback = flags[3];
+    ctx->counters.series_fallback = flags[4];  // series the fast path handed to the exact slow path
     if (flags[2]) {
         ko_set_error("ko_series_rollup: device reported error flag %d", flags[2]);
         return KO_ECUDA;
@@ -1492,13 +2704,13 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
 // arrives; this entry point never does: no cudaMalloc, no cudaFree, no ctx (ko_init creates streams/events).
 //
 // Price: every GPU that loads libkorollup.so holds the array until the process exits
-// (4 * (8 + KO_STATIC_MAX_SERIES) bytes = 256 KiB), batches above KO_STATIC_MAX_SERIES series are refused, and
+// (4 * (8 + 2 * KO_STATIC_MAX_SERIES) bytes = 512 KiB), batches above KO_STATIC_MAX_SERIES series are refused, and
 // all calls on one device share the array: it keeps the previous call's contents (the counters are cleared on
 // the caller's stream at the start of every call), so two calls whose kernels may overlap on the GPU — different
 // streams, or threads launching concurrently — race on it.  Serialise them on one stream.
 namespace {
 
-static __device__ __align__(256) int g_static_scratch[8 + KO_STATIC_MAX_SERIES];
+static __device__ __align__(256) int g_static_scratch[8 + 2 * KO_STATIC_MAX_SERIES];
 
 constexpr int STATIC_MAX_DEVICES = 64;
 struct StaticDevice {
@@ -1525,6 +2737,8 @@ int static_setup(int device, StaticDevice** out) {
         KO_CUDA(cudaFuncSetAttribute(series_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LONG_SMEM_BYTES));
         KO_CUDA(cudaFuncSetAttribute(series_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      8 * SMALL_MAX * 8 + 8 * HBINS * 4));
+        KO_CUDA(cudaFuncSetAttribute(series_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)PIPE_SMEM_BYTES));
         sd->scratch = ptr;
         sd->num_sms = sms;
         sd->ready = true;
@@ -1566,6 +2780,8 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     a.out_quant = d_out_quantiles;
     a.counters = sd->scratch;
     a.long_list = sd->scratch + 8;
+    a.defer_list = sd->scratch + 8 + n_series;
+    a.fb = 0;
     a.nq = nq;
     for (int j = 0; j < NI_MAX; ++j) {
         a.q[j] = 0.0;
@@ -1588,8 +2804,12 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     classify_series<<<(unsigned)((n_series + 255) / 256), 256, 0, st>>>(a);
     const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
     series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, st>>>(a);
+    int pgrid = sd->num_sms;
+    if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
     int grid = 2 * sd->num_sms;
     if ((int64_t)grid > n_series) grid = (int)n_series;
+    series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+    a.fb = 1;
     series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
     KO_CUDA(cudaGetLastError());
     return KO_OK;
@@ -1597,9 +2817,9 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
 
 #ifdef KO_PHASE_TIMING
 extern "C" int ko_debug_phases(unsigned long long* out16, int reset) {
-    KO_CUDA(cudaMemcpyFromSymbol(out16, g_phase, sizeof(unsigned long long) * 16));
+    KO_CUDA(cudaMemcpyFromSymbol(out16, g_phase, sizeof(unsigned long long) * 32));
     if (reset) {
-        unsigned long long z[16] = {0};
+        unsigned long long z[32] = {0};
         KO_CUDA(cudaMemcpyToSymbol(g_phase, z, sizeof(z)));
     }
     return KO_OK;
