@@ -438,9 +438,27 @@ __device__ __forceinline__ unsigned long long* hist_bmax(unsigned char* pool) {
 __device__ __noinline__ void hist_add(const Plan* pl, unsigned* hist, unsigned char* pool, int i, double x) {
     const unsigned long long k = ko_okey(x + 0.0);
     const unsigned b = (unsigned)((k - pl->kA[i]) >> pl->hshift[i]);
-    red_shared_add(&hist[i * HBINS + b], 1u);
-    red_shared_min64(&hist_bmin(pool)[i * HBINS + b], k);
-    red_shared_max64(&hist_bmax(pool)[i * HBINS + b], k);
+    // Lanes that arrive together and hit the same bin are combined (series with few distinct values would
+    // otherwise serialise 32-way on one shared-memory word): one add of the group size, one min, one max.
+    const unsigned act = __activemask();
+    const unsigned peers = __match_any_sync(act, b);
+    const int lane = threadIdx.x & 31;
+    unsigned long long kmn = k, kmx = k;
+    for (unsigned m = peers & (peers - 1); m; m &= m - 1) {   // fold the peers' keys into the group extremes
+        const unsigned long long o = __shfl_sync(peers, k, __ffs(m) - 1);
+        kmn = o < kmn ? o : kmn;
+        kmx = o > kmx ? o : kmx;
+    }
+    {
+        const unsigned long long o = __shfl_sync(peers, k, __ffs(peers) - 1);
+        kmn = o < kmn ? o : kmn;
+        kmx = o > kmx ? o : kmx;
+    }
+    if (lane == __ffs(peers) - 1) {
+        red_shared_add(&hist[i * HBINS + b], (unsigned)__popc(peers));
+        red_shared_min64(&hist_bmin(pool)[i * HBINS + b], kmn);
+        red_shared_max64(&hist_bmax(pool)[i * HBINS + b], kmx);
+    }
 }
 
 // sum += x, nvalid += 1 unless x is NaN (predicated, no selects)
@@ -1362,6 +1380,9 @@ constexpr int P_COLS = P_NS / P_NF;             // stream-thread columns per fin
 static_assert(P_COLS * P_NF == P_NS && (P_COLS == 2 || P_COLS == 3), "finish threads own 2 or 3 whole columns");
 constexpr int P_LIST = 256;                    // candidates of one sub-bracket kept for the final rank counting
 constexpr int P_SAMPLE = 1024;
+constexpr int P_LEVELS = 15;                   // distinct values a "levels" plan can list
+constexpr int P_NTHR = 31;                     // thresholds searched per sample (2 per level + one +inf pad)
+constexpr int P_MAX_L_LEVELS = 16000000;       // keeps the 16-bit per-thread counters of a levels plan exact
 
 struct PipePlan {
     int sid;                 // series index, -1 = no more work
@@ -1377,6 +1398,12 @@ struct PipePlan {
     unsigned long long kA[P_NI], kB[P_NI];
     double tA[P_NI], tB[P_NI];
     int q_iv[NI_MAX];
+    // "levels" plan, for series with few distinct values around the wanted ranks (integer-valued gauges): no
+    // candidate is captured; thr holds, ascending, each listed level v and the next double above it, padded
+    // with +inf, and the stream warps count the samples per gap between consecutive thresholds.
+    int vals, nlev;
+    int vidx[P_LEVELS + 1];
+    double thr[P_NTHR + 1];
 };
 
 struct PipeResult {          // what the stream warps hand to the finish warps, one per pool
@@ -1564,6 +1591,8 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         }
     }
     int defer = 0;
+    int soft = 0;   // the capture plan does not fit; a levels plan may
+    int vals = 0, nlev = 0;
     int ni = 0, nb = 0, tail = 0;
     double smin = INFINITY, smax = -INFINITY;   // lane 0 only
     RegArr<int, P_NI> lo, hi;
@@ -1641,10 +1670,10 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                 lo.set(ni - 1, cur_lo);
                 hi.set(ni - 1, cur_hi);
                 q_iv.v[j] = ni - 1;
-                if (j >= 2 && q_iv.v[j - 2] == ni - 1) defer = 1;   // three quantiles in one interval: slow path
+                if (j >= 2 && q_iv.v[j - 2] == ni - 1) soft = 1;   // three quantiles in one interval
             }
         }
-        int total = 0, ncap = 0;
+        int total = 0, ncap = 0, ties = 0;
         int mode[P_NI], need[P_NI];
         unsigned long long kA[P_NI], kB[P_NI];
         bool last_is_tail = false;
@@ -1688,6 +1717,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                     int below_a, na_a, below_b, na_b;
                     planner_count(r, pa >> 10, below_a, na_a);
                     planner_count(r, pb >> 10, below_b, na_b);
+                    if (na_a - below_a >= 4 || na_b - below_b >= 4) ties = 1;   // repeated values at a bracket end
                     const int ea = below_a, eb = is_tail ? valid_s - 1 : na_b - 1;  // whole tie groups at the ends
                     const double mass = (double)(eb - ea + 3) / (double)valid_s;
                     const double per_thread = fmin(mass, 1.0) * (double)L / (double)P_NS;
@@ -1699,9 +1729,64 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                 last_is_tail = is_tail;
             }
         }
-        if (nb > 2 || total > P_SLOTS) defer = 1;
-        if (tail && !last_is_tail) defer = 1;
-        if (!defer && lane == 0) {
+        if (nb > 2 || total > P_SLOTS) soft = 1;
+        if (tail && !last_is_tail) soft = 1;
+        if ((soft || ties) && !defer) {
+            // Levels plan, preferred whenever it applies (tie-heavy brackets overflow the capture slots): list the distinct values the pre-sample shows inside the intervals.  Distinctness is
+            // judged on the packed keys; whatever this misses only makes the finish warps defer the series.
+            unsigned prev_last = __shfl_up_sync(0xffffffffu, r[31], 1);
+            if (lane == 0) prev_last = 0xFFFFFFFFu;
+#pragma unroll
+            for (int i = 0; i < P_NI; ++i) {
+                if (i < ni) {
+                    const int lo_i = lo.v[i], hi_i = hi.v[i];
+                    const int a0 = lo_i < 0 ? 0 : lo_i, b0 = hi_i >= valid_s ? valid_s - 1 : hi_i;
+                    unsigned selmask = 0;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        const int p = (lane << 5) | e;
+                        const unsigned prevk = e ? r[e > 0 ? e - 1 : 0] : prev_last;
+                        const bool sl = p >= a0 && p <= b0 && (p == a0 || (r[e] >> 10) != (prevk >> 10));
+                        selmask |= sl ? (1u << e) : 0u;
+                    }
+                    int cnt = __popc(selmask), inc = cnt;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                        if (lane >= o) inc += t;
+                    }
+                    int ofs = nlev + inc - cnt;
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        if ((selmask >> e) & 1u) {
+                            if (ofs <= P_LEVELS) pp->vidx[ofs] = (int)(r[e] & 1023u);
+                            ofs++;
+                        }
+                    }
+                    nlev += __shfl_sync(0xffffffffu, inc, 31);
+                }
+            }
+            __syncwarp();
+            if (nlev < 1 || nlev > P_LEVELS || L > P_MAX_L_LEVELS) {
+                defer = soft;   // too many levels: capture plan if that fits, else slow path
+            } else {
+                const double xv = (lane < nlev) ? v[sample_pos(pp->vidx[lane], L)] : 0.0;
+                const unsigned long long key = ko_okey(xv + 0.0);
+                const unsigned long long pk = __shfl_up_sync(0xffffffffu, key, 1);
+                const bool bad = lane < nlev && (!(xv == xv) || key >= KO_KEY_PINF || (lane > 0 && key <= pk));
+                if (__any_sync(0xffffffffu, bad)) {
+                    defer = soft;
+                } else {
+                    if (lane < nlev) {
+                        pp->thr[2 * lane] = ko_key2d(key);
+                        pp->thr[2 * lane + 1] = ko_key2d(key + 1);
+                    }
+                    if (lane >= 2 * nlev && lane <= P_NTHR) pp->thr[lane] = INFINITY;
+                    vals = 1;
+                }
+            }
+        }
+        if (!defer && !vals && lane == 0) {
             int slot = 0, k = 0;
             const int spare = P_SLOTS - total;
 #pragma unroll
@@ -1741,6 +1826,8 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         pp->ni = ni;
         pp->nb = nb;
         pp->tail = tail;
+        pp->vals = vals;
+        pp->nlev = nlev;
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) pp->q_iv[j] = q_iv.v[j];
     }
@@ -1977,6 +2064,95 @@ __device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const
             if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
         }
         pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        rem2 -= P_TILE / 2;
+        if (++s == P_STAGES) {
+            s = 0;
+            par ^= 1u;
+        }
+    }
+    g += (uint32_t)ntiles;
+}
+
+// Levels plan: per sample a branch-free binary search over the 31 ascending thresholds gives the number of
+// thresholds <= x (NaN: 0), and the thread's private 16-bit counter of that gap is incremented.  Counter
+// (gap g, stream thread t) lives at pool + (g * P_NS + t) * 2.
+__device__ __forceinline__ unsigned lds_u16(uint32_t addr) {
+    unsigned short c;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(c) : "r"(addr) : "memory");
+    return c;
+}
+__device__ __forceinline__ void sts_u16(uint32_t addr, unsigned c) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((unsigned short)c) : "memory");
+}
+__device__ __forceinline__ void pipe_levels4(const double (&x)[4], PAcc& acc, uint32_t thr32, uint32_t col32) {
+    {
+        const double t = (x[0] + x[1]) + (x[2] + x[3]);
+        if (t == t) {
+            acc.sum += t;
+            acc.nvalid += 4;
+            if (any_lt4(x[0], x[1], x[2], x[3], acc.mn)) acc.mn = rare_min4(acc.mn, x[0], x[1], x[2], x[3]);
+            if (any_gt4(x[0], x[1], x[2], x[3], acc.mx)) acc.mx = rare_max4(acc.mx, x[0], x[1], x[2], x[3]);
+        } else {
+            Stats4 st = {acc.sum, acc.mn, acc.mx, acc.nvalid};
+            st = rare_nan4(st, x[0], x[1], x[2], x[3]);
+            acc.sum = st.sum;
+            acc.mn = st.mn;
+            acc.mx = st.mx;
+            acc.nvalid = st.nv;
+        }
+    }
+    uint32_t g8[4] = {0u, 0u, 0u, 0u};   // 8 * (thresholds <= x)
+#pragma unroll
+    for (int step = 16; step >= 1; step >>= 1) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const double t = lds_f64(thr32 + g8[e] + (uint32_t)(step - 1) * 8u);
+            g8[e] += (x[e] >= t) ? (uint32_t)step * 8u : 0u;
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {   // one after another: two samples of a thread often share a gap
+        const uint32_t addr = col32 + g8[e] * (uint32_t)(P_NS * 2 / 8);
+        sts_u16(addr, lds_u16(addr) + 1u);
+    }
+}
+
+__device__ __noinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc, uint32_t pool32, const PipeSmem& sm,
+                                                uint32_t& g, int stid, int lane) {
+    const uint32_t thr32 = smem_u32(&pp->thr[0]);
+    const uint32_t col32 = pool32 + (uint32_t)stid * 2u;
+#pragma unroll 4
+    for (int b = 0; b <= P_NTHR; ++b) sts_u16(col32 + (uint32_t)b * (P_NS * 2), 0u);
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    const int L = pp->L, head = pp->head, body = pp->body, ntiles = pp->ntiles;
+    const double* v = pp->v;
+    if (stid == 0 && head) {
+        const double x[4] = {v[0], nan, nan, nan};
+        pipe_levels4(x, acc, thr32, col32);
+    }
+    if (stid == 32 && head + body < L) {
+        const double x[4] = {v[L - 1], nan, nan, nan};
+        pipe_levels4(x, acc, thr32, col32);
+    }
+    const uint32_t full0 = smem_u32(sm.bars() + B_RING_FULL), empty0 = smem_u32(sm.bars() + B_RING_EMPTY);
+    const uint32_t ring0 = smem_u32(sm.ring()) + (uint32_t)stid * 16u;
+    uint32_t s = g % P_STAGES, par = (g / P_STAGES) & 1u;
+    int rem2 = body >> 1;
+    for (int t = 0; t < ntiles; ++t) {
+        mbar_wait_addr(full0 + s * 8u, par);
+        const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
+        double x[4];
+        if (rem2 >= P_TILE / 2) {
+            lds_v2f64(base, x[0], x[1]);
+            lds_v2f64(base + P_NS * 16, x[2], x[3]);
+        } else {
+            x[0] = x[1] = x[2] = x[3] = nan;
+            if (stid < rem2) lds_v2f64(base, x[0], x[1]);
+            if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
+        }
+        pipe_levels4(x, acc, thr32, col32);
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
         rem2 -= P_TILE / 2;
@@ -2306,6 +2482,81 @@ __device__ __forceinline__ bool pipe_finish(const SeriesArgs& a, const PipePlan*
     return true;
 }
 
+// Finish of a levels plan: total the per-thread gap counters, then every rank must fall on a listed level, i.e.
+// (#valid samples < v) < rank <= (#valid samples <= v); otherwise the series goes to the slow path.
+__device__ __noinline__ bool pipe_finish_levels(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
+                                                const unsigned char* pool, int ftid, int fwarp, int lane) {
+    const int nq = a.nq;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    const uint32_t pool32 = smem_u32(pool);
+    for (int b = fwarp; b <= P_NTHR; b += P_FW) {
+        unsigned t = 0;
+#pragma unroll
+        for (int wd = 0; wd < P_NS / 64; ++wd) {
+            unsigned w;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(pool32 + (uint32_t)(b * P_NS * 2 + (wd * 32 + lane) * 4)));
+            t += (w & 0xFFFFu) + (w >> 16);
+        }
+        t = warp_sum_u(t);
+        if (lane == 0) sel->part[0][b] = t;
+    }
+    fin_sync();
+    if (ftid == 0) {
+        double s = 0.0, mn = INFINITY, mx = -INFINITY;
+        unsigned n = 0;
+        for (int w = 0; w < P_SW; ++w) {
+            s += res->sum[w];
+            mn = fmin(mn, res->mn[w]);
+            mx = fmax(mx, res->mx[w]);
+            n += res->nvalid[w];
+        }
+        unsigned tot = 0;
+        for (int b = 0; b <= P_NTHR; ++b) tot += sel->part[0][b];
+        // stale samples (and the padding of the last tile) all sit in gap 0
+        unsigned cum = sel->part[0][0] - (tot - n);   // valid samples below thr[0]
+        int fail = 0;
+        unsigned rk[NI_MAX];
+        double val[NI_MAX];
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            rk[j] = (j < nq && n > 0) ? nearest_rank_dev(n, a.q[j]) : 0u;
+            val[j] = nan;
+        }
+        const int nlev = pp->nlev;
+        for (int d = 0; d < nlev; ++d) {
+            const unsigned below = cum;                       // < v_d
+            const unsigned upto = cum + sel->part[0][2 * d + 1];   // <= v_d
+#pragma unroll
+            for (int j = 0; j < NI_MAX; ++j)
+                if (rk[j] > below && rk[j] <= upto) {
+                    val[j] = pp->thr[2 * d];
+                    rk[j] = 0u;
+                }
+            cum = upto + sel->part[0][2 * d + 2];             // < v_{d+1}
+        }
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j)
+            if (rk[j] != 0u) fail = 1;
+        sel->fail = fail;
+        if (!fail) {
+            const int sid = pp->sid;
+            if (a.out_sum) a.out_sum[sid] = s;
+            if (a.out_mean) a.out_mean[sid] = n > 0 ? s / (double)n : 0.0;
+            if (a.out_min) a.out_min[sid] = n > 0 ? mn + 0.0 : nan;
+            if (a.out_max) a.out_max[sid] = n > 0 ? mx + 0.0 : nan;
+            if (a.out_last) a.out_last[sid] = pp->last;
+            if (a.out_count) a.out_count[sid] = (int64_t)n;
+            if (a.out_quant) {
+#pragma unroll
+                for (int j = 0; j < NI_MAX; ++j)
+                    if (j < nq) a.out_quant[(int64_t)sid * nq + a.qcol[j]] = val[j];
+            }
+        }
+    }
+    fin_sync();
+    return sel->fail == 0;
+}
+
 // ------------------------------------------------------------------------------------------ kernel
 __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
     extern __shared__ __align__(128) unsigned char psmem[];
@@ -2414,7 +2665,9 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 }
                 const int nb = pp->nb;
                 KO_PT0();
-                if (pp->tail) {
+                if (pp->vals) {
+                    pipe_stream_levels(pp, acc, cx.pool32, sm, g, stid, lane);
+                } else if (pp->tail) {
                     if (nb == 0) pipe_stream<0, true>(pp, acc, cx, sm, g, stid, lane);
                     else if (nb == 1) pipe_stream<1, true>(pp, acc, cx, sm, g, stid, lane);
                     else pipe_stream<2, true>(pp, acc, cx, sm, g, stid, lane);
@@ -2462,7 +2715,8 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
             if (!pp->defer) {
                 const uint32_t pool = c & 1u;
                 { KO_PT0(); mbar_wait_sleep(sm.bars() + B_POOL_FULL + pool, (c >> 1) & 1u); KO_PT1(12, ftid == 0); }
-                { KO_PT0(); ok = pipe_finish(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), sm.ovq(pool), ftid, fwarp, lane); KO_PT1(10, ftid == 0); }
+                { KO_PT0(); ok = pp->vals ? pipe_finish_levels(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), ftid, fwarp, lane)
+                                          : pipe_finish(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), sm.ovq(pool), ftid, fwarp, lane); KO_PT1(10, ftid == 0); }
                 fin_sync();
                 if (ftid == 0) {
                     for (int i = 0; i < P_NI; ++i) sm.res(pool)->ovcnt[i] = 0;

@@ -131,6 +131,31 @@ def test_ties_constants_nan_inf(rollup):
         assert_series_parity(got, exp, values, offsets, qs)
 
 
+def test_few_distinct_values(rollup):
+    """Integer-valued and quantised gauges (DCGM temperature / utilisation style): the ranks sit inside heavy tie
+    groups, which the kernel answers by counting per listed level instead of capturing candidates."""
+    rng = np.random.default_rng(11)
+    series = []
+    for L in (5000, 40320, 40321, 172801):
+        series += [
+            np.floor(40.0 + 40.0 * rng.beta(2.0, 2.0, L)),                 # 40 integer levels
+            np.floor(100.0 * rng.beta(2.0, 5.0, L)) / 10.0,                # steps of 0.1 (not exact in binary)
+            np.floor(rng.normal(0.0, 2.0, L)),                             # negative and positive levels, +-0
+            np.where(rng.random(L) < 0.5, -0.0, np.floor(rng.normal(0.0, 1.5, L))),
+            np.where(rng.random(L) < 0.97, np.floor(rng.normal(60, 2, L)), rng.random(L) * 100),   # levels + stray values
+            np.where(rng.random(L) < 0.03, np.inf, np.floor(6 * rng.random(L))),   # +inf is one of the levels
+            np.where(rng.random(L) < 0.3, np.nan, np.floor(4 * rng.random(L))),    # many stale samples
+            np.floor(rng.random(L) * 12) * 1e-310,                         # denormal levels
+            np.concatenate([np.full(L - 40, 7.0), np.arange(40.0)]),       # levels the pre-sample never sees
+        ]
+    offsets = np.concatenate([[0], np.cumsum([len(x) for x in series])]).astype(np.int64)
+    values = np.concatenate(series)
+    for qs in (QS, [0.5], [0.0, 1.0, 0.25, 0.75], [0.9, 0.1]):
+        got = rollup.series_rollup(values, offsets, qs)
+        exp = c_oracle.series_rollup(values, offsets, qs, nthreads=8)
+        assert_series_parity(got, exp, values, offsets, qs)
+
+
 def test_very_long_series_refinement_passes(rollup):
     # 30 days at 15 s (config 3/4 length): the brackets do not fit shared memory -> histogram refinement
     d = synth.make_series(dict(nodes=1, gpus=1, pods=1, L=172800), seed=6)
