@@ -49,10 +49,18 @@ struct SeriesArgs {
     double* out_last;
     int64_t* out_count;
     double* out_quant;
-    int* counters;  // [0] n_long  [1] work cursor  [2] error flag  [3] series needing extra passes  [4] deferred  [5] cursor
+    int* counters;  // [0] n_long  [2] error flag  [3] series needing extra passes  [4] deferred by the fast path
+                    // [6] deferred again by its wide second attempt  [7] work cursor of series_long
     int* long_list;
-    int* defer_list;  // series the pipelined fast path hands to series_long (counters[4] entries, cursor counters[5])
-    int fb;           // series_long works on the deferred list
+    int* defer_list;  // series the pipelined fast path could not finish (counters[4] entries)
+    // The long-series kernels are launched three times over different lists (see launch_long_path):
+    const int* work_list;   // series to process ...
+    int work_cnt;           // ... their number is counters[work_cnt]
+    int work_cur;           // series_long: index of its work cursor in counters
+    int* out_list;          // series_pipe: where the series it cannot finish go ...
+    int out_cnt;            // ... counted in counters[out_cnt]
+    int wide;               // series_pipe: second attempt, one quantile per work item, twice the bracket width
+    int pack;               // n_series < 2^27: the first attempt's list carries the unanswered quantiles in bits 27..30
     int nq;
     double q[NI_MAX];   // ascending
     int qcol[NI_MAX];   // output column of q[j]
@@ -1027,9 +1035,9 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
         mbar_fence_init();
     }
     __syncthreads();
-    const int n_long = a.counters[a.fb ? 4 : 0];
-    const int* work_list = a.fb ? a.defer_list : a.long_list;
-    int* cursor = &a.counters[a.fb ? 5 : 1];
+    const int n_long = a.counters[a.work_cnt];
+    const int* work_list = a.work_list;
+    int* cursor = &a.counters[a.work_cur];
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
     uint32_t g = 0;  // running ring tile index, identical in all threads
 #ifdef KO_PHASE_TIMING
@@ -1369,17 +1377,18 @@ constexpr int P_FW = 6;                        // finish warps
 constexpr int P_NS = P_SW * 32;                // 384 stream threads
 constexpr int P_NF = P_FW * 32;                // 128 finish threads
 constexpr int P_PW = 2;                        // planner warps (series alternate between them)
-constexpr int P_PLANS = 4;                     // plan slots
+constexpr int P_PLANS = 8;                     // plan slots (a plan takes longer to build than a series to stream)
+constexpr uint32_t P_PLAN_LOG = 3;
 constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW) * 32;   // planners, producer, stream, finish
 constexpr int P_TILE = 4 * P_NS;               // 1536 doubles (12 KB) per ring stage
-constexpr int P_STAGES = 4;
+constexpr int P_STAGES = 3;
 constexpr int P_SLOTS = 24;                    // thread-private candidate slots per stream thread
 constexpr int P_OVQ = 768;                     // overflow queue entries per pool
 constexpr int P_NI = 3;                        // at most 2 brackets + 1 upper tail
-constexpr int P_COLS = P_NS / P_NF;             // stream-thread columns per finish thread
-static_assert(P_COLS * P_NF == P_NS && (P_COLS == 2 || P_COLS == 3), "finish threads own 2 or 3 whole columns");
+static_assert(P_NS == 2 * P_NF && P_NF % 96 == 0, "finish groups of P_NF/1, /2, /3 threads own whole column pairs");
 constexpr int P_LIST = 256;                    // candidates of one sub-bracket kept for the final rank counting
 constexpr int P_SAMPLE = 1024;
+constexpr int P_CROW = P_NF + 4;               // bytes per row of the finish warps' counters
 constexpr int P_LEVELS = 15;                   // distinct values a "levels" plan can list
 constexpr int P_NTHR = 31;                     // thresholds searched per sample (2 per level + one +inf pad)
 constexpr int P_MAX_L_LEVELS = 16000000;       // keeps the 16-bit per-thread counters of a levels plan exact
@@ -1402,39 +1411,33 @@ struct PipePlan {
     // candidate is captured; thr holds, ascending, each listed level v and the next double above it, padded
     // with +inf, and the stream warps count the samples per gap between consecutive thresholds.
     int vals, nlev;
+    int qsel;                // wide attempt: the one quantile this work item answers (-1: all)
+    int item;                // wide attempt: index of the series in the work list
     int vidx[P_LEVELS + 1];
     double thr[P_NTHR + 1];
 };
 
 struct PipeResult {          // what the stream warps hand to the finish warps, one per pool
-    double sum[P_SW], mn[P_SW], mx[P_SW];
-    unsigned nvalid[P_SW];
-    unsigned cA[P_SW][P_NI];
-    unsigned cin[P_SW][P_NI];
+    double sum[P_SW], mn[P_SW], mx[P_SW];          // per stream warp (summed in warp order: reproducible)
+    // totals over all stream warps, added with shared-memory reductions, cleared by the finish warps
+    unsigned t_nvalid, t_cA[P_NI], t_cin[P_NI], t_ncap[P_NI];
     unsigned ovcnt[P_NI];
     unsigned short pcount[P_NI][P_NS];   // captured entries per stream thread
     double trash;                        // sink of captures that find slots and queue full
 };
 
 struct PipeSel {             // scratch of the finish warps
-    union {                                    // the counters are dead once their sums are taken
-        unsigned char cnt8[64][P_NF];          // per-thread byte counters of the 64 sub-brackets (8 KB)
-        unsigned long long list[NI_MAX][P_LIST];   // candidates of the chosen sub-bracket per quantile (8 KB)
-    };
-    unsigned part[P_NF / 64][64];              // sums of the counters
-    unsigned char dummy[3][P_NF];              // counters of absent samples
+    // per-thread byte counters of the 64 sub-brackets, zero between uses; the row stride of 49 words spreads the
+    // sub-brackets over the shared-memory banks
+    unsigned char cnt8[64][P_CROW];
+    double list[NI_MAX][P_LIST];               // candidates of the chosen sub-bracket per quantile
+    unsigned tot[P_NI][64];                    // sums of the counters per group
+    unsigned char dummy[2][P_NF];              // counters of absent samples
     unsigned list_cnt[NI_MAX];
-    unsigned long long lo[NI_MAX], hi[NI_MAX]; // chosen sub-bracket per quantile
-    unsigned rho[NI_MAX];
-    int act[NI_MAX];                           // 1 = needs a select
+    int bin[NI_MAX];                           // chosen sub-bracket per quantile
+    unsigned rho[NI_MAX];                      // rank inside it
     int fail;
     double val[NI_MAX];
-    unsigned long long ikA[P_NI], ikB[P_NI];   // effective bracket per interval
-    int ish[P_NI], iuse[P_NI];
-    unsigned cAt[P_NI], nin[P_NI];
-    unsigned nvalid;
-    double sum, mn, mx;
-    double wmx[P_FW];
 };
 
 __host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) / 16 * 16; }
@@ -1468,7 +1471,8 @@ struct PipeSmem {
     __device__ __forceinline__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + PO_BARS); }
 };
 
-enum { B_RING_FULL = 0, B_RING_EMPTY = 5, B_PLAN_FULL = 10, B_PLAN_FREE = 14, B_POOL_FULL = 18, B_POOL_FREE = 20 };
+enum { B_RING_FULL = 0, B_RING_EMPTY = 5, B_PLAN_FULL = 10, B_PLAN_FREE = 18, B_POOL_FULL = 26, B_POOL_FREE = 28 };
+static_assert(P_PLANS == (1 << P_PLAN_LOG) && B_PLAN_FREE - B_PLAN_FULL >= P_PLANS && B_POOL_FULL - B_PLAN_FREE >= P_PLANS, "barrier slots");
 
 __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(P_NF) : "memory"); }
 
@@ -1562,7 +1566,8 @@ struct RegArr {
 };
 
 // Whole warp, every value uniform: build the plan of series `sid` into *pp.
-__device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a, int sid, int lane) {
+__device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a, int sid, int qsel, int item,
+                                              int lane) {
     const int64_t off0 = a.offsets[sid];
     const int L = (int)(a.offsets[sid + 1] - off0);
     const double* v = a.values + off0;
@@ -1648,11 +1653,11 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         int cur_lo = 0, cur_hi = 0;   // the interval being grown
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) {
-            if (j < nq && !defer) {
+            if (j < nq && !defer && (qsel < 0 || j == qsel)) {
                 const double q = a.q[j];
                 const double pos = q * (double)valid_s;
                 const double sig = sqrt(fmax(q * (1.0 - q), 0.0) * (double)valid_s);
-                const int m = (int)ceil(CSIG * sig) + 2;
+                const int m = (int)ceil((a.wide ? 2.0 * CSIG : CSIG) * sig) + 2;
                 int aj = (int)floor(pos) - m - 1, bj = (int)ceil(pos) + m;
                 if (aj < 0) aj = -1;
                 if (bj > valid_s) bj = valid_s;
@@ -1670,7 +1675,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                 lo.set(ni - 1, cur_lo);
                 hi.set(ni - 1, cur_hi);
                 q_iv.v[j] = ni - 1;
-                if (j >= 2 && q_iv.v[j - 2] == ni - 1) soft = 1;   // three quantiles in one interval
+                if (qsel < 0 && j >= 2 && q_iv.v[j - 2] == ni - 1) soft = 1;   // three quantiles in one interval
             }
         }
         int total = 0, ncap = 0, ties = 0;
@@ -1828,6 +1833,8 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         pp->tail = tail;
         pp->vals = vals;
         pp->nlev = nlev;
+        pp->qsel = qsel;
+        pp->item = item;
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) pp->q_iv[j] = q_iv.v[j];
     }
@@ -1929,9 +1936,7 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
             acc.nvalid += 4;
             if (NB > 0 || TAIL) {   // seeded
                 if (any_lt4(x[0], x[1], x[2], x[3], acc.mn)) acc.mn = rare_min4(acc.mn, x[0], x[1], x[2], x[3]);
-                if (!TAIL) {
-                    if (any_gt4(x[0], x[1], x[2], x[3], acc.mx)) acc.mx = rare_max4(acc.mx, x[0], x[1], x[2], x[3]);
-                }
+                if (any_gt4(x[0], x[1], x[2], x[3], acc.mx)) acc.mx = rare_max4(acc.mx, x[0], x[1], x[2], x[3]);
             } else {
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
@@ -1944,7 +1949,7 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
             st = rare_nan4(st, x[0], x[1], x[2], x[3]);
             acc.sum = st.sum;
             acc.mn = st.mn;
-            if (!TAIL) acc.mx = st.mx;
+            acc.mx = st.mx;
             acc.nvalid = st.nv;
         }
     }
@@ -2165,58 +2170,18 @@ __device__ __noinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc, u
 }
 
 // ------------------------------------------------------------------------------------------ finish
-// Explicit shared-memory loads: a generic load would queue behind the planner's outstanding global gathers in
-// the load/store unit and take microseconds.
-template <typename F3, typename F1>
-__device__ __forceinline__ void pipe_for_rows(const unsigned char* pool, const double* ovq, const PipePlan* pp,
-                                              const PipeResult* res, int i, int ftid, F3 frow, F1 fone) {
-    // Each finish thread owns the private slots of P_COLS stream threads.  Shared-memory latency is > 100 cycles
-    // while the stream warps and the TMA engine keep the banks busy, so the next row is fetched before the
-    // current one is processed and frow() handles the samples of a row together.
-    const uint32_t base = smem_u32(pool) + (uint32_t)(((size_t)pp->slot0[i] * P_NS + ftid) * 8);
-    const int n0 = res->pcount[i][ftid], n1 = res->pcount[i][ftid + P_NF];
-    const int n2 = P_COLS == 3 ? res->pcount[i][ftid + 2 * P_NF] : 0;
-    const int nmax = max(n0, max(n1, n2));
-#ifdef KO_PHASE_TIMING
-    const unsigned long long _l0 = clock64();
-#endif
-    double y0 = 0.0, y1 = 0.0, y2 = 0.0;
-    if (0 < n0) y0 = lds_f64(base);
-    if (0 < n1) y1 = lds_f64(base + P_NF * 8);
-    if (P_COLS == 3 && 0 < n2) y2 = lds_f64(base + 2 * P_NF * 8);
-    for (int s = 0; s < nmax; ++s) {
-        const double x0 = y0, x1 = y1, x2 = y2;
-        const uint32_t nrow = base + (uint32_t)(s + 1) * (P_NS * 8);
-        if (s + 1 < n0) y0 = lds_f64(nrow);
-        if (s + 1 < n1) y1 = lds_f64(nrow + P_NF * 8);
-        if (P_COLS == 3 && s + 1 < n2) y2 = lds_f64(nrow + 2 * P_NF * 8);
-        frow(x0, s < n0, x1, s < n1, x2, P_COLS == 3 && s < n2);
-    }
-#ifdef KO_PHASE_TIMING
-    if (blockIdx.x == 0 && ftid == 0) {
-        g_phase[20] += clock64() - _l0;
-        g_phase[21] += (unsigned long long)nmax;
-        g_phase[22] = g_phase[22] > (unsigned long long)nmax ? g_phase[22] : (unsigned long long)nmax;
-        g_phase[23] += 1;
-    }
-#endif
-    const int ovn = (int)min(res->ovcnt[i], (unsigned)pp->ovcap[i]);
-    const uint32_t ov32 = smem_u32(ovq) + (uint32_t)pp->ov0[i] * 8u;
-    for (int q = ftid; q < ovn; q += P_NF) fone(lds_f64(ov32 + (uint32_t)q * 8u));
-}
-
-template <typename F>
-__device__ __forceinline__ void pipe_for_each(const unsigned char* pool, const double* ovq, const PipePlan* pp,
-                                              const PipeResult* res, int i, int ftid, F f) {
-    pipe_for_rows(pool, ovq, pp, res, i, ftid,
-                  [&](double x0, bool v0, double x1, bool v1, double x2, bool v2) {
-                      if (v0) f(x0);
-                      if (v1) f(x1);
-                      if (v2) f(x2);
-                  },
-                  f);
-}
-
+// The finish warps turn the captured candidates of one series into its order statistics.
+//
+// Selection without shared-memory atomics on the hot path (a warp-wide shared atomic costs ~64 cycles): the
+// bracket of an interval is cut into 64 sub-brackets, linear in key space; every finish thread counts its share of
+// the candidates into PRIVATE byte counters (plain load / add / store), the counters are summed with dp4a, the
+// sub-bracket holding the wanted rank is found with a warp scan, its few dozen candidates are collected, and
+// the exact order statistic among them is found by rank counting.
+//
+// The capturing intervals of a series (1..3) are worked on side by side: the P_NF finish threads split into one
+// group per interval, each group synchronising on its own named barrier.  Everything the groups need to agree on
+// before that (valid count, ranks, which bracket holds which rank) is computed redundantly by every thread from
+// the totals the stream warps left in PipeResult, so no barrier precedes the first scan.
 __device__ __forceinline__ unsigned lds_u8(uint32_t addr) {
     unsigned c;
     asm volatile("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
@@ -2224,6 +2189,17 @@ __device__ __forceinline__ unsigned lds_u8(uint32_t addr) {
 }
 __device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
     asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+}
+__device__ __forceinline__ unsigned lds_u32(uint32_t addr) {
+    unsigned c;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
+    return c;
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, unsigned c) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+}
+__device__ __forceinline__ void group_sync(int grp, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(3 + grp), "r"(nthreads) : "memory");
 }
 
 #ifdef KO_PHASE_TIMING
@@ -2238,253 +2214,352 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
 #else
 #define KO_FT(slot) do { } while (0)
 #endif
-// Returns false when the series has to be deferred to the exact slow path.
-//
-// Selection without shared-memory atomics on the hot path (a warp-wide shared atomic costs ~64 cycles): the
-// bracket of an interval is cut into 64 sub-brackets, linear in key space; every finish thread counts its share of
-// the candidates into PRIVATE byte counters (plain load / add / store), the counters are summed with dp4a, the
-// sub-bracket holding the wanted rank is found, its few dozen candidates are collected, and one warp finds the
-// exact order statistic among them by rank counting.
-__device__ __forceinline__ bool pipe_finish(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
-                            const unsigned char* pool, const double* ovq, int ftid, int fwarp, int lane) {
-    const int ni = pp->ni, nq = a.nq;
+
+// What every finish thread knows about its own interval after the prologue.
+struct FinIv {
+    int iv;                      // interval index
+    unsigned long long kA;       // bracket [kA, kB) in key space
+    int ish;                     // (key - kA) >> ish is the sub-bracket, in [0, 64)
+    int j0, j1;                  // quantiles (ascending positions) to select in this interval, -1 = none
+    unsigned rho0, rho1;         // their ranks inside the bracket (1-based)
+};
+
+// Visit the candidates of interval fi.iv that belong to group thread gt: the private slots of the stream threads
+// gt, gt + G, ... taken two columns at a time (shared-memory latency is > 100 cycles while the stream warps and
+// the TMA engine keep the banks busy, so the next row is fetched before the current one is processed), then a
+// share of the overflow queue.
+template <int NG, typename F2, typename F1>
+__device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, const PipePlan* pp,
+                                             const PipeResult* res, int iv, int gt, F2 frow, F1 fone) {
+    constexpr int G = P_NF / NG;
+    const uint32_t base0 = pool32 + (uint32_t)(((size_t)pp->slot0[iv] * P_NS + gt) * 8);
+#pragma unroll
+    for (int pr = 0; pr < NG; ++pr) {   // P_NS / G = 2 * NG columns
+        const int c0 = gt + 2 * pr * G;
+        const uint32_t base = base0 + (uint32_t)(2 * pr * G) * 8u;
+        const int n0 = res->pcount[iv][c0], n1 = res->pcount[iv][c0 + G];
+        const int nmax = max(n0, n1);
+        double y0 = 0.0, y1 = 0.0;
+        if (0 < n0) y0 = lds_f64(base);
+        if (0 < n1) y1 = lds_f64(base + G * 8);
+        for (int s = 0; s < nmax; ++s) {
+            const double x0 = y0, x1 = y1;
+            const uint32_t nrow = base + (uint32_t)(s + 1) * (P_NS * 8);
+            if (s + 1 < n0) y0 = lds_f64(nrow);
+            if (s + 1 < n1) y1 = lds_f64(nrow + G * 8);
+            frow(x0, s < n0, x1, s < n1);
+        }
+    }
+    const int ovn = (int)min(res->ovcnt[iv], (unsigned)pp->ovcap[iv]);
+    const uint32_t ov32 = ovq32 + (uint32_t)pp->ov0[iv] * 8u;
+    for (int q = gt; q < ovn; q += G) fone(lds_f64(ov32 + (uint32_t)q * 8u));
+}
+
+// The group phase: NG capturing intervals, G = P_NF / NG threads each.  `use` is uniform inside a group.
+template <int NG>
+__device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult* res, PipeSel* sel, uint32_t pool32,
+                                           uint32_t ovq32, const FinIv& fi, int grp, int gt, int ftid) {
+    constexpr int G = P_NF / NG;
+    constexpr int GW = G / 4;            // 32-bit words of one sub-bracket's counters inside the group
+    const bool use = fi.j0 >= 0;
+    const unsigned long long kA = fi.kA;
+    const int ish = fi.ish;
+    const uint32_t cnt32 = smem_u32(&sel->cnt8[0][0]);
+#ifdef KO_PHASE_TIMING
+    unsigned long long _ft = clock64();
+#endif
+    // ---- scan 1: private byte counters per sub-bracket (zero on entry)
+    if (use) {
+        const uint32_t col = cnt32 + (uint32_t)ftid;
+        const uint32_t dummy = smem_u32(&sel->dummy[0][0]) + (uint32_t)ftid;
+        auto addr_of = [&](double xv, bool valid, int which) -> uint32_t {
+            const unsigned long long k = ko_okey(xv + 0.0);
+            return valid ? col + (uint32_t)((k - kA) >> ish) * (uint32_t)P_CROW : dummy + (uint32_t)which * P_NF;
+        };
+        fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
+                         [&](double x0, bool v0, double x1, bool v1) {
+                             const uint32_t a0 = addr_of(x0, v0, 0), a1 = addr_of(x1, v1, 1);
+                             if (a0 == a1) {   // both samples in one sub-bracket: one after the other
+                                 sts_u8(a0, lds_u8(a0) + 1);
+                                 sts_u8(a1, lds_u8(a1) + 1);
+                             } else {
+                                 const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1);
+                                 sts_u8(a0, c0 + 1);
+                                 sts_u8(a1, c1 + 1);
+                             }
+                         },
+                         [&](double xv) {
+                             const uint32_t a0 = addr_of(xv, true, 0);
+                             sts_u8(a0, lds_u8(a0) + 1);
+                         });
+    }
+    group_sync(grp, G);
+    KO_FT(24);
+    // ---- totals per sub-bracket: thread b sums the group's byte counters of sub-bracket b with dp4a
+    if (use && gt < 64) {
+        const uint32_t w = cnt32 + (uint32_t)(gt * P_CROW + grp * G);
+        unsigned t = 0;
+#pragma unroll 8
+        for (int x = 0; x < GW; ++x) t = __dp4a(lds_u32(w + 4u * x), 0x01010101u, t);
+        sel->tot[grp][gt] = t;
+    }
+    group_sync(grp, G);
+    KO_FT(25);
+    // ---- the counters are dead: clear them for the next series; meanwhile the group's first warp finds the
+    // sub-bracket of each wanted rank with a scan over the 64 totals (two per lane)
+    if (use) {
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+            const int idx = gt + t * G;            // 64 * GW words, G threads
+            const int bin = idx / GW, wd = idx - bin * GW;
+            sts_u32(cnt32 + (uint32_t)(bin * P_CROW + grp * G + wd * 4), 0u);
+        }
+        if (gt < 32) {
+            const int lane = gt;
+            const unsigned h0 = sel->tot[grp][2 * lane], h1 = sel->tot[grp][2 * lane + 1];
+            const unsigned s = h0 + h1;
+            unsigned incl = s;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            const unsigned excl = incl - s;
+#pragma unroll
+            for (int jj = 0; jj < 2; ++jj) {
+                const int j = jj ? fi.j1 : fi.j0;
+                const unsigned rho = jj ? fi.rho1 : fi.rho0;
+                if (j >= 0) {
+                    const bool m0 = excl < rho && rho <= excl + h0;
+                    const bool m1 = excl + h0 < rho && rho <= incl;
+                    const unsigned hit = __ballot_sync(0xffffffffu, m0 || m1);
+                    if (m0 || m1) {
+                        sel->bin[j] = 2 * lane + (m1 ? 1 : 0);
+                        sel->rho[j] = rho - (m1 ? excl + h0 : excl);
+                        if ((m1 ? h1 : h0) > (unsigned)P_LIST) atomicOr(&sel->fail, 1 << j);   // a heavy tie group
+                    }
+                    if (hit == 0u && lane == 0) atomicOr(&sel->fail, 1 << j);
+                }
+            }
+        }
+    }
+    group_sync(grp, G);
+    KO_FT(26);
+    // ---- scan 2: collect the candidates of each wanted sub-bracket (at most two ranks per interval)
+    if (use) {
+        const unsigned b0 = (unsigned)sel->bin[fi.j0];   // (a quantile that failed above keeps a stale but harmless bin)
+        const unsigned b1 = fi.j1 >= 0 ? (unsigned)sel->bin[fi.j1] : 0xFFFFFFFFu;
+        const uint32_t cnt0 = smem_u32(&sel->list_cnt[fi.j0]), cnt1 = smem_u32(&sel->list_cnt[fi.j1 < 0 ? 0 : fi.j1]);
+        const uint32_t l0 = smem_u32(&sel->list[fi.j0][0]), l1 = smem_u32(&sel->list[fi.j1 < 0 ? 0 : fi.j1][0]);
+        auto take = [&](double xv) {
+            const double xc = xv + 0.0;
+            const unsigned b = (unsigned)((ko_okey(xc) - kA) >> ish);
+            if (b == b0) {
+                unsigned pos;
+                asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt0) : "memory");
+                if (pos < (unsigned)P_LIST) sts_f64(l0 + pos * 8u, xc);
+            }
+            if (b == b1) {
+                unsigned pos;
+                asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt1) : "memory");
+                if (pos < (unsigned)P_LIST) sts_f64(l1 + pos * 8u, xc);
+            }
+        };
+        fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
+                         [&](double x0, bool v0, double x1, bool v1) {
+                             if (v0) take(x0);
+                             if (v1) take(x1);
+                         },
+                         take);
+    }
+    group_sync(grp, G);
+    KO_FT(27);
+    // ---- exact order statistic inside each short list by rank counting (doubles compare like their keys)
+    if (use) {
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int j = jj ? fi.j1 : fi.j0;
+            if (j >= 0) {
+                const int n = (int)min(sel->list_cnt[j], (unsigned)P_LIST);
+                const unsigned rho = sel->rho[j];
+                const uint32_t l32 = smem_u32(&sel->list[j][0]);
+                for (int idx = gt; idx < n; idx += G) {
+                    const double e = lds_f64(l32 + (uint32_t)idx * 8u);
+                    unsigned lt = 0, le = 0;
+#pragma unroll 4
+                    for (int m = 0; m < n; ++m) {
+                        const double v = lds_f64(l32 + (uint32_t)m * 8u);
+                        lt += (v < e) ? 1u : 0u;
+                        le += (v <= e) ? 1u : 0u;
+                    }
+                    if (lt < rho && rho <= le) sel->val[j] = e;   // all writers hold the same value
+                }
+            }
+        }
+    }
+    KO_FT(28);
+}
+
+// Returns (meaningful on finish thread 0) the mask of quantiles that a later attempt has to answer; 0 = all done.
+__device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
+                                            const unsigned char* pool, const double* ovq, int ftid, int fwarp,
+                                            int lane) {
+    (void)fwarp;
+    const int ni = pp->ni, nq = a.nq, nb = pp->nb, qsel = pp->qsel;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
 #ifdef KO_PHASE_TIMING
     unsigned long long _ft = clock64();
 #endif
-    if (ftid < P_NI) sel->nin[ftid] = 0;
-    if (ftid == 0) sel->fail = 0;
-    fin_sync();
-    // captured entries per interval
-    for (int i = 0; i < ni; ++i) {
-        unsigned c = (unsigned)res->pcount[i][ftid] + res->pcount[i][ftid + P_NF] +
-                     (P_COLS == 3 ? res->pcount[i][ftid + 2 * P_NF] : 0);
-        c = warp_sum_u(c);
-        if (lane == 0) red_shared_add(&sel->nin[i], c);
-    }
-    if (pp->tail) {   // the stream warps leave the maximum to us: it is among the upper-tail candidates
-        double m = -INFINITY;
-        pipe_for_each(pool, ovq, pp, res, ni - 1, ftid, [&](double xv) { m = fmax(m, xv); });
-        m = warp_max(m);
-        if (lane == 0) sel->wmx[fwarp] = m;
-    }
-    fin_sync();
-    if (ftid == 0) {
-        double s = 0.0, mn = INFINITY, mx = -INFINITY;
-        unsigned n = 0;
+    // ---- prologue, redundantly in every thread (all values uniform)
+    const unsigned n = res->t_nvalid;
+    double mx = lane < P_SW ? res->mx[lane] : -INFINITY;
+    mx = warp_max(mx);
+    if (ftid == 32) {   // the plain statistics do not depend on the selection: written here, off the critical path
+        double s = 0.0, mn = INFINITY;
         for (int w = 0; w < P_SW; ++w) {
             s += res->sum[w];
             mn = fmin(mn, res->mn[w]);
-            mx = fmax(mx, res->mx[w]);
-            n += res->nvalid[w];
         }
-        if (pp->tail)
-            for (int w = 0; w < P_FW; ++w) mx = fmax(mx, sel->wmx[w]);
-        sel->sum = s;
-        sel->mn = mn;
-        sel->mx = mx;
-        sel->nvalid = n;
-        for (int i = 0; i < ni; ++i) {
-            unsigned ca = 0, ci = 0;
-            if (i < pp->nb)
-                for (int w = 0; w < P_SW; ++w) {
-                    ca += res->cA[w][i];
-                    ci += res->cin[w][i];
-                }
-            const unsigned nin = sel->nin[i] + res->ovcnt[i] + ci;
-            sel->nin[i] = nin;
-            sel->cAt[i] = (i < pp->nb) ? ca : n - nin;   // upper tail: everything outside is below
-            unsigned long long kB = pp->kB[i];
-            if (kB > KO_KEY_PINF) kB = ko_okey(mx + 0.0) + 1;   // upper tail: nothing lies above the series maximum
-            sel->ikA[i] = pp->kA[i];
-            sel->ikB[i] = kB;
-            const unsigned long long span = kB - pp->kA[i] - 1;   // kB > kA
-            const int bits = span ? 64 - __clzll((long long)span) : 0;
-            sel->ish[i] = bits > 6 ? bits - 6 : 0;               // (key - kA) >> ish is in [0, 64)
-            sel->iuse[i] = 0;
-        }
+        const int sid = pp->sid;
+        if (a.out_sum) a.out_sum[sid] = s;
+        if (a.out_mean) a.out_mean[sid] = n > 0 ? s / (double)n : 0.0;
+        if (a.out_min) a.out_min[sid] = n > 0 ? mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = n > 0 ? mx + 0.0 : nan;
+        if (a.out_last) a.out_last[sid] = pp->last;
+        if (a.out_count) a.out_count[sid] = (int64_t)n;
+    }
+    unsigned cAt[P_NI], nin[P_NI];
+    unsigned long long kA[P_NI], kB[P_NI];
+    int ish[P_NI], ord[P_NI];
+    bool capm[P_NI], ovbad[P_NI];
+    int ncapi = 0;
 #pragma unroll
-        for (int j = 0; j < NI_MAX; ++j) {
-            if (j >= nq) continue;
-            sel->act[j] = 0;
-            sel->val[j] = nan;
-            sel->list_cnt[j] = 0;
-            if (n == 0) continue;
+    for (int i = 0; i < P_NI; ++i) {
+        cAt[i] = nin[i] = 0;
+        kA[i] = 0;
+        kB[i] = 1;
+        ish[i] = 0;
+        ord[i] = -1;
+        capm[i] = ovbad[i] = false;
+        if (i < ni) {
+            nin[i] = res->t_ncap[i] + res->ovcnt[i] + res->t_cin[i];
+            cAt[i] = (i < nb) ? res->t_cA[i] : n - nin[i];   // upper tail: everything outside is below
+            kA[i] = pp->kA[i];
+            kB[i] = pp->kB[i];
+            if (kB[i] > KO_KEY_PINF) kB[i] = ko_okey(mx + 0.0) + 1;   // upper tail: nothing lies above the maximum
+            const unsigned long long span = kB[i] - kA[i] - 1;        // kB > kA
+            const int bits = span ? 64 - __clzll((long long)span) : 0;
+            ish[i] = bits > 6 ? bits - 6 : 0;
+            capm[i] = pp->mode[i] == M_CAPTURE;
+            ovbad[i] = res->ovcnt[i] > (unsigned)pp->ovcap[i];
+            if (capm[i]) ord[i] = ncapi++;
+        }
+    }
+    int failmask = 0;   // quantiles this attempt cannot answer
+    double dval[NI_MAX];
+    int act_iv[NI_MAX];
+    unsigned rho[NI_MAX];
+#pragma unroll
+    for (int j = 0; j < NI_MAX; ++j) {
+        dval[j] = nan;
+        act_iv[j] = -1;
+        rho[j] = 0;
+        if (j < nq && n > 0 && (qsel < 0 || j == qsel)) {
             const int i = pp->q_iv[j];
             const unsigned r = nearest_rank_dev(n, a.q[j]);
-            const unsigned cA = sel->cAt[i], nb = sel->nin[i];
-            if (r <= cA || r > cA + nb) {
-                sel->fail = 1;  // the bracket missed the rank
-                continue;
+            unsigned cA = cAt[0], nn = nin[0];
+            unsigned long long ka = kA[0], kb = kB[0];
+            bool cm = capm[0], ob = ovbad[0];
+#pragma unroll
+            for (int t = 1; t < P_NI; ++t)
+                if (i == t) {
+                    cA = cAt[t];
+                    nn = nin[t];
+                    ka = kA[t];
+                    kb = kB[t];
+                    cm = capm[t];
+                    ob = ovbad[t];
+                }
+            if (r <= cA || r > cA + nn) {
+                failmask |= 1 << j;       // the bracket missed the rank
+            } else if (!cm || kb - ka == 1) {
+                dval[j] = ko_key2d(ka);   // a single value: answered by the counts
+            } else if (ob) {
+                failmask |= 1 << j;       // more candidates than shared memory holds
+            } else {
+                act_iv[j] = i;
+                rho[j] = r - cA;
             }
-            if (pp->mode[i] == M_COUNT || sel->ikB[i] - sel->ikA[i] == 1) {
-                sel->val[j] = ko_key2d(sel->ikA[i]);
-                continue;
-            }
-            if (res->ovcnt[i] > (unsigned)pp->ovcap[i]) {
-                sel->fail = 1;  // more candidates than shared memory holds
-                continue;
-            }
-            sel->act[j] = 1;
-            sel->rho[j] = r - cA;
-            sel->iuse[i] = 1;
         }
     }
-    fin_sync();
     KO_FT(13);
-    if (sel->fail) return false;
-    int qiv[NI_MAX];
+    bool any_act = false;
 #pragma unroll
-    for (int j = 0; j < NI_MAX; ++j) qiv[j] = (j < nq) ? pp->q_iv[j] : -1;
-#pragma unroll 1
-    for (int i = 0; i < ni; ++i) {
-        if (!sel->iuse[i]) continue;   // uniform
-        const unsigned long long kA = sel->ikA[i];
-        const int ish = sel->ish[i];
-        // ---- scan 1: private byte counters per sub-bracket
-        {
-            uint32_t* w = reinterpret_cast<uint32_t*>(&sel->cnt8[0][0]);
-            for (int t = ftid; t < 64 * P_NF / 4; t += P_NF) w[t] = 0;
+    for (int j = 0; j < NI_MAX; ++j) any_act = any_act || act_iv[j] >= 0;
+    if (any_act) {
+        // my group and its interval
+        int grp = 0, gt = ftid;
+        if (ncapi == 2) {
+            grp = ftid >= P_NF / 2 ? 1 : 0;
+            gt = ftid - grp * (P_NF / 2);
+        } else if (ncapi == 3) {
+            grp = ftid / (P_NF / 3);
+            gt = ftid - grp * (P_NF / 3);
         }
-        fin_sync();
-        {
-            // private byte counters: the three samples of a row update three counters; their loads are issued
-            // together unless two of them hit the same counter (then the updates are applied one after another)
-            const uint32_t col = smem_u32(&sel->cnt8[0][0]) + (uint32_t)ftid;
-            const uint32_t dummy = smem_u32(&sel->dummy[0][0]) + (uint32_t)ftid;
-            auto addr_of = [&](double xv, bool valid, int which) -> uint32_t {
-                const unsigned long long k = ko_okey(xv + 0.0);
-                return valid ? col + (uint32_t)((k - kA) >> ish) * (uint32_t)P_NF : dummy + (uint32_t)which * P_NF;
-            };
-            pipe_for_rows(pool, ovq, pp, res, i, ftid,
-                          [&](double x0, bool v0, double x1, bool v1, double x2, bool v2) {
-                              const uint32_t a0 = addr_of(x0, v0, 0), a1 = addr_of(x1, v1, 1), a2 = addr_of(x2, v2, 2);
-                              if (a0 == a1 || a0 == a2 || a1 == a2) {
-                                  sts_u8(a0, lds_u8(a0) + 1);
-                                  sts_u8(a1, lds_u8(a1) + 1);
-                                  sts_u8(a2, lds_u8(a2) + 1);
-                              } else {
-                                  const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1), c2 = lds_u8(a2);
-                                  sts_u8(a0, c0 + 1);
-                                  sts_u8(a1, c1 + 1);
-                                  sts_u8(a2, c2 + 1);
-                              }
-                          },
-                          [&](double xv) {
-                              const uint32_t a0 = addr_of(xv, true, 0);
-                              sts_u8(a0, lds_u8(a0) + 1);
-                          });
-        }
-        fin_sync();
-        KO_FT(14);
-        {   // totals per sub-bracket: thread (bin, half) sums 64 byte counters with dp4a
-            const int bin = ftid & 63, part = ftid >> 6;   // P_NF / 64 parts of 64 byte counters each
-            const uint32_t* w = reinterpret_cast<const uint32_t*>(&sel->cnt8[bin][part * 64]);
-            unsigned t = 0;
+        FinIv fi;
+        fi.iv = 0;
+        fi.kA = 0;
+        fi.ish = 0;
+        fi.j0 = fi.j1 = -1;
+        fi.rho0 = fi.rho1 = 0;
 #pragma unroll
-            for (int x = 0; x < 16; ++x) t = __dp4a(w[x], 0x01010101u, t);
-            sel->part[part][bin] = t;
-        }
-        fin_sync();
-        if (fwarp < nq && sel->act[fwarp] == 1 && qiv[fwarp] == i && lane == 0) {
-            const int j = fwarp;   // lane 0 of warp j walks the 64 totals
-            const unsigned rho = sel->rho[j];
-            unsigned cum = 0;
-            int b = 0;
-            for (; b < 63; ++b) {
-                unsigned h = 0;
-#pragma unroll
-                for (int pt = 0; pt < P_NF / 64; ++pt) h += sel->part[pt][b];
-                if (cum + h >= rho) break;
-                cum += h;
+        for (int i = 0; i < P_NI; ++i)
+            if (ord[i] == grp) {
+                fi.iv = i;
+                fi.kA = kA[i];
+                fi.ish = ish[i];
             }
-            unsigned h = 0;
 #pragma unroll
-            for (int pt = 0; pt < P_NF / 64; ++pt) h += sel->part[pt][b];
-            const unsigned long long lo = kA + ((unsigned long long)b << ish);
-            unsigned long long hi = lo + (1ull << ish);
-            if (hi > sel->ikB[i] || hi < lo) hi = sel->ikB[i];
-            sel->lo[j] = lo;
-            sel->hi[j] = hi;
-            sel->rho[j] = rho - cum;
-            if (h > (unsigned)P_LIST) sel->fail = 1;   // a heavy tie group: leave it to the slow path
-        }
-        fin_sync();
-        if (sel->fail) return false;
-        // ---- scan 2: collect the candidates of each quantile's sub-bracket (at most two quantiles per interval
-        // on the fast path; a third one sharing the interval was rejected by the planner)
-        {
-            int j0 = -1, j1 = -1;
-#pragma unroll
-            for (int j = 0; j < NI_MAX; ++j)
-                if ((j < nq) && sel->act[j] == 1 && qiv[j] == i) {
-                    if (j0 < 0) j0 = j; else j1 = j;
+        for (int j = 0; j < NI_MAX; ++j)
+            if (act_iv[j] >= 0 && act_iv[j] == fi.iv) {
+                if (fi.j0 < 0) {
+                    fi.j0 = j;
+                    fi.rho0 = rho[j];
+                } else {
+                    fi.j1 = j;
+                    fi.rho1 = rho[j];
                 }
-            const unsigned b0 = (unsigned)((sel->lo[j0 < 0 ? 0 : j0] - kA) >> ish);
-            const unsigned b1 = j1 >= 0 ? (unsigned)((sel->lo[j1] - kA) >> ish) : 0xFFFFFFFFu;
-            const uint32_t cnt0 = smem_u32(&sel->list_cnt[j0 < 0 ? 0 : j0]), cnt1 = smem_u32(&sel->list_cnt[j1 < 0 ? 0 : j1]);
-            const uint32_t l0 = smem_u32(&sel->list[j0 < 0 ? 0 : j0][0]), l1 = smem_u32(&sel->list[j1 < 0 ? 0 : j1][0]);
-            pipe_for_each(pool, ovq, pp, res, i, ftid, [&](double xv) {
-                const unsigned long long k = ko_okey(xv + 0.0);
-                const unsigned b = (unsigned)((k - kA) >> ish);
-                if (b == b0) {
-                    unsigned pos;
-                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt0) : "memory");
-                    if (pos < (unsigned)P_LIST) asm volatile("st.shared.u64 [%0], %1;" ::"r"(l0 + pos * 8u), "l"(k) : "memory");
-                }
-                if (b == b1) {
-                    unsigned pos;
-                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt1) : "memory");
-                    if (pos < (unsigned)P_LIST) asm volatile("st.shared.u64 [%0], %1;" ::"r"(l1 + pos * 8u), "l"(k) : "memory");
-                }
-            });
-        }
-        fin_sync();
-        KO_FT(15);
-        // ---- exact order statistic inside each short list: one warp per quantile, rank counting
-        if (fwarp < nq && sel->act[fwarp] == 1 && qiv[fwarp] == i) {
-            const int j = fwarp;
-            const int n = (int)min(sel->list_cnt[j], (unsigned)P_LIST);
-            const unsigned rho = sel->rho[j];
-            const uint32_t l32 = smem_u32(&sel->list[j][0]);
-            for (int idx = lane; idx < n; idx += 32) {
-                unsigned long long e;
-                asm volatile("ld.shared.u64 %0, [%1];" : "=l"(e) : "r"(l32 + (uint32_t)idx * 8u));
-                unsigned lt = 0, le = 0;
-                for (int m = 0; m < n; ++m) {
-                    unsigned long long v;
-                    asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(l32 + (uint32_t)m * 8u));
-                    lt += (v < e) ? 1u : 0u;
-                    le += (v <= e) ? 1u : 0u;
-                }
-                if (lt < rho && rho <= le) sel->val[j] = ko_key2d(e);   // all writers hold the same value
             }
-        }
-        fin_sync();   // the lists alias the counters of the next interval
+        const uint32_t pool32 = smem_u32(pool), ovq32 = smem_u32(ovq);
+        if (ncapi == 1) fin_groups<1>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+        else if (ncapi == 2) fin_groups<2>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+        else fin_groups<3>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
     }
+    KO_FT(14);
     fin_sync();
     KO_FT(7);
     if (ftid == 0) {
-        const int sid = pp->sid;
-        const unsigned n = sel->nvalid;
-        if (a.out_sum) a.out_sum[sid] = sel->sum;
-        if (a.out_mean) a.out_mean[sid] = n > 0 ? sel->sum / (double)n : 0.0;
-        if (a.out_min) a.out_min[sid] = n > 0 ? sel->mn + 0.0 : nan;
-        if (a.out_max) a.out_max[sid] = n > 0 ? sel->mx + 0.0 : nan;
-        if (a.out_last) a.out_last[sid] = pp->last;
-        if (a.out_count) a.out_count[sid] = (int64_t)n;
-        if (a.out_quant) {
+        failmask |= sel->fail;
+        double out[NI_MAX];
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            out[j] = act_iv[j] >= 0 ? sel->val[j] : dval[j];
+            if (act_iv[j] >= 0 && !(out[j] == out[j])) failmask |= 1 << j;   // no candidate carried the rank
+        }
+        if (a.out_quant) {   // the quantiles that failed are written by a later attempt
+            const int sid = pp->sid;
 #pragma unroll
             for (int j = 0; j < NI_MAX; ++j)
-                if (j < nq) a.out_quant[(int64_t)sid * nq + a.qcol[j]] = sel->val[j];
+                if (j < nq && (qsel < 0 || j == qsel) && !((failmask >> j) & 1))
+                    a.out_quant[(int64_t)sid * nq + a.qcol[j]] = out[j];
         }
     }
-    return true;
+    return failmask;
 }
 
 // Finish of a levels plan: total the per-thread gap counters, then every rank must fall on a listed level, i.e.
 // (#valid samples < v) < rank <= (#valid samples <= v); otherwise the series goes to the slow path.
-__device__ __noinline__ bool pipe_finish_levels(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
+__device__ __noinline__ int pipe_finish_levels(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
                                                 const unsigned char* pool, int ftid, int fwarp, int lane) {
     const int nq = a.nq;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
@@ -2498,7 +2573,7 @@ __device__ __noinline__ bool pipe_finish_levels(const SeriesArgs& a, const PipeP
             t += (w & 0xFFFFu) + (w >> 16);
         }
         t = warp_sum_u(t);
-        if (lane == 0) sel->part[0][b] = t;
+        if (lane == 0) sel->tot[0][b] = t;
     }
     fin_sync();
     if (ftid == 0) {
@@ -2508,37 +2583,37 @@ __device__ __noinline__ bool pipe_finish_levels(const SeriesArgs& a, const PipeP
             s += res->sum[w];
             mn = fmin(mn, res->mn[w]);
             mx = fmax(mx, res->mx[w]);
-            n += res->nvalid[w];
         }
+        n = res->t_nvalid;
         unsigned tot = 0;
-        for (int b = 0; b <= P_NTHR; ++b) tot += sel->part[0][b];
+        for (int b = 0; b <= P_NTHR; ++b) tot += sel->tot[0][b];
         // stale samples (and the padding of the last tile) all sit in gap 0
-        unsigned cum = sel->part[0][0] - (tot - n);   // valid samples below thr[0]
+        unsigned cum = sel->tot[0][0] - (tot - n);   // valid samples below thr[0]
         int fail = 0;
         unsigned rk[NI_MAX];
         double val[NI_MAX];
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) {
-            rk[j] = (j < nq && n > 0) ? nearest_rank_dev(n, a.q[j]) : 0u;
+            rk[j] = (j < nq && n > 0 && (pp->qsel < 0 || j == pp->qsel)) ? nearest_rank_dev(n, a.q[j]) : 0u;
             val[j] = nan;
         }
         const int nlev = pp->nlev;
         for (int d = 0; d < nlev; ++d) {
             const unsigned below = cum;                       // < v_d
-            const unsigned upto = cum + sel->part[0][2 * d + 1];   // <= v_d
+            const unsigned upto = cum + sel->tot[0][2 * d + 1];   // <= v_d
 #pragma unroll
             for (int j = 0; j < NI_MAX; ++j)
                 if (rk[j] > below && rk[j] <= upto) {
                     val[j] = pp->thr[2 * d];
                     rk[j] = 0u;
                 }
-            cum = upto + sel->part[0][2 * d + 2];             // < v_{d+1}
+            cum = upto + sel->tot[0][2 * d + 2];             // < v_{d+1}
         }
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j)
-            if (rk[j] != 0u) fail = 1;
+            if (rk[j] != 0u) fail |= 1 << j;   // the rank fell on a value that is not listed
         sel->fail = fail;
-        if (!fail) {
+        {
             const int sid = pp->sid;
             if (a.out_sum) a.out_sum[sid] = s;
             if (a.out_mean) a.out_mean[sid] = n > 0 ? s / (double)n : 0.0;
@@ -2549,12 +2624,13 @@ __device__ __noinline__ bool pipe_finish_levels(const SeriesArgs& a, const PipeP
             if (a.out_quant) {
 #pragma unroll
                 for (int j = 0; j < NI_MAX; ++j)
-                    if (j < nq) a.out_quant[(int64_t)sid * nq + a.qcol[j]] = val[j];
+                    if (j < nq && (pp->qsel < 0 || j == pp->qsel) && !((fail >> j) & 1))
+                        a.out_quant[(int64_t)sid * nq + a.qcol[j]] = val[j];
             }
         }
     }
     fin_sync();
-    return sel->fail == 0;
+    return sel->fail;
 }
 
 // ------------------------------------------------------------------------------------------ kernel
@@ -2575,20 +2651,34 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
         for (int s = 0; s < 2; ++s) {
             mbar_init(sm.bars() + B_POOL_FULL + s, P_SW);
             mbar_init(sm.bars() + B_POOL_FREE + s, 1);
-            for (int i = 0; i < P_NI; ++i) sm.res(s)->ovcnt[i] = 0;
+            PipeResult* r0 = sm.res(s);
+            r0->t_nvalid = 0;
+            for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
+        }
+        {
+            PipeSel* sl = sm.sel();
+            sl->fail = 0;
+            for (int j = 0; j < NI_MAX; ++j) {
+                sl->list_cnt[j] = 0;
+                sl->val[j] = __longlong_as_double(0x7FF8000000000000LL);
+            }
         }
         mbar_fence_init();
     }
+    {   // the finish warps' byte counters start (and are left) zero
+        uint32_t* w = reinterpret_cast<uint32_t*>(&sm.sel()->cnt8[0][0]);
+        for (int t = tid; t < 64 * P_CROW / 4; t += P_THREADS) w[t] = 0;
+    }
     __syncthreads();
-    const int n_long = a.counters[0];
+    const long long n_long = (long long)a.counters[a.work_cnt] * (a.wide ? a.nq : 1);
 
     if (warp < P_PW) {
         // ================================================================ PLANNERS
         // Series are dealt to the CTAs round-robin (ordinal k of this CTA is long_list[blockIdx.x + k*gridDim.x]);
         // planner warp p prepares the ordinals k = p, p + P_PW, ...
         for (uint32_t k = (uint32_t)warp;; k += P_PW) {
-            const uint32_t slot = k & 3u;
-            mbar_wait_sleep(sm.bars() + B_PLAN_FREE + slot, ((k >> 2) & 1u) ^ 1u);
+            const uint32_t slot = k & (P_PLANS - 1);
+            mbar_wait_sleep(sm.bars() + B_PLAN_FREE + slot, ((k >> P_PLAN_LOG) & 1u) ^ 1u);
             const long long w = (long long)blockIdx.x + (long long)k * gridDim.x;
             PipePlan* pp = sm.plan(slot);
             if (w >= n_long) {
@@ -2597,7 +2687,24 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
                 break;
             }
-            { KO_PT0(); planner_build(pp, a, a.long_list[w], lane); KO_PT1(8, lane == 0); }
+            {
+                KO_PT0();
+                const int item = a.wide ? (int)(w / a.nq) : (int)w;
+                const int qsel = a.wide ? (int)(w - (long long)item * a.nq) : -1;
+                const int entry = a.work_list[item];
+                const bool packed = a.wide && a.pack;
+                const int sid = packed ? (entry & 0x07FFFFFF) : (entry & 0x7FFFFFFF);
+                if (packed && !((entry >> (27 + qsel)) & 1)) {   // this quantile was answered by the first attempt
+                    if (lane == 0) {
+                        pp->sid = sid;
+                        pp->defer = 2;
+                    }
+                    __syncwarp();
+                } else {
+                    planner_build(pp, a, sid, qsel, item, lane);
+                }
+                KO_PT1(8, lane == 0);
+            }
             if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
         }
     } else if (warp == P_PW) {
@@ -2605,8 +2712,8 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
         if (lane == 0) {
             uint32_t g = 0;
             for (uint32_t k = 0;; ++k) {
-                const uint32_t slot = k & 3u;
-                mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> 2) & 1u);
+                const uint32_t slot = k & (P_PLANS - 1);
+                mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> P_PLAN_LOG) & 1u);
                 const PipePlan* pp = sm.plan(slot);
                 if (pp->sid < 0) break;
                 if (!pp->defer) {
@@ -2632,8 +2739,8 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
         const int swarp = warp - (P_PW + 1);
         uint32_t g = 0, c = 0;
         for (uint32_t k = 0;; ++k) {
-            const uint32_t slot = k & 3u;
-            { KO_PT0(); mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> 2) & 1u); KO_PT1(11, stid == 0); }
+            const uint32_t slot = k & (P_PLANS - 1);
+            { KO_PT0(); mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> P_PLAN_LOG) & 1u); KO_PT1(11, stid == 0); }
             const PipePlan* pp = sm.plan(slot);
             if (pp->sid < 0) break;
             if (!pp->defer) {
@@ -2682,19 +2789,25 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 const unsigned wn = warp_sum_u(acc.nvalid);
                 const unsigned ca0 = warp_sum_u(acc.cA[0]), ca1 = warp_sum_u(acc.cA[1]);
                 const unsigned ci0 = warp_sum_u(acc.cin[0]), ci1 = warp_sum_u(acc.cin[1]);
+                unsigned pc[P_NI], wpc[P_NI];
+#pragma unroll
+                for (int i = 0; i < P_NI; ++i) {
+                    pc[i] = (acc.p[i] - p0[i]) / (P_NS * 8);
+                    wpc[i] = warp_sum_u(pc[i]);
+                    res->pcount[i][stid] = (unsigned short)pc[i];
+                }
                 if (lane == 0) {
                     res->sum[swarp] = ws;
                     res->mn[swarp] = wmn;
                     res->mx[swarp] = wmx;
-                    res->nvalid[swarp] = wn;
-                    res->cA[swarp][0] = ca0;
-                    res->cA[swarp][1] = ca1;
-                    res->cin[swarp][0] = ci0;
-                    res->cin[swarp][1] = ci1;
-                }
+                    red_shared_add(&res->t_nvalid, wn);
+                    red_shared_add(&res->t_cA[0], ca0);
+                    red_shared_add(&res->t_cA[1], ca1);
+                    red_shared_add(&res->t_cin[0], ci0);
+                    red_shared_add(&res->t_cin[1], ci1);
 #pragma unroll
-                for (int i = 0; i < P_NI; ++i)
-                    res->pcount[i][stid] = (unsigned short)((acc.p[i] - p0[i]) / (P_NS * 8));
+                    for (int i = 0; i < P_NI; ++i) red_shared_add(&res->t_ncap[i], wpc[i]);
+                }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(sm.bars() + B_POOL_FULL + pool);
                 ++c;
@@ -2707,27 +2820,41 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
         const int ftid = tid - (P_PW + 1) * 32 - P_NS, fwarp = warp - (P_PW + 1) - P_SW;
         uint32_t c = 0;
         for (uint32_t k = 0;; ++k) {
-            const uint32_t slot = k & 3u;
-            mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> 2) & 1u);
+            const uint32_t slot = k & (P_PLANS - 1);
+            mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> P_PLAN_LOG) & 1u);
             const PipePlan* pp = sm.plan(slot);
             if (pp->sid < 0) break;
-            bool ok = false;
+            int todo = 0;   // quantiles left for a later attempt
+            if (pp->defer == 1) todo = pp->qsel < 0 ? (a.nq > 0 ? (1 << a.nq) - 1 : 1) : (1 << pp->qsel);
             if (!pp->defer) {
                 const uint32_t pool = c & 1u;
                 { KO_PT0(); mbar_wait_sleep(sm.bars() + B_POOL_FULL + pool, (c >> 1) & 1u); KO_PT1(12, ftid == 0); }
-                { KO_PT0(); ok = pp->vals ? pipe_finish_levels(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), ftid, fwarp, lane)
+                { KO_PT0(); todo = pp->vals ? pipe_finish_levels(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), ftid, fwarp, lane)
                                           : pipe_finish(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), sm.ovq(pool), ftid, fwarp, lane); KO_PT1(10, ftid == 0); }
                 fin_sync();
                 if (ftid == 0) {
-                    for (int i = 0; i < P_NI; ++i) sm.res(pool)->ovcnt[i] = 0;
+                    PipeResult* r0 = sm.res(pool);
+                    PipeSel* sl = sm.sel();
+                    r0->t_nvalid = 0;
+                    for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
+                    sl->fail = 0;
+                    for (int j = 0; j < NI_MAX; ++j) {
+                        sl->list_cnt[j] = 0;
+                        sl->val[j] = __longlong_as_double(0x7FF8000000000000LL);
+                    }
                     mbar_arrive(sm.bars() + B_POOL_FREE + pool);
                 }
                 ++c;
             }
             if (ftid == 0) {
-                if (!ok) {  // exact slow path afterwards
-                    const int pos = atomicAdd(&a.counters[4], 1);
-                    a.defer_list[pos] = pp->sid;
+                if (todo) {  // next attempt: wide brackets per quantile, then the exact slow path
+                    bool first = true;
+                    if (a.wide)   // several quantiles of one series may fail: list it once
+                        first = (atomicOr(const_cast<int*>(&a.work_list[pp->item]), (int)0x80000000) >= 0);
+                    if (first) {
+                        const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
+                        a.out_list[pos] = (!a.wide && a.pack) ? (pp->sid | (todo << 27)) : pp->sid;
+                    }
                 }
             }
             fin_sync();
@@ -2738,6 +2865,42 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
 
 
 bool g_attr_done = false;
+
+// The kernels of the long-series path, enqueued on `st`:
+//   1. series_pipe over every long series (fast path: one pass per series);
+//   2. series_pipe again over what step 1 could not finish, one work item per (series, quantile), with brackets
+//      twice as wide -- a bracket that missed its rank (about one series in a thousand) is settled here;
+//   3. series_long, the exact multi-pass slow path, over what is still left (heavy tie groups that fit neither
+//      the capture slots nor a levels plan, series with almost no valid samples).
+static void launch_long_path(SeriesArgs a, int num_sms, int64_t n_series, cudaStream_t st) {
+    int pgrid = num_sms;
+    if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
+    int grid = 2 * num_sms;
+    if ((int64_t)grid > n_series) grid = (int)n_series;
+    a.pack = n_series < (1LL << 27) ? 1 : 0;
+    a.work_list = a.long_list;
+    a.work_cnt = 0;
+    a.work_cur = 1;
+    a.out_list = a.defer_list;
+    a.out_cnt = 4;
+    a.wide = 0;
+    series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+    if (a.nq > 0) {
+        a.work_list = a.defer_list;
+        a.work_cnt = 4;
+        a.out_list = a.long_list;   // the first list is no longer needed
+        a.out_cnt = 6;
+        a.wide = 1;
+        series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+        a.work_list = a.long_list;
+        a.work_cnt = 6;
+    } else {
+        a.work_list = a.defer_list;
+        a.work_cnt = 4;
+    }
+    a.work_cur = 7;
+    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
+}
 
 }  // namespace
 
@@ -2761,7 +2924,6 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     a.counters = d_scratch;
     a.long_list = d_scratch + 8;
     a.defer_list = d_scratch + 8 + n_series;
-    a.fb = 0;
     a.nq = nq;
     // quantiles ascending (stable insertion sort), remembering the caller's column
     for (int j = 0; j < NI_MAX; ++j) {
@@ -2793,18 +2955,12 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     classify_series<<<(unsigned)((n_series + cb - 1) / cb), cb, 0, stream>>>(a);
     const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
     series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, stream>>>(a);
-    int pgrid = ctx->num_sms;
-    if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
-    int grid = 2 * ctx->num_sms;
-    if ((int64_t)grid > n_series) grid = (int)n_series;
     KO_CUDA(cudaEventRecord(ctx->ev_k0, stream));
-    series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, stream>>>(a);   // fast path
-    a.fb = 1;
-    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, stream>>>(a);     // exact slow path over the deferred series
+    launch_long_path(a, ctx->num_sms, n_series, stream);
     KO_CUDA(cudaEventRecord(ctx->ev_k1, stream));
     ctx->k_timed = true;
     KO_CUDA(cudaGetLastError());
-    ctx->counters.kernel_launches += 4;
+    ctx->counters.kernel_launches += nq > 0 ? 5 : 4;
     return KO_OK;
 }
 
@@ -3035,7 +3191,6 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     a.counters = sd->scratch;
     a.long_list = sd->scratch + 8;
     a.defer_list = sd->scratch + 8 + n_series;
-    a.fb = 0;
     a.nq = nq;
     for (int j = 0; j < NI_MAX; ++j) {
         a.q[j] = 0.0;
@@ -3058,13 +3213,7 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     classify_series<<<(unsigned)((n_series + 255) / 256), 256, 0, st>>>(a);
     const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
     series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, st>>>(a);
-    int pgrid = sd->num_sms;
-    if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
-    int grid = 2 * sd->num_sms;
-    if ((int64_t)grid > n_series) grid = (int)n_series;
-    series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
-    a.fb = 1;
-    series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
+    launch_long_path(a, sd->num_sms, n_series, st);
     KO_CUDA(cudaGetLastError());
     return KO_OK;
 }

@@ -28,7 +28,7 @@ for qs in ([], [0.5], [0.5, 0.95, 0.99]):
     tot = sum(buf[:7])
     print("qs=%s kernel_ms=%.3f CTA0 cycles total=%d (%.1f us at 1.9GHz)" % (qs, ms, tot, tot / 1900.0))
     print("   " + "  ".join("%s=%.1f%%(%.1fus)" % (nm, 100.0 * buf[i] / max(tot, 1), buf[i] / 1900.0) for i, nm in enumerate(names)))
-    print("   finish parts (us): decide=%.1f scan1=%.1f digit+compact=%.1f warp_select=%.1f" % tuple(buf[i] / 1900.0 for i in (13, 14, 15, 7)))
+    print("   finish parts (us): prologue=%.1f groups=%.1f final_sync=%.1f | scan1=%.1f totals=%.1f walk+zero=%.1f scan2=%.1f rank=%.1f" % tuple(buf[i] / 1900.0 for i in (13, 14, 7, 24, 25, 26, 27, 28)))
     print("   for_each calls=%d max nmax=%d" % (buf[23], buf[22]))
     print("   for_each loops: %.1f us total, %d iterations -> %.0f cycles/iteration" % (buf[20] / 1900.0, buf[21], buf[20] / max(buf[21], 1)))
     print("   pipe CTA0 (us): planner=%.1f stream=%.1f finish=%.1f stream_wait_plan=%.1f finish_wait_pool=%.1f" % tuple(buf[i] / 1900.0 for i in (8, 9, 10, 11, 12)))
