@@ -981,7 +981,8 @@ __device__ void build_refine_plan(Plan* pl, int nq, const unsigned long long* nk
 }
 
 #ifdef KO_PHASE_TIMING
-__device__ unsigned long long g_phase[32];
+__device__ unsigned long long g_phase[48];
+#define KO_COUNT(reason, wide) atomicAdd(&g_phase[32 + (reason) + ((wide) ? 8 : 0)], 1ull)
 #define KO_TICK(slot)                                                   \
     do {                                                                \
         if (blockIdx.x == 0 && threadIdx.x == 0) {                      \
@@ -992,6 +993,7 @@ __device__ unsigned long long g_phase[32];
     } while (0)
 #else
 #define KO_TICK(slot) do { } while (0)
+#define KO_COUNT(reason, wide) do { } while (0)
 #endif
 
 template <int KPT>
@@ -1403,7 +1405,6 @@ struct PipePlan {
     int ni, nb, tail;        // intervals: nb brackets first, then the optional upper tail
     int mode[P_NI];
     int slot0[P_NI], nslots[P_NI];
-    int ov0[P_NI], ovcap[P_NI];
     unsigned long long kA[P_NI], kB[P_NI];
     double tA[P_NI], tB[P_NI];
     int q_iv[NI_MAX];
@@ -1421,7 +1422,9 @@ struct PipeResult {          // what the stream warps hand to the finish warps, 
     double sum[P_SW], mn[P_SW], mx[P_SW];          // per stream warp (summed in warp order: reproducible)
     // totals over all stream warps, added with shared-memory reductions, cleared by the finish warps
     unsigned t_nvalid, t_cA[P_NI], t_cin[P_NI], t_ncap[P_NI];
-    unsigned ovcnt[P_NI];
+    unsigned ovcnt[P_NI];                // captures that found the thread's private slots full, per interval
+    unsigned ovn;                        // ... and in total: entries claimed in the shared overflow queue
+    unsigned char ovtag[P_OVQ];          // interval of each overflow queue entry
     unsigned short pcount[P_NI][P_NS];   // captured entries per stream thread
     double trash;                        // sink of captures that find slots and queue full
 };
@@ -1436,6 +1439,7 @@ struct PipeSel {             // scratch of the finish warps
     unsigned list_cnt[NI_MAX];
     int bin[NI_MAX];                           // chosen sub-bracket per quantile
     unsigned rho[NI_MAX];                      // rank inside it
+    unsigned nlist[NI_MAX];                    // candidates inside it
     int fail;
     double val[NI_MAX];
 };
@@ -1642,7 +1646,10 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         }
         const int valid_s = nv;
         planner_sort(r, lane);
-        if (valid_s < 64) defer = 1;  // too few valid samples to bracket: leave it to the exact slow path
+        if (valid_s < 64) {
+            defer = 1;  // too few valid samples to bracket: leave it to the exact slow path
+            if (lane == 0) KO_COUNT(0, a.wide);
+        }
         if (!defer) {   // the sample's extremes seed the running min / max of the stream warps
             const unsigned p0 = planner_at(r, 0, lane), p1 = planner_at(r, valid_s - 1, lane);
             if (lane == 0) {
@@ -1671,6 +1678,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                     ni++;
                 } else {
                     defer = 1;
+                    if (lane == 0) KO_COUNT(1, a.wide);
                 }
                 lo.set(ni - 1, cur_lo);
                 hi.set(ni - 1, cur_hi);
@@ -1774,6 +1782,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
             __syncwarp();
             if (nlev < 1 || nlev > P_LEVELS || L > P_MAX_L_LEVELS) {
                 defer = soft;   // too many levels: capture plan if that fits, else slow path
+                if (soft && lane == 0) KO_COUNT(2, a.wide);
             } else {
                 const double xv = (lane < nlev) ? v[sample_pos(pp->vidx[lane], L)] : 0.0;
                 const unsigned long long key = ko_okey(xv + 0.0);
@@ -1792,7 +1801,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
             }
         }
         if (!defer && !vals && lane == 0) {
-            int slot = 0, k = 0;
+            int slot = 0;
             const int spare = P_SLOTS - total;
 #pragma unroll
             for (int i = 0; i < P_NI; ++i) {
@@ -1804,14 +1813,9 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                     pp->tB[i] = ko_key2d(kB[i] > KO_KEY_PINF ? KO_KEY_PINF : kB[i]);
                     pp->slot0[i] = slot;
                     pp->nslots[i] = 0;
-                    pp->ov0[i] = 0;
-                    pp->ovcap[i] = 0;
                     if (mode[i] == M_CAPTURE) {
                         pp->nslots[i] = need[i] + spare / ncap;
                         slot += pp->nslots[i];
-                        pp->ov0[i] = k * (P_OVQ / ncap);
-                        pp->ovcap[i] = P_OVQ / ncap;
-                        k++;
                     }
                 }
             }
@@ -1854,10 +1858,19 @@ struct PStreamCtx {
     uint32_t pool32;       // shared address of this series' pool
     uint32_t ovq32;        // shared address of its overflow queue
     uint32_t ovcnt32;      // shared address of PipeResult::ovcnt
+    uint32_t ovn32;        // ... of PipeResult::ovn
+    uint32_t ovtag32;      // ... of PipeResult::ovtag
     uint32_t trash32;
-    int ov0[P_NI], ovcap[P_NI];
 };
 
+__device__ __forceinline__ unsigned lds_u8(uint32_t addr) {
+    unsigned c;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
+    return c;
+}
+__device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+}
 // Store x into the thread's next private slot of interval i; when the slots are full (a few per cent of the
 // captures) claim an entry of the overflow queue with a shared-memory atomic.
 __device__ __forceinline__ void pipe_capture(const PStreamCtx& c, uint32_t& p, uint32_t pend, int i, double x,
@@ -1868,8 +1881,13 @@ __device__ __forceinline__ void pipe_capture(const PStreamCtx& c, uint32_t& p, u
         p += P_NS * 8;
     } else {
         unsigned pos;
-        asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(c.ovcnt32 + 4u * i) : "memory");
-        addr = (pos < (unsigned)c.ovcap[i]) ? c.ovq32 + (uint32_t)(c.ov0[i] + pos) * 8u : c.trash32;
+        asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(c.ovn32) : "memory");
+        asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(c.ovcnt32 + 4u * i) : "memory");
+        addr = c.trash32;
+        if (pos < (unsigned)P_OVQ) {
+            addr = c.ovq32 + pos * 8u;
+            sts_u8(c.ovtag32 + pos, (unsigned)i);
+        }
     }
     sts_f64(addr, x);
 }
@@ -2182,14 +2200,6 @@ __device__ __noinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc, u
 // group per interval, each group synchronising on its own named barrier.  Everything the groups need to agree on
 // before that (valid count, ranks, which bracket holds which rank) is computed redundantly by every thread from
 // the totals the stream warps left in PipeResult, so no barrier precedes the first scan.
-__device__ __forceinline__ unsigned lds_u8(uint32_t addr) {
-    unsigned c;
-    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
-    return c;
-}
-__device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
-    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
-}
 __device__ __forceinline__ unsigned lds_u32(uint32_t addr) {
     unsigned c;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
@@ -2250,64 +2260,43 @@ __device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, co
             frow(x0, s < n0, x1, s < n1);
         }
     }
-    const int ovn = (int)min(res->ovcnt[iv], (unsigned)pp->ovcap[iv]);
-    const uint32_t ov32 = ovq32 + (uint32_t)pp->ov0[iv] * 8u;
-    for (int q = gt; q < ovn; q += G) fone(lds_f64(ov32 + (uint32_t)q * 8u));
+    // the overflow queue is shared by the intervals of the series: entries carry their interval as a tag
+    const int ovn = (int)min(res->ovn, (unsigned)P_OVQ);
+    const uint32_t tag32 = smem_u32(&res->ovtag[0]);
+    for (int q = gt; q < ovn; q += G)
+        if ((int)lds_u8(tag32 + (uint32_t)q) == iv) fone(lds_f64(ovq32 + (uint32_t)q * 8u));
 }
 
 // The group phase: NG capturing intervals, G = P_NF / NG threads each.  `use` is uniform inside a group.
+//
+// Per wanted rank the candidates are narrowed to one of 64 sub-brackets by counting; a sub-bracket that still
+// holds more than P_LIST candidates (skewed data, heavy tie groups) is cut into 64 again, until the candidates
+// fit the list or the sub-bracket is a single key (then that key is the answer).
 template <int NG>
 __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult* res, PipeSel* sel, uint32_t pool32,
                                            uint32_t ovq32, const FinIv& fi, int grp, int gt, int ftid) {
     constexpr int G = P_NF / NG;
     constexpr int GW = G / 4;            // 32-bit words of one sub-bracket's counters inside the group
     const bool use = fi.j0 >= 0;
-    const unsigned long long kA = fi.kA;
-    const int ish = fi.ish;
     const uint32_t cnt32 = smem_u32(&sel->cnt8[0][0]);
+    const uint32_t col = cnt32 + (uint32_t)ftid;
+    const uint32_t dummy = smem_u32(&sel->dummy[0][0]) + (uint32_t)ftid;
 #ifdef KO_PHASE_TIMING
     unsigned long long _ft = clock64();
 #endif
-    // ---- scan 1: private byte counters per sub-bracket (zero on entry)
-    if (use) {
-        const uint32_t col = cnt32 + (uint32_t)ftid;
-        const uint32_t dummy = smem_u32(&sel->dummy[0][0]) + (uint32_t)ftid;
-        auto addr_of = [&](double xv, bool valid, int which) -> uint32_t {
-            const unsigned long long k = ko_okey(xv + 0.0);
-            return valid ? col + (uint32_t)((k - kA) >> ish) * (uint32_t)P_CROW : dummy + (uint32_t)which * P_NF;
-        };
-        fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
-                         [&](double x0, bool v0, double x1, bool v1) {
-                             const uint32_t a0 = addr_of(x0, v0, 0), a1 = addr_of(x1, v1, 1);
-                             if (a0 == a1) {   // both samples in one sub-bracket: one after the other
-                                 sts_u8(a0, lds_u8(a0) + 1);
-                                 sts_u8(a1, lds_u8(a1) + 1);
-                             } else {
-                                 const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1);
-                                 sts_u8(a0, c0 + 1);
-                                 sts_u8(a1, c1 + 1);
-                             }
-                         },
-                         [&](double xv) {
-                             const uint32_t a0 = addr_of(xv, true, 0);
-                             sts_u8(a0, lds_u8(a0) + 1);
-                         });
-    }
-    group_sync(grp, G);
-    KO_FT(24);
-    // ---- totals per sub-bracket: thread b sums the group's byte counters of sub-bracket b with dp4a
-    if (use && gt < 64) {
-        const uint32_t w = cnt32 + (uint32_t)(gt * P_CROW + grp * G);
-        unsigned t = 0;
+    // totals of the group's byte counters per sub-bracket (thread b sums sub-bracket b with dp4a), then, with the
+    // counters dead, clear them for the next use while the group's first warp finds the sub-bracket of each
+    // wanted rank by a scan over the 64 totals (two per lane).  Three group barriers.
+    auto totals_and_walk = [&](int ja, unsigned rhoa, int jb, unsigned rhob) {
+        group_sync(grp, G);
+        if (gt < 64) {
+            const uint32_t w = cnt32 + (uint32_t)(gt * P_CROW + grp * G);
+            unsigned t = 0;
 #pragma unroll 8
-        for (int x = 0; x < GW; ++x) t = __dp4a(lds_u32(w + 4u * x), 0x01010101u, t);
-        sel->tot[grp][gt] = t;
-    }
-    group_sync(grp, G);
-    KO_FT(25);
-    // ---- the counters are dead: clear them for the next series; meanwhile the group's first warp finds the
-    // sub-bracket of each wanted rank with a scan over the 64 totals (two per lane)
-    if (use) {
+            for (int x = 0; x < GW; ++x) t = __dp4a(lds_u32(w + 4u * x), 0x01010101u, t);
+            sel->tot[grp][gt] = t;
+        }
+        group_sync(grp, G);
 #pragma unroll
         for (int t = 0; t < 16; ++t) {
             const int idx = gt + t * G;            // 64 * GW words, G threads
@@ -2327,8 +2316,8 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
             const unsigned excl = incl - s;
 #pragma unroll
             for (int jj = 0; jj < 2; ++jj) {
-                const int j = jj ? fi.j1 : fi.j0;
-                const unsigned rho = jj ? fi.rho1 : fi.rho0;
+                const int j = jj ? jb : ja;
+                const unsigned rho = jj ? rhob : rhoa;
                 if (j >= 0) {
                     const bool m0 = excl < rho && rho <= excl + h0;
                     const bool m1 = excl + h0 < rho && rho <= incl;
@@ -2336,50 +2325,121 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                     if (m0 || m1) {
                         sel->bin[j] = 2 * lane + (m1 ? 1 : 0);
                         sel->rho[j] = rho - (m1 ? excl + h0 : excl);
-                        if ((m1 ? h1 : h0) > (unsigned)P_LIST) atomicOr(&sel->fail, 1 << j);   // a heavy tie group
+                        sel->nlist[j] = m1 ? h1 : h0;
                     }
-                    if (hit == 0u && lane == 0) atomicOr(&sel->fail, 1 << j);
+                    if (hit == 0u && lane == 0) {   // cannot happen while the counts are consistent
+                        atomicOr(&sel->fail, 1 << j);
+                        sel->bin[j] = 0;
+                        sel->nlist[j] = 0;
+                        KO_COUNT(5, 0);
+                    }
                 }
             }
         }
-    }
-    group_sync(grp, G);
-    KO_FT(26);
-    // ---- scan 2: collect the candidates of each wanted sub-bracket (at most two ranks per interval)
+        group_sync(grp, G);
+    };
+    unsigned long long lo[2] = {0, 0};   // sub-bracket [lo, lo + 2^sh) of each wanted rank
+    int sh[2] = {0, 0};
+    bool direct[2] = {false, false};
     if (use) {
-        const unsigned b0 = (unsigned)sel->bin[fi.j0];   // (a quantile that failed above keeps a stale but harmless bin)
-        const unsigned b1 = fi.j1 >= 0 ? (unsigned)sel->bin[fi.j1] : 0xFFFFFFFFu;
-        const uint32_t cnt0 = smem_u32(&sel->list_cnt[fi.j0]), cnt1 = smem_u32(&sel->list_cnt[fi.j1 < 0 ? 0 : fi.j1]);
-        const uint32_t l0 = smem_u32(&sel->list[fi.j0][0]), l1 = smem_u32(&sel->list[fi.j1 < 0 ? 0 : fi.j1][0]);
-        auto take = [&](double xv) {
-            const double xc = xv + 0.0;
-            const unsigned b = (unsigned)((ko_okey(xc) - kA) >> ish);
-            if (b == b0) {
-                unsigned pos;
-                asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt0) : "memory");
-                if (pos < (unsigned)P_LIST) sts_f64(l0 + pos * 8u, xc);
-            }
-            if (b == b1) {
-                unsigned pos;
-                asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt1) : "memory");
-                if (pos < (unsigned)P_LIST) sts_f64(l1 + pos * 8u, xc);
-            }
-        };
-        fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
-                         [&](double x0, bool v0, double x1, bool v1) {
-                             if (v0) take(x0);
-                             if (v1) take(x1);
-                         },
-                         take);
-    }
-    group_sync(grp, G);
-    KO_FT(27);
-    // ---- exact order statistic inside each short list by rank counting (doubles compare like their keys)
-    if (use) {
+        const unsigned long long kA = fi.kA;
+        const int ish = fi.ish;
+        // ---- first cut: private byte counters per sub-bracket (zero on entry), every candidate of the interval
+        {
+            auto addr_of = [&](double xv, bool valid, int which) -> uint32_t {
+                const unsigned long long k = ko_okey(xv + 0.0);
+                return valid ? col + (uint32_t)((k - kA) >> ish) * (uint32_t)P_CROW : dummy + (uint32_t)which * P_NF;
+            };
+            fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
+                             [&](double x0, bool v0, double x1, bool v1) {
+                                 const uint32_t a0 = addr_of(x0, v0, 0), a1 = addr_of(x1, v1, 1);
+                                 if (a0 == a1) {   // both samples in one sub-bracket: one after the other
+                                     sts_u8(a0, lds_u8(a0) + 1);
+                                     sts_u8(a1, lds_u8(a1) + 1);
+                                 } else {
+                                     const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1);
+                                     sts_u8(a0, c0 + 1);
+                                     sts_u8(a1, c1 + 1);
+                                 }
+                             },
+                             [&](double xv) {
+                                 const uint32_t a0 = addr_of(xv, true, 0);
+                                 sts_u8(a0, lds_u8(a0) + 1);
+                             });
+        }
+        KO_FT(24);
+        totals_and_walk(fi.j0, fi.rho0, fi.j1, fi.rho1);
+        KO_FT(25);
+        // ---- further cuts, one wanted rank at a time, only while its sub-bracket holds too many candidates
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
             const int j = jj ? fi.j1 : fi.j0;
-            if (j >= 0) {
+            if (j < 0) continue;
+            lo[jj] = kA + ((unsigned long long)sel->bin[j] << ish);
+            sh[jj] = ish;
+            while (sel->nlist[j] > (unsigned)P_LIST && sh[jj] > 0) {   // uniform in the group
+                const unsigned long long l0 = lo[jj];
+                const int wsh = sh[jj], bsh = wsh > 6 ? wsh - 6 : 0;
+                const unsigned rho = sel->rho[j];
+                auto bump = [&](double xv) {
+                    const unsigned long long d = ko_okey(xv + 0.0) - l0;
+                    if ((d >> wsh) == 0) {
+                        const uint32_t ad = col + (uint32_t)(d >> bsh) * (uint32_t)P_CROW;
+                        sts_u8(ad, lds_u8(ad) + 1);
+                    }
+                };
+                fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
+                                 [&](double x0, bool v0, double x1, bool v1) {
+                                     if (v0) bump(x0);
+                                     if (v1) bump(x1);
+                                 },
+                                 bump);
+                totals_and_walk(j, rho, -1, 0u);
+                lo[jj] = l0 + ((unsigned long long)sel->bin[j] << bsh);
+                sh[jj] = bsh;
+            }
+            if (sel->nlist[j] > (unsigned)P_LIST) {   // a single key holds the rank
+                direct[jj] = true;
+                if (gt == 0) sel->val[j] = ko_key2d(lo[jj]);
+            }
+        }
+        KO_FT(26);
+        // ---- collect the candidates of each wanted sub-bracket (at most two ranks per interval)
+        {
+            const int ja = direct[0] ? -1 : fi.j0, jb = direct[1] ? -1 : fi.j1;
+            const unsigned long long la = lo[0], lb = lo[1];
+            const int sa = sh[0], sb = sh[1];
+            const uint32_t cnt0 = smem_u32(&sel->list_cnt[ja < 0 ? 0 : ja]), cnt1 = smem_u32(&sel->list_cnt[jb < 0 ? 0 : jb]);
+            const uint32_t l0 = smem_u32(&sel->list[ja < 0 ? 0 : ja][0]), l1 = smem_u32(&sel->list[jb < 0 ? 0 : jb][0]);
+            auto take = [&](double xv) {
+                const double xc = xv + 0.0;
+                const unsigned long long k = ko_okey(xc);
+                if (ja >= 0 && ((k - la) >> sa) == 0) {
+                    unsigned pos;
+                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt0) : "memory");
+                    if (pos < (unsigned)P_LIST) sts_f64(l0 + pos * 8u, xc);
+                }
+                if (jb >= 0 && ((k - lb) >> sb) == 0) {
+                    unsigned pos;
+                    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt1) : "memory");
+                    if (pos < (unsigned)P_LIST) sts_f64(l1 + pos * 8u, xc);
+                }
+            };
+            if (ja >= 0 || jb >= 0)
+                fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
+                                 [&](double x0, bool v0, double x1, bool v1) {
+                                     if (v0) take(x0);
+                                     if (v1) take(x1);
+                                 },
+                                 take);
+        }
+        group_sync(grp, G);
+        KO_FT(27);
+        // ---- exact order statistic inside each short list by rank counting (doubles compare like their keys)
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+            const int j = jj ? fi.j1 : fi.j0;
+            if (j >= 0 && !direct[jj]) {
                 const int n = (int)min(sel->list_cnt[j], (unsigned)P_LIST);
                 const unsigned rho = sel->rho[j];
                 const uint32_t l32 = smem_u32(&sel->list[j][0]);
@@ -2396,8 +2456,8 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                 }
             }
         }
+        KO_FT(28);
     }
-    KO_FT(28);
 }
 
 // Returns (meaningful on finish thread 0) the mask of quantiles that a later attempt has to answer; 0 = all done.
@@ -2451,7 +2511,7 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
             const int bits = span ? 64 - __clzll((long long)span) : 0;
             ish[i] = bits > 6 ? bits - 6 : 0;
             capm[i] = pp->mode[i] == M_CAPTURE;
-            ovbad[i] = res->ovcnt[i] > (unsigned)pp->ovcap[i];
+            ovbad[i] = res->ovn > (unsigned)P_OVQ;
             if (capm[i]) ord[i] = ncapi++;
         }
     }
@@ -2482,10 +2542,12 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
                 }
             if (r <= cA || r > cA + nn) {
                 failmask |= 1 << j;       // the bracket missed the rank
+                if (ftid == 0) KO_COUNT(3, a.wide);
             } else if (!cm || kb - ka == 1) {
                 dval[j] = ko_key2d(ka);   // a single value: answered by the counts
             } else if (ob) {
                 failmask |= 1 << j;       // more candidates than shared memory holds
+                if (ftid == 0) KO_COUNT(4, a.wide);
             } else {
                 act_iv[j] = i;
                 rho[j] = r - cA;
@@ -2544,7 +2606,10 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) {
             out[j] = act_iv[j] >= 0 ? sel->val[j] : dval[j];
-            if (act_iv[j] >= 0 && !(out[j] == out[j])) failmask |= 1 << j;   // no candidate carried the rank
+            if (act_iv[j] >= 0 && !(out[j] == out[j])) {
+                if (!((failmask >> j) & 1)) KO_COUNT(6, a.wide);
+                failmask |= 1 << j;   // no candidate carried the rank
+            }
         }
         if (a.out_quant) {   // the quantiles that failed are written by a later attempt
             const int sid = pp->sid;
@@ -2611,7 +2676,10 @@ __device__ __noinline__ int pipe_finish_levels(const SeriesArgs& a, const PipePl
         }
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j)
-            if (rk[j] != 0u) fail |= 1 << j;   // the rank fell on a value that is not listed
+            if (rk[j] != 0u) {
+                fail |= 1 << j;   // the rank fell on a value that is not listed
+                KO_COUNT(7, a.wide);
+            }
         sel->fail = fail;
         {
             const int sid = pp->sid;
@@ -2653,6 +2721,7 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
             mbar_init(sm.bars() + B_POOL_FREE + s, 1);
             PipeResult* r0 = sm.res(s);
             r0->t_nvalid = 0;
+            r0->ovn = 0;
             for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
         }
         {
@@ -2760,6 +2829,8 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 cx.pool32 = smem_u32(sm.pool(pool));
                 cx.ovq32 = smem_u32(sm.ovq(pool));
                 cx.ovcnt32 = smem_u32(&res->ovcnt[0]);
+                cx.ovn32 = smem_u32(&res->ovn);
+                cx.ovtag32 = smem_u32(&res->ovtag[0]);
                 cx.trash32 = smem_u32(&res->trash);
 #pragma unroll
                 for (int i = 0; i < P_NI; ++i) {
@@ -2767,8 +2838,6 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                     p0[i] = on ? (uint32_t)(((size_t)pp->slot0[i] * P_NS + stid) * 8) : 0u;
                     acc.p[i] = p0[i];
                     acc.pend[i] = on ? p0[i] + (uint32_t)pp->nslots[i] * P_NS * 8 : 0u;
-                    cx.ov0[i] = on ? pp->ov0[i] : 0;
-                    cx.ovcap[i] = on ? pp->ovcap[i] : 0;
                 }
                 const int nb = pp->nb;
                 KO_PT0();
@@ -2836,6 +2905,7 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                     PipeResult* r0 = sm.res(pool);
                     PipeSel* sl = sm.sel();
                     r0->t_nvalid = 0;
+                    r0->ovn = 0;
                     for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
                     sl->fail = 0;
                     for (int j = 0; j < NI_MAX; ++j) {
@@ -3220,9 +3290,9 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
 
 #ifdef KO_PHASE_TIMING
 extern "C" int ko_debug_phases(unsigned long long* out16, int reset) {
-    KO_CUDA(cudaMemcpyFromSymbol(out16, g_phase, sizeof(unsigned long long) * 32));
+    KO_CUDA(cudaMemcpyFromSymbol(out16, g_phase, sizeof(unsigned long long) * 48));
     if (reset) {
-        unsigned long long z[32] = {0};
+        unsigned long long z[48] = {0};
         KO_CUDA(cudaMemcpyToSymbol(g_phase, z, sizeof(z)));
     }
     return KO_OK;

@@ -15,7 +15,7 @@ q = torch.zeros((n, 4), dtype=torch.float64, device="cuda")
 s = torch.zeros(n, dtype=torch.float64, device="cuda")
 names = ["fetch", "sample+sort", "plan", "stream", "reduce+decide", "select", "finish"]
 for qs in ([], [0.5], [0.5, 0.95, 0.99]):
-    buf = (ctypes.c_ulonglong * 32)()
+    buf = (ctypes.c_ulonglong * 48)()
     r.series_rollup_dev(dv.data_ptr(), do.data_ptr(), n, qs, s.data_ptr(), 0, 0, 0, 0, 0, q.data_ptr() if qs else 0,
                         torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
