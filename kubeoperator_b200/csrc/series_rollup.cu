@@ -61,6 +61,11 @@ struct SeriesArgs {
     int out_cnt;            // ... counted in counters[out_cnt]
     int wide;               // series_pipe: second attempt, one quantile per work item, twice the bracket width
     int pack;               // n_series < 2^27: the first attempt's list carries the unanswered quantiles in bits 27..30
+    // series_plan writes one plan per work item w in [w_begin, w_begin + plan_cap) to plans[w - w_begin];
+    // series_pipe, launched after it over the same window, fetches them
+    void* plans;
+    long long w_begin;
+    int plan_cap;
     int nq;
     double q[NI_MAX];   // ascending
     int qcol[NI_MAX];   // output column of q[j]
@@ -1378,7 +1383,7 @@ constexpr int P_SW = 12;                       // stream warps
 constexpr int P_FW = 6;                        // finish warps
 constexpr int P_NS = P_SW * 32;                // 384 stream threads
 constexpr int P_NF = P_FW * 32;                // 128 finish threads
-constexpr int P_PW = 2;                        // planner warps (series alternate between them)
+constexpr int P_PW = 1;                        // plan loader warp
 constexpr int P_PLANS = 8;                     // plan slots (a plan takes longer to build than a series to stream)
 constexpr uint32_t P_PLAN_LOG = 3;
 constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW) * 32;   // planners, producer, stream, finish
@@ -1395,7 +1400,7 @@ constexpr int P_LEVELS = 15;                   // distinct values a "levels" pla
 constexpr int P_NTHR = 31;                     // thresholds searched per sample (2 per level + one +inf pad)
 constexpr int P_MAX_L_LEVELS = 16000000;       // keeps the 16-bit per-thread counters of a levels plan exact
 
-struct PipePlan {
+struct alignas(16) PipePlan {
     int sid;                 // series index, -1 = no more work
     int defer;               // not eligible for the fast path
     int L, head, body, ntiles;
@@ -1843,6 +1848,49 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         for (int j = 0; j < NI_MAX; ++j) pp->q_iv[j] = q_iv.v[j];
     }
     __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------ plan kernel
+// One warp per work item, ahead of series_pipe: the plans are about 5 000 instructions of straight-line code per
+// series, which inside the pipelined kernel kept evicting the stream and finish loops from the instruction caches.
+constexpr int PLAN_WARPS = 8;
+__global__ void __launch_bounds__(PLAN_WARPS * 32) series_plan(SeriesArgs a) {
+    __shared__ PipePlan sp[PLAN_WARPS];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long n_items = (long long)a.counters[a.work_cnt] * (a.wide ? a.nq : 1);
+    const long long hi = n_items < a.w_begin + a.plan_cap ? n_items : a.w_begin + a.plan_cap;
+    const long long gw = (long long)blockIdx.x * PLAN_WARPS + warp, nw = (long long)gridDim.x * PLAN_WARPS;
+    PipePlan* pp = &sp[warp];
+    for (long long w = a.w_begin + gw; w < hi; w += nw) {
+        const int item = a.wide ? (int)(w / a.nq) : (int)w;
+        const int qsel = a.wide ? (int)(w - (long long)item * a.nq) : -1;
+        const int entry = a.work_list[item];
+        const bool packed = a.wide && a.pack;
+        const int sid = packed ? (entry & 0x07FFFFFF) : (entry & 0x7FFFFFFF);
+        if (packed && !((entry >> (27 + qsel)) & 1)) {   // this quantile was answered by the first attempt
+            if (lane == 0) {
+                pp->sid = sid;
+                pp->defer = 2;
+            }
+        } else {
+            planner_build(pp, a, sid, qsel, item, lane);
+        }
+        __syncwarp();
+        const uint4* src = reinterpret_cast<const uint4*>(pp);
+        uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<PipePlan*>(a.plans) + (w - a.w_begin));
+        for (int t = lane; t < (int)(sizeof(PipePlan) / 16); t += 32) dst[t] = src[t];
+        __syncwarp();
+    }
+    // wide attempt: what does not fit the plan window goes straight to the slow path's list (once per series)
+    if (a.wide && lane == 0)
+        for (long long w = hi + gw; w < n_items; w += nw) {
+            const int item = (int)(w / a.nq);
+            const int entry = atomicOr(const_cast<int*>(&a.work_list[item]), (int)0x80000000);
+            if (entry >= 0) {
+                const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
+                a.out_list[pos] = a.pack ? (entry & 0x07FFFFFF) : entry;
+            }
+        }
 }
 
 // ------------------------------------------------------------------------------------------ stream
@@ -2742,39 +2790,25 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
     const long long n_long = (long long)a.counters[a.work_cnt] * (a.wide ? a.nq : 1);
 
     if (warp < P_PW) {
-        // ================================================================ PLANNERS
-        // Series are dealt to the CTAs round-robin (ordinal k of this CTA is long_list[blockIdx.x + k*gridDim.x]);
-        // planner warp p prepares the ordinals k = p, p + P_PW, ...
-        for (uint32_t k = (uint32_t)warp;; k += P_PW) {
-            const uint32_t slot = k & (P_PLANS - 1);
-            mbar_wait_sleep(sm.bars() + B_PLAN_FREE + slot, ((k >> P_PLAN_LOG) & 1u) ^ 1u);
-            const long long w = (long long)blockIdx.x + (long long)k * gridDim.x;
-            PipePlan* pp = sm.plan(slot);
-            if (w >= n_long) {
-                if (lane == 0) pp->sid = -1;
-                __syncwarp();
-                if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
-                break;
-            }
-            {
-                KO_PT0();
-                const int item = a.wide ? (int)(w / a.nq) : (int)w;
-                const int qsel = a.wide ? (int)(w - (long long)item * a.nq) : -1;
-                const int entry = a.work_list[item];
-                const bool packed = a.wide && a.pack;
-                const int sid = packed ? (entry & 0x07FFFFFF) : (entry & 0x7FFFFFFF);
-                if (packed && !((entry >> (27 + qsel)) & 1)) {   // this quantile was answered by the first attempt
-                    if (lane == 0) {
-                        pp->sid = sid;
-                        pp->defer = 2;
-                    }
-                    __syncwarp();
-                } else {
-                    planner_build(pp, a, sid, qsel, item, lane);
+        // ================================================================ PLAN LOADER
+        // Work items are dealt to the CTAs round-robin (ordinal k of this CTA is item w_begin + blockIdx.x +
+        // k * gridDim.x); their plans, written by series_plan, are fetched into the plan slots with bulk copies.
+        if (lane == 0) {
+            const long long hi = n_long < a.w_begin + a.plan_cap ? n_long : a.w_begin + a.plan_cap;
+            for (uint32_t k = 0;; ++k) {
+                const uint32_t slot = k & (P_PLANS - 1);
+                mbar_wait_sleep(sm.bars() + B_PLAN_FREE + slot, ((k >> P_PLAN_LOG) & 1u) ^ 1u);
+                const long long w = a.w_begin + (long long)blockIdx.x + (long long)k * gridDim.x;
+                PipePlan* pp = sm.plan(slot);
+                if (w >= hi) {
+                    pp->sid = -1;
+                    mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
+                    break;
                 }
-                KO_PT1(8, lane == 0);
+                mbar_expect_tx(sm.bars() + B_PLAN_FULL + slot, (uint32_t)sizeof(PipePlan));
+                tma_bulk_g2s(pp, reinterpret_cast<const PipePlan*>(a.plans) + (w - a.w_begin),
+                             (uint32_t)sizeof(PipePlan), sm.bars() + B_PLAN_FULL + slot);
             }
-            if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FULL + slot);
         }
     } else if (warp == P_PW) {
         // ================================================================ PRODUCER
@@ -2936,32 +2970,61 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
 
 bool g_attr_done = false;
 
+constexpr int PLAN_CAP_CTX = 16384;      // plan window of the context's scratch (9 MB)
+constexpr int PLAN_CAP_STATIC = 2048;    // ... of the static scratch of ko_series_rollup_static (1.1 MB)
+// counters + the two series lists, rounded so that the plans behind them are 256-byte aligned
+constexpr size_t series_lists_bytes(int64_t n_series) { return ((size_t)(8 + 2 * n_series) * sizeof(int) + 255) / 256 * 256; }
+
 // The kernels of the long-series path, enqueued on `st`:
-//   1. series_pipe over every long series (fast path: one pass per series);
-//   2. series_pipe again over what step 1 could not finish, one work item per (series, quantile), with brackets
-//      twice as wide -- a bracket that missed its rank (about one series in a thousand) is settled here;
-//   3. series_long, the exact multi-pass slow path, over what is still left (heavy tie groups that fit neither
-//      the capture slots nor a levels plan, series with almost no valid samples).
-static void launch_long_path(SeriesArgs a, int num_sms, int64_t n_series, cudaStream_t st) {
+//   1. first attempt, in windows of plan_cap series: series_plan (brackets from a pre-sample) then series_pipe
+//      (fast path: one pass per series);
+//   2. second attempt over what step 1 could not finish, one work item per (series, unanswered quantile), with
+//      brackets twice as wide -- a bracket that missed its rank or overflowed is settled here;
+//   3. series_long, the exact multi-pass slow path, over what is still left (series with almost no valid samples,
+//      brackets that fit neither the capture slots nor a levels plan).
+// One window covers n_series <= plan_cap.  Beyond that the number of long series is read back from the device
+// (one stream synchronisation) so that only the windows that hold work are launched.
+static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series, void* plans, int plan_cap,
+                                    cudaStream_t st, int* launches) {
     int pgrid = num_sms;
     if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
     int grid = 2 * num_sms;
     if ((int64_t)grid > n_series) grid = (int)n_series;
     a.pack = n_series < (1LL << 27) ? 1 : 0;
+    a.plans = plans;
+    a.plan_cap = plan_cap;
+    int64_t n_long = n_series;
+    if (n_series > (int64_t)plan_cap) {
+        int h = 0;
+        cudaError_t e = cudaMemcpyAsync(&h, a.counters, sizeof(int), cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) return e;
+        n_long = h;
+    }
     a.work_list = a.long_list;
     a.work_cnt = 0;
     a.work_cur = 1;
     a.out_list = a.defer_list;
     a.out_cnt = 4;
     a.wide = 0;
-    series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+    for (int64_t w0 = 0; w0 < n_long; w0 += plan_cap) {
+        const int64_t cnt = n_long - w0 < plan_cap ? n_long - w0 : plan_cap;
+        a.w_begin = w0;
+        const int pg = (int)((cnt + PLAN_WARPS - 1) / PLAN_WARPS);
+        series_plan<<<pg < 4 * num_sms ? pg : 4 * num_sms, PLAN_WARPS * 32, 0, st>>>(a);
+        series_pipe<<<(int64_t)pgrid < cnt ? pgrid : (int)cnt, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+        *launches += 2;
+    }
     if (a.nq > 0) {
         a.work_list = a.defer_list;
         a.work_cnt = 4;
         a.out_list = a.long_list;   // the first list is no longer needed
         a.out_cnt = 6;
         a.wide = 1;
+        a.w_begin = 0;
+        series_plan<<<num_sms, PLAN_WARPS * 32, 0, st>>>(a);
         series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+        *launches += 2;
         a.work_list = a.long_list;
         a.work_cnt = 6;
     } else {
@@ -2970,6 +3033,8 @@ static void launch_long_path(SeriesArgs a, int num_sms, int64_t n_series, cudaSt
     }
     a.work_cur = 7;
     series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
+    *launches += 1;
+    return cudaSuccess;
 }
 
 }  // namespace
@@ -3026,15 +3091,19 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
     series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, stream>>>(a);
     KO_CUDA(cudaEventRecord(ctx->ev_k0, stream));
-    launch_long_path(a, ctx->num_sms, n_series, stream);
+    int launches = 2;
+    void* plans = reinterpret_cast<unsigned char*>(d_scratch) + series_lists_bytes(n_series);
+    KO_CUDA(launch_long_path(a, ctx->num_sms, n_series, plans, PLAN_CAP_CTX, stream, &launches));
     KO_CUDA(cudaEventRecord(ctx->ev_k1, stream));
     ctx->k_timed = true;
     KO_CUDA(cudaGetLastError());
-    ctx->counters.kernel_launches += nq > 0 ? 5 : 4;
+    ctx->counters.kernel_launches += launches;
     return KO_OK;
 }
 
-size_t ko_series_scratch_bytes(int64_t n_series) { return (size_t)(8 + 2 * n_series) * sizeof(int); }
+size_t ko_series_scratch_bytes(int64_t n_series) {
+    return series_lists_bytes(n_series) + (size_t)PLAN_CAP_CTX * sizeof(PipePlan);
+}
 
 extern "C" int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_offsets,
                                     int64_t n_series, const double* q, int nq, double* d_out_sum,
@@ -3190,7 +3259,8 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
 // streams, or threads launching concurrently — race on it.  Serialise them on one stream.
 namespace {
 
-static __device__ __align__(256) int g_static_scratch[8 + 2 * KO_STATIC_MAX_SERIES];
+static __device__ __align__(256) int g_static_scratch[(series_lists_bytes(KO_STATIC_MAX_SERIES) +
+                                                        (size_t)PLAN_CAP_STATIC * sizeof(PipePlan)) / sizeof(int)];
 
 constexpr int STATIC_MAX_DEVICES = 64;
 struct StaticDevice {
@@ -3283,7 +3353,9 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     classify_series<<<(unsigned)((n_series + 255) / 256), 256, 0, st>>>(a);
     const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
     series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, st>>>(a);
-    launch_long_path(a, sd->num_sms, n_series, st);
+    int launches = 0;
+    void* plans = reinterpret_cast<unsigned char*>(sd->scratch) + series_lists_bytes(KO_STATIC_MAX_SERIES);
+    KO_CUDA(launch_long_path(a, sd->num_sms, n_series, plans, PLAN_CAP_STATIC, st, &launches));
     KO_CUDA(cudaGetLastError());
     return KO_OK;
 }
