@@ -1924,7 +1924,7 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
 __device__ __forceinline__ void pipe_capture(const PStreamCtx& c, uint32_t& p, uint32_t pend, int i, double x,
                                              int lane) {
     (void)lane;
-    uint32_t addr = c.pool32 + p;
+    uint32_t addr = p;
     if (p != pend) {
         p += P_NS * 8;
     } else {
@@ -1981,6 +1981,35 @@ __device__ __noinline__ Stats4 rare_nan4(Stats4 st, double a, double b, double c
     return st;
 }
 
+// One sample against a bracket / the upper tail, as predicated PTX (the compiler's own lowering of the same C++
+// spends two instructions per conditional count).  p is the shared-memory address of the thread's next free slot.
+__device__ __forceinline__ void cap_bracket(double x, double tA, double tB, unsigned& cA, uint32_t& p) {
+    asm volatile(
+        "{\n.reg .pred lt, in;\n"
+        "setp.lt.f64 lt, %2, %3;\n"
+        "@lt add.u32 %0, %0, 1;\n"
+        "setp.lt.and.f64 in, %2, %4, !lt;\n"
+        "@in st.shared.f64 [%1], %2;\n"
+        "@in add.u32 %1, %1, %5;\n}"
+        : "+r"(cA), "+r"(p) : "d"(x), "d"(tA), "d"(tB), "n"(P_NS * 8) : "memory");
+}
+__device__ __forceinline__ void cnt_bracket(double x, double tA, double tB, unsigned& cA, unsigned& cin) {
+    asm("{\n.reg .pred lt, in;\n"
+        "setp.lt.f64 lt, %2, %3;\n"
+        "@lt add.u32 %0, %0, 1;\n"
+        "setp.lt.and.f64 in, %2, %4, !lt;\n"
+        "@in add.u32 %1, %1, 1;\n}"
+        : "+r"(cA), "+r"(cin) : "d"(x), "d"(tA), "d"(tB));
+}
+__device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p) {
+    asm volatile(
+        "{\n.reg .pred in;\n"
+        "setp.ge.f64 in, %1, %2;\n"
+        "@in st.shared.f64 [%0], %1;\n"
+        "@in add.u32 %0, %0, %3;\n}"
+        : "+r"(p) : "d"(x), "d"(tT), "n"(P_NS * 8) : "memory");
+}
+
 template <int NB, bool TAIL>
 struct PFast {
     double tA[NB > 0 ? NB : 1], tB[NB > 0 ? NB : 1];
@@ -2023,37 +2052,22 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
     // samples are handled by straight-line predicated code (no branches, no overflow test per sample).
     bool room = true;
 #pragma unroll
-    for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i) room = room && (acc.pend[i] - acc.p[i] >= 4u * P_NS * 8u);
+    for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i)
+        room = room && ((i < NB && !fr.cap[i < NB ? i : 0]) || acc.pend[i] - acc.p[i] >= 4u * P_NS * 8u);
     if (room) {
 #pragma unroll
         for (int i = 0; i < NB; ++i) {
             if (fr.cap[i]) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const bool lt = x[e] < fr.tA[i];
-                    acc.cA[i] += lt ? 1u : 0u;
-                    if (!lt && (x[e] < fr.tB[i])) {
-                        sts_f64(c.pool32 + acc.p[i], x[e]);
-                        acc.p[i] += P_NS * 8;
-                    }
-                }
+                for (int e = 0; e < 4; ++e) cap_bracket(x[e], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i]);
             } else {   // count-only bracket (a tie group)
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const bool lt = x[e] < fr.tA[i];
-                    acc.cA[i] += lt ? 1u : 0u;
-                    acc.cin[i] += (!lt && (x[e] < fr.tB[i])) ? 1u : 0u;
-                }
+                for (int e = 0; e < 4; ++e) cnt_bracket(x[e], fr.tA[i], fr.tB[i], acc.cA[i], acc.cin[i]);
             }
         }
         if (TAIL) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                if (x[e] >= fr.tT) {
-                    sts_f64(c.pool32 + acc.p[NB], x[e]);
-                    acc.p[NB] += P_NS * 8;
-                }
-            }
+            for (int e = 0; e < 4; ++e) cap_tail(x[e], fr.tT, acc.p[NB]);
         }
         return;
     }
@@ -2123,7 +2137,7 @@ __device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const
     uint32_t s = g % P_STAGES, par = (g / P_STAGES) & 1u;
     int rem2 = body >> 1;
     for (int t = 0; t < ntiles; ++t) {
-        mbar_wait_addr(full0 + s * 8u, par);
+        { KO_PT0(); mbar_wait_addr(full0 + s * 8u, par); KO_PT1(16, stid == 0); }
         const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
         double x[4];
         if (rem2 >= P_TILE / 2) {
@@ -2190,7 +2204,7 @@ __device__ __forceinline__ void pipe_levels4(const double (&x)[4], PAcc& acc, ui
     }
 }
 
-__device__ __noinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc, uint32_t pool32, const PipeSmem& sm,
+__device__ __forceinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc, uint32_t pool32, const PipeSmem& sm,
                                                 uint32_t& g, int stid, int lane) {
     const uint32_t thr32 = smem_u32(&pp->thr[0]);
     const uint32_t col32 = pool32 + (uint32_t)stid * 2u;
@@ -2459,15 +2473,21 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
             const int sa = sh[0], sb = sh[1];
             const uint32_t cnt0 = smem_u32(&sel->list_cnt[ja < 0 ? 0 : ja]), cnt1 = smem_u32(&sel->list_cnt[jb < 0 ? 0 : jb]);
             const uint32_t l0 = smem_u32(&sel->list[ja < 0 ? 0 : ja][0]), l1 = smem_u32(&sel->list[jb < 0 ? 0 : jb][0]);
+            // the sub-brackets as ranges of doubles (doubles order like their keys): [dla, dha) and [dlb, dhb); an
+            // upper end beyond +inf is a NaN, which no comparison passes
+            const unsigned long long ha = la + (1ull << sa), hb = lb + (1ull << sb);
+            const double qnan = __longlong_as_double(0x7FF8000000000000LL);
+            const double dla = ko_key2d(la), dlb = ko_key2d(lb);
+            const double dha = (ha < la || ha > KO_KEY_PINF) ? qnan : ko_key2d(ha);
+            const double dhb = (hb < lb || hb > KO_KEY_PINF) ? qnan : ko_key2d(hb);
             auto take = [&](double xv) {
                 const double xc = xv + 0.0;
-                const unsigned long long k = ko_okey(xc);
-                if (ja >= 0 && ((k - la) >> sa) == 0) {
+                if (ja >= 0 && xc >= dla && !(xc >= dha)) {
                     unsigned pos;
                     asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt0) : "memory");
                     if (pos < (unsigned)P_LIST) sts_f64(l0 + pos * 8u, xc);
                 }
-                if (jb >= 0 && ((k - lb) >> sb) == 0) {
+                if (jb >= 0 && xc >= dlb && !(xc >= dhb)) {
                     unsigned pos;
                     asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(cnt1) : "memory");
                     if (pos < (unsigned)P_LIST) sts_f64(l1 + pos * 8u, xc);
@@ -2672,7 +2692,7 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
 
 // Finish of a levels plan: total the per-thread gap counters, then every rank must fall on a listed level, i.e.
 // (#valid samples < v) < rank <= (#valid samples <= v); otherwise the series goes to the slow path.
-__device__ __noinline__ int pipe_finish_levels(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
+__device__ __forceinline__ int pipe_finish_levels(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
                                                 const unsigned char* pool, int ftid, int fwarp, int lane) {
     const int nq = a.nq;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
@@ -2869,7 +2889,7 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
 #pragma unroll
                 for (int i = 0; i < P_NI; ++i) {
                     const bool on = i < ni;
-                    p0[i] = on ? (uint32_t)(((size_t)pp->slot0[i] * P_NS + stid) * 8) : 0u;
+                    p0[i] = on ? cx.pool32 + (uint32_t)(((size_t)pp->slot0[i] * P_NS + stid) * 8) : 0u;
                     acc.p[i] = p0[i];
                     acc.pend[i] = on ? p0[i] + (uint32_t)pp->nslots[i] * P_NS * 8 : 0u;
                 }

@@ -31,4 +31,4 @@ for qs in ([], [0.5], [0.5, 0.95, 0.99]):
     print("   finish parts (us): prologue=%.1f groups=%.1f final_sync=%.1f | scan1=%.1f totals=%.1f walk+zero=%.1f scan2=%.1f rank=%.1f" % tuple(buf[i] / 1900.0 for i in (13, 14, 7, 24, 25, 26, 27, 28)))
     print("   for_each calls=%d max nmax=%d" % (buf[23], buf[22]))
     print("   for_each loops: %.1f us total, %d iterations -> %.0f cycles/iteration" % (buf[20] / 1900.0, buf[21], buf[20] / max(buf[21], 1)))
-    print("   pipe CTA0 (us): planner=%.1f stream=%.1f finish=%.1f stream_wait_plan=%.1f finish_wait_pool=%.1f" % tuple(buf[i] / 1900.0 for i in (8, 9, 10, 11, 12)))
+    print("   pipe CTA0 (us): planner=%.1f stream=%.1f finish=%.1f stream_wait_plan=%.1f finish_wait_pool=%.1f stream_wait_data=%.1f" % tuple(buf[i] / 1900.0 for i in (8, 9, 10, 11, 12, 16)))
