@@ -1440,7 +1440,7 @@ struct PipeSel {             // scratch of the finish warps
     unsigned char cnt8[64][P_CROW];
     double list[NI_MAX][P_LIST];               // candidates of the chosen sub-bracket per quantile
     unsigned tot[P_NI][64];                    // sums of the counters per group
-    unsigned char dummy[2][P_NF];              // counters of absent samples
+    unsigned char dummy[4][P_NF];              // counters of absent samples
     unsigned list_cnt[NI_MAX];
     int bin[NI_MAX];                           // chosen sub-bracket per quantile
     unsigned rho[NI_MAX];                      // rank inside it
@@ -1721,9 +1721,11 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                 kA[i] = ka;
                 mode[i] = M_CAPTURE;
                 bool is_tail = false;
-                if (ka == kb) {
+                if (ka == kb) {   // the whole bracket is one tie group: a levels plan answers it, or nothing here does
                     mode[i] = M_COUNT;
                     kB[i] = ka + 1;
+                    ties = 1;
+                    soft = 1;
                 } else if (hi_i >= valid_s) {
                     is_tail = true;
                     kB[i] = KO_KEY_PINF + 1;
@@ -1898,7 +1900,6 @@ struct PAcc {
     double sum, mn, mx;
     unsigned nvalid;
     unsigned cA[2];
-    unsigned cin[2];
     uint32_t p[P_NI], pend[P_NI];
 };
 
@@ -1993,14 +1994,6 @@ __device__ __forceinline__ void cap_bracket(double x, double tA, double tB, unsi
         "@in add.u32 %1, %1, %5;\n}"
         : "+r"(cA), "+r"(p) : "d"(x), "d"(tA), "d"(tB), "n"(P_NS * 8) : "memory");
 }
-__device__ __forceinline__ void cnt_bracket(double x, double tA, double tB, unsigned& cA, unsigned& cin) {
-    asm("{\n.reg .pred lt, in;\n"
-        "setp.lt.f64 lt, %2, %3;\n"
-        "@lt add.u32 %0, %0, 1;\n"
-        "setp.lt.and.f64 in, %2, %4, !lt;\n"
-        "@in add.u32 %1, %1, 1;\n}"
-        : "+r"(cA), "+r"(cin) : "d"(x), "d"(tA), "d"(tB));
-}
 __device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p) {
     asm volatile(
         "{\n.reg .pred in;\n"
@@ -2013,7 +2006,6 @@ __device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p) {
 template <int NB, bool TAIL>
 struct PFast {
     double tA[NB > 0 ? NB : 1], tB[NB > 0 ? NB : 1];
-    bool cap[NB > 0 ? NB : 1];
     double tT;
 };
 
@@ -2052,18 +2044,12 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
     // samples are handled by straight-line predicated code (no branches, no overflow test per sample).
     bool room = true;
 #pragma unroll
-    for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i)
-        room = room && ((i < NB && !fr.cap[i < NB ? i : 0]) || acc.pend[i] - acc.p[i] >= 4u * P_NS * 8u);
+    for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i) room = room && (acc.pend[i] - acc.p[i] >= 4u * P_NS * 8u);
     if (room) {
 #pragma unroll
         for (int i = 0; i < NB; ++i) {
-            if (fr.cap[i]) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) cap_bracket(x[e], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i]);
-            } else {   // count-only bracket (a tie group)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) cnt_bracket(x[e], fr.tA[i], fr.tB[i], acc.cA[i], acc.cin[i]);
-            }
+            for (int e = 0; e < 4; ++e) cap_bracket(x[e], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i]);
         }
         if (TAIL) {
 #pragma unroll
@@ -2083,14 +2069,9 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
             any = any || in[e];
         }
         if (any) {
-            if (fr.cap[i]) {
 #pragma unroll
-                for (int e = 0; e < 4; ++e)
-                    if (in[e]) pipe_capture(c, acc.p[i], acc.pend[i], i, x[e], lane);
-            } else {
-#pragma unroll
-                for (int e = 0; e < 4; ++e) acc.cin[i] += in[e] ? 1u : 0u;
-            }
+            for (int e = 0; e < 4; ++e)
+                if (in[e]) pipe_capture(c, acc.p[i], acc.pend[i], i, x[e], lane);
         }
     }
     if (TAIL) {
@@ -2118,7 +2099,6 @@ __device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const
     for (int i = 0; i < NB; ++i) {
         fr.tA[i] = pp->tA[i];
         fr.tB[i] = pp->tB[i];
-        fr.cap[i] = pp->mode[i] == M_CAPTURE;
     }
     fr.tT = TAIL ? pp->tA[NB] : 0.0;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
@@ -2300,26 +2280,30 @@ struct FinIv {
 // gt, gt + G, ... taken two columns at a time (shared-memory latency is > 100 cycles while the stream warps and
 // the TMA engine keep the banks busy, so the next row is fetched before the current one is processed), then a
 // share of the overflow queue.
-template <int NG, typename F2, typename F1>
+template <int NG, typename F4, typename F1>
 __device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, const PipePlan* pp,
-                                             const PipeResult* res, int iv, int gt, F2 frow, F1 fone) {
+                                             const PipeResult* res, int iv, int gt, F4 frow, F1 fone) {
     constexpr int G = P_NF / NG;
     const uint32_t base0 = pool32 + (uint32_t)(((size_t)pp->slot0[iv] * P_NS + gt) * 8);
 #pragma unroll
-    for (int pr = 0; pr < NG; ++pr) {   // P_NS / G = 2 * NG columns
+    for (int pr = 0; pr < NG; ++pr) {   // P_NS / G = 2 * NG columns; two columns and two rows per step
         const int c0 = gt + 2 * pr * G;
         const uint32_t base = base0 + (uint32_t)(2 * pr * G) * 8u;
         const int n0 = res->pcount[iv][c0], n1 = res->pcount[iv][c0 + G];
         const int nmax = max(n0, n1);
-        double y0 = 0.0, y1 = 0.0;
+        double y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0;
         if (0 < n0) y0 = lds_f64(base);
         if (0 < n1) y1 = lds_f64(base + G * 8);
-        for (int s = 0; s < nmax; ++s) {
-            const double x0 = y0, x1 = y1;
-            const uint32_t nrow = base + (uint32_t)(s + 1) * (P_NS * 8);
-            if (s + 1 < n0) y0 = lds_f64(nrow);
-            if (s + 1 < n1) y1 = lds_f64(nrow + G * 8);
-            frow(x0, s < n0, x1, s < n1);
+        if (1 < n0) y2 = lds_f64(base + P_NS * 8);
+        if (1 < n1) y3 = lds_f64(base + P_NS * 8 + G * 8);
+        for (int s = 0; s < nmax; s += 2) {
+            const double x0 = y0, x1 = y1, x2 = y2, x3 = y3;
+            const uint32_t nrow = base + (uint32_t)(s + 2) * (P_NS * 8);
+            if (s + 2 < n0) y0 = lds_f64(nrow);
+            if (s + 2 < n1) y1 = lds_f64(nrow + G * 8);
+            if (s + 3 < n0) y2 = lds_f64(nrow + P_NS * 8);
+            if (s + 3 < n1) y3 = lds_f64(nrow + P_NS * 8 + G * 8);
+            frow(x0, s < n0, x1, s < n1, x2, s + 1 < n0, x3, s + 1 < n1);
         }
     }
     // the overflow queue is shared by the intervals of the series: entries carry their interval as a tag
@@ -2413,16 +2397,19 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                 return valid ? col + (uint32_t)((k - kA) >> ish) * (uint32_t)P_CROW : dummy + (uint32_t)which * P_NF;
             };
             fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
-                             [&](double x0, bool v0, double x1, bool v1) {
+                             [&](double x0, bool v0, double x1, bool v1, double x2, bool v2, double x3, bool v3) {
+                                 // four counters are loaded together and stored in order; a later sample that hits
+                                 // the counter of an earlier one carries that one's increment
                                  const uint32_t a0 = addr_of(x0, v0, 0), a1 = addr_of(x1, v1, 1);
-                                 if (a0 == a1) {   // both samples in one sub-bracket: one after the other
-                                     sts_u8(a0, lds_u8(a0) + 1);
-                                     sts_u8(a1, lds_u8(a1) + 1);
-                                 } else {
-                                     const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1);
-                                     sts_u8(a0, c0 + 1);
-                                     sts_u8(a1, c1 + 1);
-                                 }
+                                 const uint32_t a2 = addr_of(x2, v2, 2), a3 = addr_of(x3, v3, 3);
+                                 const unsigned c0 = lds_u8(a0), c1 = lds_u8(a1), c2 = lds_u8(a2), c3 = lds_u8(a3);
+                                 const unsigned d1 = c1 + (a1 == a0 ? 1u : 0u);
+                                 const unsigned d2 = c2 + (a2 == a0 ? 1u : 0u) + (a2 == a1 ? 1u : 0u);
+                                 const unsigned d3 = c3 + (a3 == a0 ? 1u : 0u) + (a3 == a1 ? 1u : 0u) + (a3 == a2 ? 1u : 0u);
+                                 sts_u8(a0, c0 + 1);
+                                 sts_u8(a1, d1 + 1);
+                                 sts_u8(a2, d2 + 1);
+                                 sts_u8(a3, d3 + 1);
                              },
                              [&](double xv) {
                                  const uint32_t a0 = addr_of(xv, true, 0);
@@ -2451,9 +2438,11 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                     }
                 };
                 fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
-                                 [&](double x0, bool v0, double x1, bool v1) {
+                                 [&](double x0, bool v0, double x1, bool v1, double x2, bool v2, double x3, bool v3) {
                                      if (v0) bump(x0);
                                      if (v1) bump(x1);
+                                     if (v2) bump(x2);
+                                     if (v3) bump(x3);
                                  },
                                  bump);
                 totals_and_walk(j, rho, -1, 0u);
@@ -2495,9 +2484,11 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
             };
             if (ja >= 0 || jb >= 0)
                 fin_for_rows<NG>(pool32, ovq32, pp, res, fi.iv, gt,
-                                 [&](double x0, bool v0, double x1, bool v1) {
+                                 [&](double x0, bool v0, double x1, bool v1, double x2, bool v2, double x3, bool v3) {
                                      if (v0) take(x0);
                                      if (v1) take(x1);
+                                     if (v2) take(x2);
+                                     if (v3) take(x3);
                                  },
                                  take);
         }
@@ -2877,7 +2868,6 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 acc.mx = pp->smax;
                 acc.nvalid = 0;
                 acc.cA[0] = acc.cA[1] = 0;
-                acc.cin[0] = acc.cin[1] = 0;
                 uint32_t p0[P_NI];
                 PStreamCtx cx;
                 cx.pool32 = smem_u32(sm.pool(pool));
@@ -2911,7 +2901,6 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 const double ws = warp_sum(acc.sum), wmn = warp_min(acc.mn), wmx = warp_max(acc.mx);
                 const unsigned wn = warp_sum_u(acc.nvalid);
                 const unsigned ca0 = warp_sum_u(acc.cA[0]), ca1 = warp_sum_u(acc.cA[1]);
-                const unsigned ci0 = warp_sum_u(acc.cin[0]), ci1 = warp_sum_u(acc.cin[1]);
                 unsigned pc[P_NI], wpc[P_NI];
 #pragma unroll
                 for (int i = 0; i < P_NI; ++i) {
@@ -2926,8 +2915,6 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                     red_shared_add(&res->t_nvalid, wn);
                     red_shared_add(&res->t_cA[0], ca0);
                     red_shared_add(&res->t_cA[1], ca1);
-                    red_shared_add(&res->t_cin[0], ci0);
-                    red_shared_add(&res->t_cin[1], ci1);
 #pragma unroll
                     for (int i = 0; i < P_NI; ++i) red_shared_add(&res->t_ncap[i], wpc[i]);
                 }
