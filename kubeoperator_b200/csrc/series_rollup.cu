@@ -1756,6 +1756,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
             // judged on the packed keys; whatever this misses only makes the finish warps defer the series.
             unsigned prev_last = __shfl_up_sync(0xffffffffu, r[31], 1);
             if (lane == 0) prev_last = 0xFFFFFFFFu;
+            unsigned seen = 0xFFFFFFFFu;   // packed position of the last level listed by an earlier interval
 #pragma unroll
             for (int i = 0; i < P_NI; ++i) {
                 if (i < ni) {
@@ -1766,9 +1767,11 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                     for (int e = 0; e < 32; ++e) {
                         const int p = (lane << 5) | e;
                         const unsigned prevk = e ? r[e > 0 ? e - 1 : 0] : prev_last;
-                        const bool sl = p >= a0 && p <= b0 && (p == a0 || (r[e] >> 10) != (prevk >> 10));
+                        const unsigned mine = r[e] >> 10;
+                        const bool sl = p >= a0 && p <= b0 && (p == a0 ? mine != seen : mine != (prevk >> 10));
                         selmask |= sl ? (1u << e) : 0u;
                     }
+                    seen = planner_at(r, b0, lane) >> 10;
                     int cnt = __popc(selmask), inc = cnt;
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) {
@@ -1920,27 +1923,6 @@ __device__ __forceinline__ unsigned lds_u8(uint32_t addr) {
 __device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
     asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
 }
-// Store x into the thread's next private slot of interval i; when the slots are full (a few per cent of the
-// captures) claim an entry of the overflow queue with a shared-memory atomic.
-__device__ __forceinline__ void pipe_capture(const PStreamCtx& c, uint32_t& p, uint32_t pend, int i, double x,
-                                             int lane) {
-    (void)lane;
-    uint32_t addr = p;
-    if (p != pend) {
-        p += P_NS * 8;
-    } else {
-        unsigned pos;
-        asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(c.ovn32) : "memory");
-        asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(c.ovcnt32 + 4u * i) : "memory");
-        addr = c.trash32;
-        if (pos < (unsigned)P_OVQ) {
-            addr = c.ovq32 + pos * 8u;
-            sts_u8(c.ovtag32 + pos, (unsigned)i);
-        }
-    }
-    sts_f64(addr, x);
-}
-
 // Helpers of the stream loop.  The compare chains are PTX so that the compiler does not rewrite them into a
 // min/max tree, and the rare updates are out-of-line calls so that they stay behind a real branch instead of
 // being predicated into every iteration.
@@ -1983,24 +1965,46 @@ __device__ __noinline__ Stats4 rare_nan4(Stats4 st, double a, double b, double c
 }
 
 // One sample against a bracket / the upper tail, as predicated PTX (the compiler's own lowering of the same C++
-// spends two instructions per conditional count).  p is the shared-memory address of the thread's next free slot.
-__device__ __forceinline__ void cap_bracket(double x, double tA, double tB, unsigned& cA, uint32_t& p) {
+// spends two instructions per conditional count).  p is the shared-memory address of the thread's next free
+// private slot, pend the end of its slots; a sample that finds them full sets bit E of ovm and is queued by the
+// caller (rare), so that the common path has no branch per sample and no "is there room" test per step.
+template <int E>
+__device__ __forceinline__ void cap_bracket(double x, double tA, double tB, unsigned& cA, uint32_t& p, uint32_t pend,
+                                            unsigned& ovm) {
     asm volatile(
-        "{\n.reg .pred lt, in;\n"
-        "setp.lt.f64 lt, %2, %3;\n"
+        "{\n.reg .pred lt, in, st, ov;\n"
+        "setp.lt.f64 lt, %3, %4;\n"
         "@lt add.u32 %0, %0, 1;\n"
-        "setp.lt.and.f64 in, %2, %4, !lt;\n"
-        "@in st.shared.f64 [%1], %2;\n"
-        "@in add.u32 %1, %1, %5;\n}"
-        : "+r"(cA), "+r"(p) : "d"(x), "d"(tA), "d"(tB), "n"(P_NS * 8) : "memory");
+        "setp.lt.and.f64 in, %3, %5, !lt;\n"
+        "setp.ne.and.u32 st, %1, %6, in;\n"
+        "setp.eq.and.u32 ov, %1, %6, in;\n"
+        "@st st.shared.f64 [%1], %3;\n"
+        "@st add.u32 %1, %1, %7;\n"
+        "@ov or.b32 %2, %2, %8;\n}"
+        : "+r"(cA), "+r"(p), "+r"(ovm) : "d"(x), "d"(tA), "d"(tB), "r"(pend), "n"(P_NS * 8), "n"(1 << E) : "memory");
 }
-__device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p) {
+template <int E>
+__device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p, uint32_t pend, unsigned& ovm) {
     asm volatile(
-        "{\n.reg .pred in;\n"
-        "setp.ge.f64 in, %1, %2;\n"
-        "@in st.shared.f64 [%0], %1;\n"
-        "@in add.u32 %0, %0, %3;\n}"
-        : "+r"(p) : "d"(x), "d"(tT), "n"(P_NS * 8) : "memory");
+        "{\n.reg .pred in, st, ov;\n"
+        "setp.ge.f64 in, %2, %3;\n"
+        "setp.ne.and.u32 st, %0, %4, in;\n"
+        "setp.eq.and.u32 ov, %0, %4, in;\n"
+        "@st st.shared.f64 [%0], %2;\n"
+        "@st add.u32 %0, %0, %5;\n"
+        "@ov or.b32 %1, %1, %6;\n}"
+        : "+r"(p), "+r"(ovm) : "d"(x), "d"(tT), "r"(pend), "n"(P_NS * 8), "n"(1 << E) : "memory");
+}
+// A capture that found the thread's private slots full: claim an entry of the shared overflow queue.
+__device__ __noinline__ void pipe_overflow(uint32_t ovn32, uint32_t ovcnt32, uint32_t ovq32, uint32_t ovtag32,
+                                           int i, double x) {
+    unsigned pos;
+    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(ovn32) : "memory");
+    asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(ovcnt32 + 4u * i) : "memory");
+    if (pos < (unsigned)P_OVQ) {
+        sts_f64(ovq32 + pos * 8u, x);
+        sts_u8(ovtag32 + pos, (unsigned)i);
+    }
 }
 
 template <int NB, bool TAIL>
@@ -2040,55 +2044,33 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
             acc.nvalid = st.nv;
         }
     }
-    // Brackets and tail.  Common case: every capturing interval still has four free private slots, so the four
-    // samples are handled by straight-line predicated code (no branches, no overflow test per sample).
-    bool room = true;
-#pragma unroll
-    for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i) room = room && (acc.pend[i] - acc.p[i] >= 4u * P_NS * 8u);
-    if (room) {
-#pragma unroll
-        for (int i = 0; i < NB; ++i) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) cap_bracket(x[e], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i]);
-        }
-        if (TAIL) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e) cap_tail(x[e], fr.tT, acc.p[NB]);
-        }
-        return;
-    }
+    // Brackets and tail: straight-line predicated code; overflowing captures are queued afterwards.
 #pragma unroll
     for (int i = 0; i < NB; ++i) {
-        bool in[4];
-        bool any = false;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const bool lt = x[e] < fr.tA[i];
-            acc.cA[i] += lt ? 1u : 0u;
-            in[e] = !lt && (x[e] < fr.tB[i]);
-            any = any || in[e];
-        }
-        if (any) {
+        unsigned ovm = 0;
+        cap_bracket<0>(x[0], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
+        cap_bracket<1>(x[1], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
+        cap_bracket<2>(x[2], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
+        cap_bracket<3>(x[3], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
+        if (ovm) {
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                if (in[e]) pipe_capture(c, acc.p[i], acc.pend[i], i, x[e], lane);
+                if ((ovm >> e) & 1u) pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, i, x[e]);
         }
     }
     if (TAIL) {
-        constexpr int i = NB;
-        bool in[4];
-        bool any = false;
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            in[e] = x[e] >= fr.tT;
-            any = any || in[e];
-        }
-        if (any) {
+        unsigned ovm = 0;
+        cap_tail<0>(x[0], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        cap_tail<1>(x[1], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        cap_tail<2>(x[2], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        cap_tail<3>(x[3], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        if (ovm) {
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                if (in[e]) pipe_capture(c, acc.p[i], acc.pend[i], i, x[e], lane);
+                if ((ovm >> e) & 1u) pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, NB, x[e]);
         }
     }
+    (void)lane;
 }
 
 template <int NB, bool TAIL>
