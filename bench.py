@@ -178,15 +178,18 @@ def run_ours(args, rank, world, local_rank):
         rollup.series_rollup_dev(d_values.data_ptr(), d_offsets.data_ptr(), n_series, QS, outs["sum"].data_ptr(),
                                  outs["mean"].data_ptr(), outs["min"].data_ptr(), outs["max"].data_ptr(),
                                  outs["last"].data_ptr(), d_count.data_ptr(), d_quant.data_ptr(), stream)
-        if world > 1:   # fleet-wide p95 of the per-node mean CPU usage: histogram all-gather + refine
+        if world > 1:   # fleet-wide p95 of the per-node mean CPU usage
             node_vals = outs["mean"][node_idx].contiguous()
-            nv = int((node_vals == node_vals).sum().item())
+            if n_nodes <= fleet.SMALL_FLEET_CAP:     # few values: one all-gather, select on the host
+                fleet_q[0] = fleet.fleet_quantile_small(node_vals, 0.95, n_nodes, dist, dev)
+            else:                                    # histogram all-gather, refined 16 bits per round
+                nv = int((node_vals == node_vals).sum().item())
 
-            def hist_fn(shift, mask, prefix):
-                rollup.key_histogram_dev(node_vals.data_ptr(), node_vals.numel(), shift, mask, prefix,
-                                         d_hist.data_ptr(), stream)
-                return d_hist
-            fleet_q[0] = fleet.fleet_quantile(hist_fn, nv, 0.95, dist, dev)
+                def hist_fn(shift, mask, prefix):
+                    rollup.key_histogram_dev(node_vals.data_ptr(), node_vals.numel(), shift, mask, prefix,
+                                             d_hist.data_ptr(), stream)
+                    return d_hist
+                fleet_q[0] = fleet.fleet_quantile(hist_fn, nv, 0.95, dist, dev)
 
     def sync_all():
         if world > 1:
@@ -278,7 +281,7 @@ def run_ours(args, rank, world, local_rank):
                        "series_per_rank": n_series, "samples_per_series": L, "samples_per_rank": samples,
                        "quantiles": QS, "stats": ["sum", "mean", "min", "max", "last", "count"],
                        "l2": "inputs (%.2f GB per rank) are larger than the 126 MB L2; no flush needed" % (samples * 8 / 1e9),
-                       "multi_gpu": "fleet p95 of per-node mean CPU usage via NCCL all-gather of key histograms"
+                       "multi_gpu": "fleet p95 of per-node mean CPU usage: one NCCL all-gather of the per-node means (histogram rounds above 65536 nodes per rank)"
                                     if world > 1 else "none (N=1: no NCCL)",
                        "data_gen": "torch on device, distributions of kubeoperator_b200/synth.py"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -8,8 +8,10 @@
  *
  * Conventions
  *   - All buffers are caller-allocated, C-contiguous, native endian.  `*_dev` entry points take DEVICE
- *     pointers and a CUDA stream (as void*) and never synchronise; the others take HOST pointers, do
- *     their own H2D/D2H and return when the outputs are valid.
+ *     pointers and a CUDA stream (as void*) and only enqueue work (one exception: ko_series_rollup_dev with
+ *     more than 16384 series, and ko_series_rollup_static with more than 2048, wait once on the stream to
+ *     read back how many of them are long); the others take HOST pointers, do their own H2D/D2H and
+ *     return when the outputs are valid.
  *   - Return 0 (KO_OK) or a negative KO_E* code; ko_last_error() gives the message (thread-local,
  *     library-owned).  There is NO CPU fallback: without a CUDA device every compute call fails.
  *   - CUDA is initialised lazily inside ko_init(), never at load time, so the library may be dlopen'ed
@@ -117,7 +119,7 @@ int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_o
  * thread that cannot afford the device-wide synchronisation hidden in cudaMalloc / cudaFree, or any section of
  * a program in which the CUDA allocator is off limits.  This entry point has NO COUNTERPART IN THE REFERENCE
  * (and needs no ko_ctx): the work list and counters that ko_series_rollup_dev keeps in memory it cudaMallocs on
- * demand live here in a fixed array inside the library image, 4*(8+2*KO_STATIC_MAX_SERIES) bytes = 512 KiB,
+ * demand live here in a fixed array inside the library image (series lists, 4*(8+2*KO_STATIC_MAX_SERIES) bytes, plus a window of 2048 plans: 1.7 MiB),
  * which every GPU that loads the library holds until the process exits.  It calls no cudaMalloc, cudaFree or
  * other allocating routine.  Limits and rules:
  *   - n_series > KO_STATIC_MAX_SERIES is refused with KO_EINVAL (split the batch);

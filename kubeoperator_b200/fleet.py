@@ -75,6 +75,32 @@ def fleet_quantile(hist_fn, n_valid_local, q, dist=None, device="cpu"):
     return key_to_double(prefix) + 0.0
 
 
+SMALL_FLEET_CAP = 1 << 16
+
+
+def fleet_quantile_small(values, q, cap, dist=None, device="cpu"):
+    """Exact nearest-rank quantile over all shards when every shard holds at most ``cap`` values (the same
+    ``cap`` on every rank, <= SMALL_FLEET_CAP): ONE all-gather of the NaN-padded values and a selection on the
+    host, instead of the four histogram rounds of fleet_quantile (each a collective and a host sync).  NaN =
+    no value, as everywhere in the rollup.  Same result as fleet_quantile."""
+    import torch
+    assert 0 < cap <= SMALL_FLEET_CAP
+    v = torch.as_tensor(values, dtype=torch.float64, device=device).reshape(-1)
+    assert v.numel() <= cap
+    buf = torch.full((cap,), float("nan"), dtype=torch.float64, device=device)
+    buf[:v.numel()] = v
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        out = torch.empty(dist.get_world_size() * cap, dtype=torch.float64, device=device)
+        dist.all_gather_into_tensor(out, buf)
+        buf = out
+    allv = buf.cpu().numpy()
+    allv = allv[allv == allv]
+    if allv.size == 0:
+        return float("nan")
+    r = max(1, min(allv.size, int(math.ceil(q * allv.size))))
+    return float(np.partition(allv, r - 1)[r - 1]) + 0.0
+
+
 def fleet_topk(local_keys, local_global_idx, k, dist=None, device="cpu"):
     """Global indices of the fleet's top-k by (key descending, global index ascending) — the order
     quick_sort_pods gives on the concatenated list (api.py:495-500), truncated to k.  ``local_keys`` /

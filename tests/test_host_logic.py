@@ -55,6 +55,7 @@ def _worker(rank, world, port, q_out):
     for q in (0.5, 0.95, 0.99, 1.0):
         res[q] = fleet.fleet_quantile(lambda s, m, p: ro.key_histogram_np(mine, s, m, p),
                                       int((mine == mine).sum()), q, dist)
+        res[("small", q)] = fleet.fleet_quantile_small(mine, q, 4096, dist)   # one all-gather instead of four rounds
     keys = rng.integers(0, 9, 400)
     lo, hi = fleet.shard_range(len(keys), rank, world)
     order = ro.stable_desc_order_np(keys[lo:hi])[:10]
@@ -82,12 +83,15 @@ def test_fleet_merge_gloo_world2():
     allv = np.concatenate([rng.beta(2, 5, 5001), [np.nan, np.nan, 0.0, -0.0, 7.5]])
     for qv in (0.5, 0.95, 0.99, 1.0):
         assert res[qv] == ro.fleet_quantile([allv], qv)
+        assert res[("small", qv)] == res[qv]
     keys = rng.integers(0, 9, 400)
     assert res["topk"] == ro.stable_desc_order_np(keys)[:10].tolist()
     assert res["sum"] == [3.0, 4.0]
 
 
 def test_fleet_quantile_empty_and_single():
+    assert np.isnan(fleet.fleet_quantile_small(np.array([np.nan, np.nan]), 0.5, 8))
+    assert fleet.fleet_quantile_small(np.array([3.25]), 0.99, 8) == 3.25
     assert np.isnan(fleet.fleet_quantile(lambda s, m, p: np.zeros(65536, np.int64), 0, 0.5))
     v = np.array([3.25])
     assert fleet.fleet_quantile(lambda s, m, p: ro.key_histogram_np(v, s, m, p), 1, 0.99) == 3.25
