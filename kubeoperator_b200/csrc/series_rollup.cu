@@ -1940,6 +1940,18 @@ __device__ __forceinline__ bool any_gt4(double a, double b, double c, double d, 
         : "=r"(r) : "d"(a), "d"(b), "d"(c), "d"(d), "d"(m));
     return r != 0;
 }
+// t is NaN, or one of a..d is below mn or above mx: one predicate for the three rare events of a step
+__device__ __forceinline__ bool rare4(double t, double a, double b, double c, double d, double mn, double mx) {
+    unsigned r;
+    asm("{\n.reg .pred p, q, n;\nsetp.neu.f64 n, %1, %1;\n"
+        "setp.lt.f64 p, %2, %6;\nsetp.gt.f64 q, %2, %7;\n"
+        "setp.lt.or.f64 p, %3, %6, p;\nsetp.gt.or.f64 q, %3, %7, q;\n"
+        "setp.lt.or.f64 p, %4, %6, p;\nsetp.gt.or.f64 q, %4, %7, q;\n"
+        "setp.lt.or.f64 p, %5, %6, p;\nsetp.gt.or.f64 q, %5, %7, q;\n"
+        "or.pred p, p, q;\nor.pred p, p, n;\nselp.u32 %0, 1, 0, p;\n}"
+        : "=r"(r) : "d"(t), "d"(a), "d"(b), "d"(c), "d"(d), "d"(mn), "d"(mx));
+    return r != 0;
+}
 __device__ __noinline__ double rare_min4(double m, double a, double b, double c, double d) {
     return fmin(fmin(m, fmin(a, b)), fmin(c, d));
 }
@@ -1966,9 +1978,9 @@ __device__ __noinline__ Stats4 rare_nan4(Stats4 st, double a, double b, double c
 
 // One sample against a bracket / the upper tail, as predicated PTX (the compiler's own lowering of the same C++
 // spends two instructions per conditional count).  p is the shared-memory address of the thread's next free
-// private slot, pend the end of its slots; a sample that finds them full sets bit E of ovm and is queued by the
+// private slot, pend the end of its slots; a sample that finds them full sets BIT in ovm and is queued by the
 // caller (rare), so that the common path has no branch per sample and no "is there room" test per step.
-template <int E>
+template <int BIT>
 __device__ __forceinline__ void cap_bracket(double x, double tA, double tB, unsigned& cA, uint32_t& p, uint32_t pend,
                                             unsigned& ovm) {
     asm volatile(
@@ -1981,9 +1993,9 @@ __device__ __forceinline__ void cap_bracket(double x, double tA, double tB, unsi
         "@st st.shared.f64 [%1], %3;\n"
         "@st add.u32 %1, %1, %7;\n"
         "@ov or.b32 %2, %2, %8;\n}"
-        : "+r"(cA), "+r"(p), "+r"(ovm) : "d"(x), "d"(tA), "d"(tB), "r"(pend), "n"(P_NS * 8), "n"(1 << E) : "memory");
+        : "+r"(cA), "+r"(p), "+r"(ovm) : "d"(x), "d"(tA), "d"(tB), "r"(pend), "n"(P_NS * 8), "n"(BIT) : "memory");
 }
-template <int E>
+template <int BIT>
 __device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p, uint32_t pend, unsigned& ovm) {
     asm volatile(
         "{\n.reg .pred in, st, ov;\n"
@@ -1993,7 +2005,7 @@ __device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p, uint3
         "@st st.shared.f64 [%0], %2;\n"
         "@st add.u32 %0, %0, %5;\n"
         "@ov or.b32 %1, %1, %6;\n}"
-        : "+r"(p), "+r"(ovm) : "d"(x), "d"(tT), "r"(pend), "n"(P_NS * 8), "n"(1 << E) : "memory");
+        : "+r"(p), "+r"(ovm) : "d"(x), "d"(tT), "r"(pend), "n"(P_NS * 8), "n"(BIT) : "memory");
 }
 // A capture that found the thread's private slots full: claim an entry of the shared overflow queue.
 __device__ __noinline__ void pipe_overflow(uint32_t ovn32, uint32_t ovcnt32, uint32_t ovq32, uint32_t ovtag32,
@@ -2022,18 +2034,25 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
     // warps take the maximum from there.
     {
         const double t = (x[0] + x[1]) + (x[2] + x[3]);
-        if (t == t) {
+        if (NB > 0 || TAIL) {   // seeded: one test (and one branch) for "a NaN, a new minimum or a new maximum"
+            if (!rare4(t, x[0], x[1], x[2], x[3], acc.mn, acc.mx)) {
+                acc.sum += t;
+                acc.nvalid += 4;
+            } else {
+                Stats4 st = {acc.sum, acc.mn, acc.mx, acc.nvalid};
+                st = rare_nan4(st, x[0], x[1], x[2], x[3]);
+                acc.sum = st.sum;
+                acc.mn = st.mn;
+                acc.mx = st.mx;
+                acc.nvalid = st.nv;
+            }
+        } else if (t == t) {
             acc.sum += t;
             acc.nvalid += 4;
-            if (NB > 0 || TAIL) {   // seeded
-                if (any_lt4(x[0], x[1], x[2], x[3], acc.mn)) acc.mn = rare_min4(acc.mn, x[0], x[1], x[2], x[3]);
-                if (any_gt4(x[0], x[1], x[2], x[3], acc.mx)) acc.mx = rare_max4(acc.mx, x[0], x[1], x[2], x[3]);
-            } else {
 #pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    if (x[e] < acc.mn) acc.mn = x[e];
-                    if (x[e] > acc.mx) acc.mx = x[e];
-                }
+            for (int e = 0; e < 4; ++e) {
+                if (x[e] < acc.mn) acc.mn = x[e];
+                if (x[e] > acc.mx) acc.mx = x[e];
             }
         } else {
             Stats4 st = {acc.sum, acc.mn, acc.mx, acc.nvalid};
@@ -2044,31 +2063,33 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
             acc.nvalid = st.nv;
         }
     }
-    // Brackets and tail: straight-line predicated code; overflowing captures are queued afterwards.
-#pragma unroll
-    for (int i = 0; i < NB; ++i) {
-        unsigned ovm = 0;
-        cap_bracket<0>(x[0], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
-        cap_bracket<1>(x[1], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
-        cap_bracket<2>(x[2], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
-        cap_bracket<3>(x[3], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
-        if (ovm) {
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                if ((ovm >> e) & 1u) pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, i, x[e]);
-        }
+    // Brackets and tail: straight-line predicated code; overflowing captures (bit 4*interval + sample of ovm) are
+    // queued afterwards.
+    unsigned ovm = 0;
+#define KO_CAP_BRACKET(i)                                                                                        \
+    cap_bracket<(1 << (4 * (i) + 0))>(x[0], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);            \
+    cap_bracket<(1 << (4 * (i) + 1))>(x[1], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);            \
+    cap_bracket<(1 << (4 * (i) + 2))>(x[2], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);            \
+    cap_bracket<(1 << (4 * (i) + 3))>(x[3], fr.tA[i], fr.tB[i], acc.cA[i], acc.p[i], acc.pend[i], ovm);
+    if (NB > 0) {
+        KO_CAP_BRACKET(0)
     }
+    if (NB > 1) {
+        KO_CAP_BRACKET(NB > 1 ? 1 : 0)
+    }
+#undef KO_CAP_BRACKET
     if (TAIL) {
-        unsigned ovm = 0;
-        cap_tail<0>(x[0], fr.tT, acc.p[NB], acc.pend[NB], ovm);
-        cap_tail<1>(x[1], fr.tT, acc.p[NB], acc.pend[NB], ovm);
-        cap_tail<2>(x[2], fr.tT, acc.p[NB], acc.pend[NB], ovm);
-        cap_tail<3>(x[3], fr.tT, acc.p[NB], acc.pend[NB], ovm);
-        if (ovm) {
+        cap_tail<(1 << (4 * NB + 0))>(x[0], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        cap_tail<(1 << (4 * NB + 1))>(x[1], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        cap_tail<(1 << (4 * NB + 2))>(x[2], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+        cap_tail<(1 << (4 * NB + 3))>(x[3], fr.tT, acc.p[NB], acc.pend[NB], ovm);
+    }
+    if (ovm) {
+#pragma unroll
+        for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i)
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-                if ((ovm >> e) & 1u) pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, NB, x[e]);
-        }
+                if ((ovm >> (4 * i + e)) & 1u) pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, i, x[e]);
     }
     (void)lane;
 }
