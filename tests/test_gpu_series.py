@@ -156,6 +156,59 @@ def test_few_distinct_values(rollup):
         assert_series_parity(got, exp, values, offsets, qs)
 
 
+def test_more_long_series_than_one_plan_window(rollup):
+    """20 000 long series: the plans are built in windows of 16 384 (the call reads back the number of long
+    series once), and the static entry point's window is 2 048."""
+    import torch
+    from kubeoperator_b200 import korollup
+    rng = np.random.default_rng(12)
+    n, L = 20000, 1100
+    values = rng.beta(2.0, 5.0, n * L)
+    values[rng.random(n * L) < 1e-3] = np.nan
+    values[::7] = np.floor(values[::7] * 50)          # some repeated values
+    offsets = np.arange(n + 1, dtype=np.int64) * L
+    got = rollup.series_rollup(values, offsets, QS)
+    exp = c_oracle.series_rollup(values, offsets, QS, nthreads=8)
+    assert_series_parity(got, exp, values, offsets, QS)
+    # the no-allocation entry point over 5 000 of them (three windows of 2 048)
+    m = 5000
+    dv, do = torch.from_numpy(values[:m * L]).cuda(), torch.from_numpy(offsets[:m + 1]).cuda()
+    qt = torch.zeros((m, 3), dtype=torch.float64, device="cuda")
+    cnt = torch.zeros(m, dtype=torch.int64, device="cuda")
+    korollup.series_rollup_static(0, dv.data_ptr(), do.data_ptr(), m, QS, 0, 0, 0, 0, 0, cnt.data_ptr(),
+                                  qt.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert np.array_equal(cnt.cpu().numpy(), exp["count"][:m])
+    assert np.array_equal(_bits(qt.cpu().numpy()), _bits(exp["quantiles"][:m]))
+
+
+def test_brackets_that_miss_overflow_or_are_skewed(rollup):
+    """Series built to defeat the pre-sample: the wanted ranks lie where the 1024 strided sample points say
+    nothing (second attempt with wide brackets, then the slow path), candidates pile up in one sub-bracket
+    (cut again), and three separate brackets at once."""
+    rng = np.random.default_rng(13)
+    L = 40960                                           # sample stride 40: positions 20, 60, 100, ...
+    idx = np.arange(L)
+    on_sample = (idx % 40) == 20
+    series = [
+        np.where(on_sample, rng.random(L), 5.0 + rng.random(L)),          # the sample sees only the low 2.5 %
+        np.where(on_sample, 5.0 + rng.random(L), rng.random(L)),          # ... only the high 2.5 %
+        np.where(on_sample, 1.0, rng.random(L) * 1e-3),                   # sample is constant, data is not
+        np.concatenate([rng.random(L // 2), 1.0 + 1e-9 * rng.random(L - L // 2)]),   # half the mass in a sliver
+        np.where(rng.random(L) < 0.5, 0.25 + 1e-12 * rng.integers(0, 300, L), rng.random(L)),   # dense cluster at p50
+        np.exp(rng.normal(0, 4, L)),                                      # heavy tail: tail sub-brackets are skewed
+        -np.exp(rng.normal(0, 4, L)),
+        rng.standard_cauchy(L),
+        np.where(rng.random(L) < 0.4, np.floor(rng.random(L) * 3), rng.random(L) * 3),   # levels mixed with noise
+    ]
+    offsets = np.arange(len(series) + 1, dtype=np.int64) * L
+    values = np.concatenate(series)
+    for qs in (QS, [0.1, 0.5, 0.99], [0.02, 0.5, 0.98, 0.999], [0.5], [0.999], [0.3, 0.35]):
+        got = rollup.series_rollup(values, offsets, qs)
+        exp = c_oracle.series_rollup(values, offsets, qs, nthreads=8)
+        assert_series_parity(got, exp, values, offsets, qs)
+
+
 def test_very_long_series_refinement_passes(rollup):
     # 30 days at 15 s (config 3/4 length): the brackets do not fit shared memory -> histogram refinement
     d = synth.make_series(dict(nodes=1, gpus=1, pods=1, L=172800), seed=6)
