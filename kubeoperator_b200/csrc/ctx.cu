@@ -90,6 +90,8 @@ int ko_init(const int* devices, int n_devices, ko_ctx** out) {
     }
     KO_CUDA(cudaEventCreate(&ctx->ev_k0));
     KO_CUDA(cudaEventCreate(&ctx->ev_k1));
+    KO_CUDA(cudaEventCreate(&ctx->ev_p0));
+    KO_CUDA(cudaEventCreate(&ctx->ev_p1));
     ctx->alive = true;
     *out = ctx;
     return KO_OK;
@@ -114,6 +116,8 @@ void ko_destroy(ko_ctx* ctx) {
         }
         cudaEventDestroy(ctx->ev_k0);
         cudaEventDestroy(ctx->ev_k1);
+        cudaEventDestroy(ctx->ev_p0);
+        cudaEventDestroy(ctx->ev_p1);
         cudaStreamDestroy(ctx->stream);
         cudaStreamDestroy(ctx->copy_stream);
     }
@@ -133,6 +137,15 @@ int ko_last_series_kernel_ms(ko_ctx* ctx, float* out_ms) {
     KO_REQUIRE(ctx->k_timed, "ko_last_series_kernel_ms: no series rollup has been launched yet");
     KO_CUDA(cudaEventSynchronize(ctx->ev_k1));
     KO_CUDA(cudaEventElapsedTime(out_ms, ctx->ev_k0, ctx->ev_k1));
+    return KO_OK;
+}
+
+int ko_last_series_pipe_ms(ko_ctx* ctx, float* out_ms) {
+    KO_REQUIRE(ctx && out_ms, "ko_last_series_pipe_ms: NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_REQUIRE(ctx->k_timed, "ko_last_series_pipe_ms: no series rollup has been launched yet");
+    KO_CUDA(cudaEventSynchronize(ctx->ev_k1));
+    KO_CUDA(cudaEventElapsedTime(out_ms, ctx->ev_p0, ctx->ev_p1));
     return KO_OK;
 }
 

@@ -44,7 +44,8 @@ struct ko_ctx {
     cudaStream_t copy_stream = nullptr;  // H2D stream of the chunked series pipeline
     cudaEvent_t ev_copied[2] = {nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr};
-    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the last series_long launch (roofline timing)
+    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the long-series kernels of the last series rollup
+    cudaEvent_t ev_p0 = nullptr, ev_p1 = nullptr;  // around its first series_pipe launch alone (roofline timing)
     bool k_timed = false;
     KoBuf scratch;       // work lists / counters / sort buffers (kernel scratch)
     KoBuf stage[2];      // double-buffered device staging of series values

@@ -2995,7 +2995,8 @@ constexpr size_t series_lists_bytes(int64_t n_series) { return ((size_t)(8 + 2 *
 // One window covers n_series <= plan_cap.  Beyond that the number of long series is read back from the device
 // (one stream synchronisation) so that only the windows that hold work are launched.
 static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series, void* plans, int plan_cap,
-                                    cudaStream_t st, int* launches) {
+                                    cudaStream_t st, int* launches, cudaEvent_t ev_p0 = nullptr,
+                                    cudaEvent_t ev_p1 = nullptr) {
     int pgrid = num_sms;
     if ((int64_t)pgrid > n_series) pgrid = (int)n_series;
     int grid = 2 * num_sms;
@@ -3022,8 +3023,14 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
         a.w_begin = w0;
         const int pg = (int)((cnt + PLAN_WARPS - 1) / PLAN_WARPS);
         series_plan<<<pg < 4 * num_sms ? pg : 4 * num_sms, PLAN_WARPS * 32, 0, st>>>(a);
+        if (w0 == 0 && ev_p0) cudaEventRecord(ev_p0, st);
         series_pipe<<<(int64_t)pgrid < cnt ? pgrid : (int)cnt, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
+        if (w0 == 0 && ev_p1) cudaEventRecord(ev_p1, st);
         *launches += 2;
+    }
+    if (n_long <= 0 && ev_p0) {   // nothing long: an empty interval
+        cudaEventRecord(ev_p0, st);
+        cudaEventRecord(ev_p1, st);
     }
     if (a.nq > 0) {
         a.work_list = a.defer_list;
@@ -3103,7 +3110,8 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     KO_CUDA(cudaEventRecord(ctx->ev_k0, stream));
     int launches = 2;
     void* plans = reinterpret_cast<unsigned char*>(d_scratch) + series_lists_bytes(n_series);
-    KO_CUDA(launch_long_path(a, ctx->num_sms, n_series, plans, PLAN_CAP_CTX, stream, &launches));
+    KO_CUDA(launch_long_path(a, ctx->num_sms, n_series, plans, PLAN_CAP_CTX, stream, &launches, ctx->ev_p0,
+                             ctx->ev_p1));
     KO_CUDA(cudaEventRecord(ctx->ev_k1, stream));
     ctx->k_timed = true;
     KO_CUDA(cudaGetLastError());

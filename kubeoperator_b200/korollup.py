@@ -31,6 +31,7 @@ ABI = {
     "ko_destroy": [_c_vp],
     "ko_get_counters": [_c_vp, _c_vp],
     "ko_last_series_kernel_ms": [_c_vp, _c_vp],
+    "ko_last_series_pipe_ms": [_c_vp, _c_vp],
     "ko_pin": [_c_vp, _c_i64],
     "ko_unpin": [_c_vp],
     "ko_cluster_rollup": [_c_vp] + [_c_vp] * 5 + [_c_i64, _c_i32, _c_dbl] + [_c_vp] * 8,
@@ -155,6 +156,12 @@ class Rollup:
     def last_series_kernel_ms(self):
         ms = ctypes.c_float(0)
         self._check(self._lib.ko_last_series_kernel_ms(self._ctx, ctypes.byref(ms)))
+        return float(ms.value)
+
+    def last_series_pipe_ms(self):
+        """Device time of the dominant kernel alone (first series_pipe launch of the last series rollup)."""
+        ms = ctypes.c_float(0)
+        self._check(self._lib.ko_last_series_pipe_ms(self._ctx, ctypes.byref(ms)))
         return float(ms.value)
 
     def pin(self, array):
