@@ -322,6 +322,70 @@ __device__ unsigned long long warp_radix_select(const unsigned long long* keys, 
     }
 }
 
+// Short windows (<= 256 samples, e.g. 5 min .. 1 h at 15 s): the warp sorts the series' keys in registers, K per
+// lane (sorted position p lives in lane p / K, register p % K), with a bitonic network of shuffles; every
+// quantile is then a single register read.  Stale samples carry KO_KEY_NAN and sort to the end.
+template <int K>
+__device__ __forceinline__ void warp_sort_keys(unsigned long long (&r)[K], int lane) {
+    constexpr int N = 32 * K;
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= K) {   // partner in another lane
+                const int m = j / K;
+                const bool lower = (lane & m) == 0;
+#pragma unroll
+                for (int e = 0; e < K; ++e) {
+                    const bool up = (((lane * K) | e) & k) == 0;
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, r[e], m);
+                    const unsigned long long lo = r[e] < o ? r[e] : o, hi = r[e] < o ? o : r[e];
+                    r[e] = (lower == up) ? lo : hi;
+                }
+            } else {        // partner in another register of the same lane
+#pragma unroll
+                for (int e = 0; e < K; ++e) {
+                    if ((e & j) == 0) {
+                        const bool up = (((lane * K) | e) & k) == 0;
+                        const unsigned long long x0 = r[e], x1 = r[e | j];
+                        const unsigned long long lo = x0 < x1 ? x0 : x1, hi = x0 < x1 ? x1 : x0;
+                        r[e] = up ? lo : hi;
+                        r[e | j] = up ? hi : lo;
+                    }
+                }
+            }
+        }
+    }
+}
+template <int K>
+__device__ __forceinline__ void small_sorted_quantiles(const SeriesArgs& a, const double* v, int L, unsigned nv,
+                                                       int64_t sid, int lane) {
+    unsigned long long r[K];
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        const int i = lane + 32 * e;   // coalesced; which register holds which sample does not matter before the sort
+        double x = __longlong_as_double(0x7FF8000000000000LL);
+        if (i < L) x = ko_ld_stream(v + i);
+        r[e] = (x == x) ? ko_okey(x + 0.0) : KO_KEY_NAN;
+    }
+    warp_sort_keys<K>(r, lane);
+#pragma unroll
+    for (int j = 0; j < NI_MAX; ++j) {
+        if (j < a.nq) {
+            double res = __longlong_as_double(0x7FF8000000000000LL);
+            if (nv > 0) {
+                const int p = (int)nearest_rank_dev(nv, a.q[j]) - 1;
+                unsigned long long mine = 0;
+#pragma unroll
+                for (int e = 0; e < K; ++e)
+                    if (e == (p % K)) mine = r[e];
+                res = ko_key2d(__shfl_sync(0xffffffffu, mine, p / K));
+            }
+            if (lane == 0) a.out_quant[sid * a.nq + a.qcol[j]] = res;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
     extern __shared__ __align__(16) unsigned char smem_small[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -351,7 +415,7 @@ __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
         }
         mn = fmin(mn, x);
         mx = fmax(mx, x);
-        if (keys) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
+        if (keys && L > 256) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
     }
     sum = warp_sum(sum);
     mn = warp_min(mn);
@@ -368,7 +432,12 @@ __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
         if (a.out_last) a.out_last[sid] = last_idx >= 0 ? v[last_idx] : nan;
         if (a.out_count) a.out_count[sid] = (int64_t)nv;
     }
-    if (a.nq > 0 && a.out_quant) {
+    if (a.nq > 0 && a.out_quant && L <= 256) {   // sorted in registers (the samples are re-read: they sit in L1)
+        if (L <= 32) small_sorted_quantiles<1>(a, v, L, nv, sid, lane);
+        else if (L <= 64) small_sorted_quantiles<2>(a, v, L, nv, sid, lane);
+        else if (L <= 128) small_sorted_quantiles<4>(a, v, L, nv, sid, lane);
+        else small_sorted_quantiles<8>(a, v, L, nv, sid, lane);
+    } else if (a.nq > 0 && a.out_quant) {
         __syncwarp();
         const unsigned long long kmin = ko_okey(mn + 0.0), kmax = ko_okey(mx + 0.0);
         for (int j = 0; j < a.nq; ++j) {
