@@ -1935,6 +1935,7 @@ __global__ void __launch_bounds__(PLAN_WARPS * 32) series_plan(SeriesArgs a) {
     const long long hi = n_items < a.w_begin + a.plan_cap ? n_items : a.w_begin + a.plan_cap;
     const long long gw = (long long)blockIdx.x * PLAN_WARPS + warp, nw = (long long)gridDim.x * PLAN_WARPS;
     PipePlan* pp = &sp[warp];
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.counters[a.work_cur] = 0;   // cursor of the series_pipe launch that follows
     for (long long w = a.w_begin + gw; w < hi; w += nw) {
         const int item = a.wide ? (int)(w / a.nq) : (int)w;
         const int qsel = a.wide ? (int)(w - (long long)item * a.nq) : -1;
@@ -2874,14 +2875,15 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
 
     if (warp < P_PW) {
         // ================================================================ PLAN LOADER
-        // Work items are dealt to the CTAs round-robin (ordinal k of this CTA is item w_begin + blockIdx.x +
-        // k * gridDim.x); their plans, written by series_plan, are fetched into the plan slots with bulk copies.
+        // Work items come from a global cursor (reset by series_plan); their plans, written by series_plan, are
+        // fetched into the plan slots with bulk copies.
         if (lane == 0) {
             const long long hi = n_long < a.w_begin + a.plan_cap ? n_long : a.w_begin + a.plan_cap;
             for (uint32_t k = 0;; ++k) {
                 const uint32_t slot = k & (P_PLANS - 1);
                 mbar_wait_sleep(sm.bars() + B_PLAN_FREE + slot, ((k >> P_PLAN_LOG) & 1u) ^ 1u);
-                const long long w = a.w_begin + (long long)blockIdx.x + (long long)k * gridDim.x;
+                // items are handed out one at a time (series differ in cost: levels plans, second attempts)
+                const long long w = a.w_begin + (long long)atomicAdd(&a.counters[a.work_cur], 1);
                 PipePlan* pp = sm.plan(slot);
                 if (w >= hi) {
                     pp->sid = -1;
@@ -3107,6 +3109,7 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
         a.out_list = a.long_list;   // the first list is no longer needed
         a.out_cnt = 6;
         a.wide = 1;
+        a.work_cur = 5;
         a.w_begin = 0;
         series_plan<<<num_sms, PLAN_WARPS * 32, 0, st>>>(a);
         series_pipe<<<pgrid, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
