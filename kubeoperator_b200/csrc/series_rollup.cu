@@ -242,11 +242,7 @@ __device__ __forceinline__ double warp_max(double v) {
     for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
-__device__ __forceinline__ unsigned warp_sum_u(unsigned v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
+__device__ __forceinline__ unsigned warp_sum_u(unsigned v) { return __reduce_add_sync(0xffffffffu, v); }
 
 // Locate the digit whose cumulative count first reaches rho.  Called by one full warp on a 256-bin
 // histogram; returns (digit, count before the digit, count of the digit) in every lane.
@@ -1882,6 +1878,10 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         if (!defer && !vals && lane == 0) {
             int slot = 0;
             const int spare = P_SLOTS - total;
+            int big = 0;   // the interval with most candidates also takes what an even split leaves over
+#pragma unroll
+            for (int i = 1; i < P_NI; ++i)
+                if (i < ni && need[i] > need[big]) big = i;
 #pragma unroll
             for (int i = 0; i < P_NI; ++i) {
                 if (i < ni) {
@@ -1893,7 +1893,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                     pp->slot0[i] = slot;
                     pp->nslots[i] = 0;
                     if (mode[i] == M_CAPTURE) {
-                        pp->nslots[i] = need[i] + spare / ncap;
+                        pp->nslots[i] = need[i] + spare / ncap + (i == big ? spare % ncap : 0);
                         slot += pp->nslots[i];
                     }
                 }
