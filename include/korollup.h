@@ -180,6 +180,24 @@ int ko_loki_count(ko_ctx* ctx, const uint8_t* buf, const int64_t* line_offsets, 
 int ko_counter_increase(ko_ctx* ctx, const double* values, const int64_t* offsets, int64_t n_series,
                         double step_seconds, double* out_increase, double* out_rate);
 
+/* ---- §8f rank 1: Prometheus HTTP API response -> columnar samples (HOST code, no GPU needed) -------------
+ * The reference reads Prometheus with requests.json() and picks ['data']['result'][0]['value'][1], a string,
+ * one node and one query at a time (prometheus_client.py:91-116; scrape targets :67-72).  These calls turn a
+ * whole response body -- a query_range "matrix" or an instant "vector" -- into the columnar layout the rollup
+ * entry points take: ko_prom_open scans the structure (fails with KO_ESTATE when "status" is not "success",
+ * the reference's guard at :94, and with KO_EINVAL on malformed JSON), ko_prom_dims reports sizes,
+ * ko_prom_fill converts the sample strings (correctly rounded, as Python's float(); "NaN", "+Inf", "-Inf")
+ * into caller buffers -- values[n_samples], optional timestamps[n_samples], offsets[n_series+1], and
+ * optionally the byte range of every series' "metric" object for the caller's label handling -- on
+ * n_threads host threads.  The body must stay valid until ko_prom_close.  Fill straight into a ko_pin()ned
+ * buffer to hand the result to ko_series_rollup without another copy. */
+typedef struct ko_prom_doc ko_prom_doc;
+int ko_prom_open(const char* json, int64_t len, ko_prom_doc** out);
+int ko_prom_dims(const ko_prom_doc* doc, int64_t* n_series, int64_t* n_samples);
+int ko_prom_fill(const ko_prom_doc* doc, double* values, double* timestamps, int64_t* offsets,
+                 int64_t* metric_begin, int64_t* metric_end, int n_threads);
+void ko_prom_close(ko_prom_doc* doc);
+
 #ifdef __cplusplus
 }
 #endif

@@ -46,6 +46,10 @@ ABI = {
     "ko_key_histogram_dev": [_c_vp, _c_vp, _c_i64, _c_int, ctypes.c_uint64, ctypes.c_uint64, _c_vp, _c_vp],
     "ko_loki_count": [_c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_i64, _c_vp],
     "ko_counter_increase": [_c_vp, _c_vp, _c_vp, _c_i64, _c_dbl, _c_vp, _c_vp],
+    "ko_prom_open": [ctypes.c_char_p, _c_i64, ctypes.POINTER(_c_vp)],
+    "ko_prom_dims": [_c_vp, ctypes.POINTER(_c_i64), ctypes.POINTER(_c_i64)],
+    "ko_prom_fill": [_c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_int],
+    "ko_prom_close": [_c_vp],
 }
 
 
@@ -83,6 +87,7 @@ def load_library():
         fn.restype = _c_int
     lib.ko_last_error.restype = ctypes.c_char_p
     lib.ko_destroy.restype = None
+    lib.ko_prom_close.restype = None
     _lib = lib
     return lib
 

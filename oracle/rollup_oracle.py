@@ -398,3 +398,28 @@ def counter_rate(values, step_seconds):
     if first < 0:
         return 0.0
     return inc / ((last - first) * step_seconds)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# §8f rank 1: Prometheus response -> columnar.  Restates what the reference does with a response
+# (core/apps/kubeops_api/prometheus_client.py:91-116: req.json(), status == 'success', result[i]['value'][1]
+# is a STRING that the caller later float()s, cluster_monitor.py:171-182) for whole matrices / vectors.
+def prom_columnar(body):
+    """(values, offsets, timestamps, metrics) of a query / query_range response body; raises ValueError
+    when status is not 'success' (the reference skips the assignment in that case)."""
+    import json as _json
+    doc = _json.loads(body)
+    if doc.get("status") != "success":
+        raise ValueError("status is not success: %s" % doc.get("error"))
+    data = doc.get("data", {})
+    if data.get("resultType") not in ("matrix", "vector"):
+        raise ValueError("resultType %r carries no series" % data.get("resultType"))
+    values, stamps, offsets, metrics = [], [], [0], []
+    for s in data.get("result", []):
+        pairs = s["values"] if "values" in s else ([s["value"]] if "value" in s else [])
+        for t, v in pairs:
+            stamps.append(float(t))
+            values.append(float(v))          # float("NaN"), float("+Inf"), float("-Inf") as Prometheus prints them
+        offsets.append(len(values))
+        metrics.append(s.get("metric", {}))
+    return values, offsets, stamps, metrics
