@@ -2,18 +2,21 @@
 // quantiles.  BUILD-DEFINED semantics (oracle/rollup_oracle.py series_stats); the reference only ships
 // PromQL strings for this (core/apps/kubeops_api/prometheus_client.py:90-111), see include/korollup.h.
 //
-// HBM-bound: 8 algorithmic bytes per sample, read once.  Three kernels per call:
+// HBM-bound by design: 8 algorithmic bytes per sample, read once.  Kernels of one call:
 //   classify_series   — builds the work list of long series (scratch) and validates offsets
-//   series_small      — one warp per series of <= 1024 samples (coalesced streaming loads, shuffle
-//                       reductions, warp-private shared-memory radix select for quantiles)
-//   series_long       — persistent CTAs, one series at a time per CTA: a producer warp streams the series
-//                       through a 4-stage TMA ring (cp.async.bulk + mbarrier) while 8 consumer warps
-//                       fuse the statistics with a bracketed selection: a strided pre-sample (sorted in
-//                       registers / shuffles) gives a value bracket per quantile; the single streaming pass counts
-//                       samples below each bracket and captures the few inside it into shared memory,
-//                       where a shared-memory radix select finds the exact order statistic.  Brackets
-//                       that miss or overflow are refined by further passes (histogram in key space),
-//                       so the result is always exact.
+//   series_small      — one warp per series of <= 1024 samples: coalesced streaming loads, shuffle reductions;
+//                       quantiles from a register bitonic sort (<= 256 samples) or a warp-private shared-memory
+//                       radix select
+//   series_plan       — one warp per long series: a strided 1024-point pre-sample, sorted in registers with
+//                       shuffles, gives a value bracket per quantile (or a list of distinct levels for
+//                       integer-valued series); the plan goes to a window in scratch
+//   series_pipe       — persistent, one CTA of 20 warps per SM, warp-specialised: plan loader, TMA producer
+//                       (cp.async.bulk + mbarrier ring), 12 stream warps that fuse the statistics with "count
+//                       below the bracket, keep what is inside it" in ONE pass, 6 finish warps that select the
+//                       exact order statistic among the kept candidates of the previous series meanwhile
+//   series_pipe again — second attempt with wide brackets over the few quantiles the first could not answer
+//   series_long       — exact multi-pass slow path (histogram refinement in key space) over what is left
+// Every bracket is verified by exact counts, so the result is always the oracle's value.
 #include <math.h>
 
 #include "ko_common.cuh"
@@ -2188,27 +2191,32 @@ __device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const
     const uint32_t full0 = smem_u32(sm.bars() + B_RING_FULL), empty0 = smem_u32(sm.bars() + B_RING_EMPTY);
     const uint32_t ring0 = smem_u32(sm.ring()) + (uint32_t)stid * 16u;
     uint32_t s = g % P_STAGES, par = (g / P_STAGES) & 1u;
-    int rem2 = body >> 1;
-    for (int t = 0; t < ntiles; ++t) {
+    const int nfull = body / P_TILE;   // whole tiles; a last partial one follows when body is not a multiple
+    for (int t = 0; t < nfull; ++t) {
         { KO_PT0(); mbar_wait_addr(full0 + s * 8u, par); KO_PT1(16, stid == 0); }
         const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
         double x[4];
-        if (rem2 >= P_TILE / 2) {
-            lds_v2f64(base, x[0], x[1]);
-            lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        } else {
-            x[0] = x[1] = x[2] = x[3] = nan;
-            if (stid < rem2) lds_v2f64(base, x[0], x[1]);
-            if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        }
+        lds_v2f64(base, x[0], x[1]);
+        lds_v2f64(base + P_NS * 16, x[2], x[3]);
         pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
-        rem2 -= P_TILE / 2;
         if (++s == P_STAGES) {
             s = 0;
             par ^= 1u;
         }
+    }
+    if (nfull < ntiles) {
+        const int rem2 = (body - nfull * P_TILE) >> 1;
+        mbar_wait_addr(full0 + s * 8u, par);
+        const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
+        double x[4];
+        x[0] = x[1] = x[2] = x[3] = nan;
+        if (stid < rem2) lds_v2f64(base, x[0], x[1]);
+        if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
+        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
     }
     g += (uint32_t)ntiles;
 }
@@ -2277,27 +2285,32 @@ __device__ __forceinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc
     const uint32_t full0 = smem_u32(sm.bars() + B_RING_FULL), empty0 = smem_u32(sm.bars() + B_RING_EMPTY);
     const uint32_t ring0 = smem_u32(sm.ring()) + (uint32_t)stid * 16u;
     uint32_t s = g % P_STAGES, par = (g / P_STAGES) & 1u;
-    int rem2 = body >> 1;
-    for (int t = 0; t < ntiles; ++t) {
+    const int nfull = body / P_TILE;   // whole tiles, then the partial one
+    for (int t = 0; t < nfull; ++t) {
         mbar_wait_addr(full0 + s * 8u, par);
         const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
         double x[4];
-        if (rem2 >= P_TILE / 2) {
-            lds_v2f64(base, x[0], x[1]);
-            lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        } else {
-            x[0] = x[1] = x[2] = x[3] = nan;
-            if (stid < rem2) lds_v2f64(base, x[0], x[1]);
-            if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        }
+        lds_v2f64(base, x[0], x[1]);
+        lds_v2f64(base + P_NS * 16, x[2], x[3]);
         pipe_levels4(x, acc, thr32, col32);
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
-        rem2 -= P_TILE / 2;
         if (++s == P_STAGES) {
             s = 0;
             par ^= 1u;
         }
+    }
+    if (nfull < ntiles) {
+        const int rem2 = (body - nfull * P_TILE) >> 1;
+        mbar_wait_addr(full0 + s * 8u, par);
+        const uint32_t base = ring0 + s * (uint32_t)(P_TILE * 8);
+        double x[4];
+        x[0] = x[1] = x[2] = x[3] = nan;
+        if (stid < rem2) lds_v2f64(base, x[0], x[1]);
+        if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
+        pipe_levels4(x, acc, thr32, col32);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
     }
     g += (uint32_t)ntiles;
 }
