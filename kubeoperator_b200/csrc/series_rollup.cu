@@ -1448,19 +1448,21 @@ __global__ void __launch_bounds__(NTHREADS, 2) series_long(SeriesArgs a) {
 #define KO_PT1(slot, cond) do { } while (0)
 #endif
 constexpr int P_SW = 12;                       // stream warps
-constexpr int P_FW = 6;                        // finish warps
+constexpr int P_FW = 8;                        // finish warps
 constexpr int P_NS = P_SW * 32;                // 384 stream threads
 constexpr int P_NF = P_FW * 32;                // 128 finish threads
 constexpr int P_PW = 1;                        // plan loader warp
-constexpr int P_PLANS = 8;                     // plan slots (a plan takes longer to build than a series to stream)
-constexpr uint32_t P_PLAN_LOG = 3;
+constexpr int P_PLANS = 4;                     // plan slots
+constexpr uint32_t P_PLAN_LOG = 2;
 constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW) * 32;   // planners, producer, stream, finish
 constexpr int P_TILE = 4 * P_NS;               // 1536 doubles (12 KB) per ring stage
 constexpr int P_STAGES = 3;
 constexpr int P_SLOTS = 24;                    // thread-private candidate slots per stream thread
-constexpr int P_OVQ = 768;                     // overflow queue entries per pool
+constexpr int P_OVQ = 640;                     // overflow queue entries per pool
 constexpr int P_NI = 3;                        // at most 2 brackets + 1 upper tail
-static_assert(P_NS == 2 * P_NF && P_NF % 96 == 0, "finish groups of P_NF/1, /2, /3 threads own whole column pairs");
+// finish groups: all P_NF threads for one capturing interval, halves for two, three groups of 64 threads for three
+static_assert(P_NF >= 192 && P_NF % 64 == 0 && P_NS % 64 == 0, "group sizes");
+__host__ __device__ constexpr int fin_group_size(int ng) { return ng == 3 ? 64 : P_NF / ng; }
 constexpr int P_LIST = 256;                    // candidates of one sub-bracket kept for the final rank counting
 constexpr int P_SAMPLE = 1024;
 constexpr int P_CROW = P_NF + 4;               // bytes per row of the finish warps' counters
@@ -2369,13 +2371,16 @@ struct FinIv {
 template <int NG, typename F4, typename F1>
 __device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, const PipePlan* pp,
                                              const PipeResult* res, int iv, int gt, F4 frow, F1 fone) {
-    constexpr int G = P_NF / NG;
+    constexpr int G = fin_group_size(NG);
+    constexpr int NCOL = (P_NS + G - 1) / G;      // columns of the busiest thread (stream threads gt, gt + G, ...)
+    constexpr int NPAIR = (NCOL + 1) / 2;         // taken two columns and two rows per step
     const uint32_t base0 = pool32 + (uint32_t)(((size_t)pp->slot0[iv] * P_NS + gt) * 8);
 #pragma unroll
-    for (int pr = 0; pr < NG; ++pr) {   // P_NS / G = 2 * NG columns; two columns and two rows per step
-        const int c0 = gt + 2 * pr * G;
+    for (int pr = 0; pr < NPAIR; ++pr) {
+        const int c0 = gt + 2 * pr * G, c1 = c0 + G;
         const uint32_t base = base0 + (uint32_t)(2 * pr * G) * 8u;
-        const int n0 = res->pcount[iv][c0], n1 = res->pcount[iv][c0 + G];
+        const int n0 = c0 < P_NS ? res->pcount[iv][c0 < P_NS ? c0 : 0] : 0;
+        const int n1 = c1 < P_NS ? res->pcount[iv][c1 < P_NS ? c1 : 0] : 0;
         const int nmax = max(n0, n1);
         double y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0;
         if (0 < n0) y0 = lds_f64(base);
@@ -2407,7 +2412,7 @@ __device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, co
 template <int NG>
 __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult* res, PipeSel* sel, uint32_t pool32,
                                            uint32_t ovq32, const FinIv& fi, int grp, int gt, int ftid) {
-    constexpr int G = P_NF / NG;
+    constexpr int G = fin_group_size(NG);
     constexpr int GW = G / 4;            // 32-bit words of one sub-bracket's counters inside the group
     const bool use = fi.j0 >= 0;
     const uint32_t cnt32 = smem_u32(&sel->cnt8[0][0]);
@@ -2705,14 +2710,9 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
     for (int j = 0; j < NI_MAX; ++j) any_act = any_act || act_iv[j] >= 0;
     if (any_act) {
         // my group and its interval
-        int grp = 0, gt = ftid;
-        if (ncapi == 2) {
-            grp = ftid >= P_NF / 2 ? 1 : 0;
-            gt = ftid - grp * (P_NF / 2);
-        } else if (ncapi == 3) {
-            grp = ftid / (P_NF / 3);
-            gt = ftid - grp * (P_NF / 3);
-        }
+        const int gsz = fin_group_size(ncapi);
+        const int grp = ftid / gsz, gt = ftid - grp * gsz;
+        const bool member = grp < ncapi;   // three groups of 64 leave the last warps without one
         FinIv fi;
         fi.iv = 0;
         fi.kA = 0;
@@ -2738,9 +2738,14 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
                 }
             }
         const uint32_t pool32 = smem_u32(pool), ovq32 = smem_u32(ovq);
-        if (ncapi == 1) fin_groups<1>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
-        else if (ncapi == 2) fin_groups<2>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
-        else fin_groups<3>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+        if (!member) {
+        } else if (ncapi == 1) {
+            fin_groups<1>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+        } else if (ncapi == 2) {
+            fin_groups<2>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+        } else {
+            fin_groups<3>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+        }
     }
     KO_FT(14);
     fin_sync();
