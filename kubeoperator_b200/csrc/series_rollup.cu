@@ -10,9 +10,9 @@
 //   series_plan       — one warp per long series: a strided 1024-point pre-sample, sorted in registers with
 //                       shuffles, gives a value bracket per quantile (or a list of distinct levels for
 //                       integer-valued series); the plan goes to a window in scratch
-//   series_pipe       — persistent, one CTA of 20 warps per SM, warp-specialised: plan loader, TMA producer
+//   series_pipe       — persistent, one CTA of 22 warps per SM, warp-specialised: plan loader, TMA producer
 //                       (cp.async.bulk + mbarrier ring), 12 stream warps that fuse the statistics with "count
-//                       below the bracket, keep what is inside it" in ONE pass, 6 finish warps that select the
+//                       below the bracket, keep what is inside it" in ONE pass, 8 finish warps that select the
 //                       exact order statistic among the kept candidates of the previous series meanwhile
 //   series_pipe again — second attempt with wide brackets over the few quantiles the first could not answer
 //   series_long       — exact multi-pass slow path (histogram refinement in key space) over what is left
@@ -2379,6 +2379,24 @@ __device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, co
     for (int pr = 0; pr < NPAIR; ++pr) {
         const int c0 = gt + 2 * pr * G, c1 = c0 + G;
         const uint32_t base = base0 + (uint32_t)(2 * pr * G) * 8u;
+        if ((2 * pr + 1) * G >= P_NS) {   // (compile time) an odd column left over: four of its rows per step
+            const int n0 = c0 < P_NS ? res->pcount[iv][c0 < P_NS ? c0 : 0] : 0;
+            double y0 = 0.0, y1 = 0.0, y2 = 0.0, y3 = 0.0;
+            if (0 < n0) y0 = lds_f64(base);
+            if (1 < n0) y1 = lds_f64(base + P_NS * 8);
+            if (2 < n0) y2 = lds_f64(base + 2 * P_NS * 8);
+            if (3 < n0) y3 = lds_f64(base + 3 * P_NS * 8);
+            for (int s = 0; s < n0; s += 4) {
+                const double x0 = y0, x1 = y1, x2 = y2, x3 = y3;
+                const uint32_t nrow = base + (uint32_t)(s + 4) * (P_NS * 8);
+                if (s + 4 < n0) y0 = lds_f64(nrow);
+                if (s + 5 < n0) y1 = lds_f64(nrow + P_NS * 8);
+                if (s + 6 < n0) y2 = lds_f64(nrow + 2 * P_NS * 8);
+                if (s + 7 < n0) y3 = lds_f64(nrow + 3 * P_NS * 8);
+                frow(x0, s < n0, x1, s + 1 < n0, x2, s + 2 < n0, x3, s + 3 < n0);
+            }
+            continue;
+        }
         const int n0 = c0 < P_NS ? res->pcount[iv][c0 < P_NS ? c0 : 0] : 0;
         const int n1 = c1 < P_NS ? res->pcount[iv][c1 < P_NS ? c1 : 0] : 0;
         const int nmax = max(n0, n1);
