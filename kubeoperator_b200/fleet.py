@@ -6,6 +6,8 @@ Per-series statistics need no communication (series are sharded by ID).  Collect
 in the CPU tests — are used only for the small fleet-level exchange:
 * ``fleet_quantile``: exact nearest-rank quantile of the pooled per-shard values by all-gathering 65 536-bin
   key histograms and refining 16 bits per round (4 rounds for a 64-bit key);
+* ``fleet_quantile_small`` / ``fleet_quantile_device``: when every shard holds few values (<= 65 536), ONE
+  all-gather of the values themselves and a selection on the host / on the GPU (no read-back per step);
 * ``fleet_topk``: all-gather of every shard's top-k (key, global index) and a merge that keeps the
   reference's stable descending order (ties by global index);
 * ``fleet_scalars``: all-reduce of the additive fleet scalars.
@@ -78,27 +80,67 @@ def fleet_quantile(hist_fn, n_valid_local, q, dist=None, device="cpu"):
 SMALL_FLEET_CAP = 1 << 16
 
 
-def fleet_quantile_small(values, q, cap, dist=None, device="cpu"):
+def fleet_quantile_small(values, q, cap, dist=None, device="cpu", workspace=None):
     """Exact nearest-rank quantile over all shards when every shard holds at most ``cap`` values (the same
     ``cap`` on every rank, <= SMALL_FLEET_CAP): ONE all-gather of the NaN-padded values and a selection on the
     host, instead of the four histogram rounds of fleet_quantile (each a collective and a host sync).  NaN =
-    no value, as everywhere in the rollup.  Same result as fleet_quantile."""
+    no value, as everywhere in the rollup.  Same result as fleet_quantile.  ``workspace``: a dict the caller
+    keeps between calls; the send / receive / pinned host buffers are created once in it."""
     import torch
     assert 0 < cap <= SMALL_FLEET_CAP
     v = torch.as_tensor(values, dtype=torch.float64, device=device).reshape(-1)
     assert v.numel() <= cap
-    buf = torch.full((cap,), float("nan"), dtype=torch.float64, device=device)
-    buf[:v.numel()] = v
-    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
-        out = torch.empty(dist.get_world_size() * cap, dtype=torch.float64, device=device)
-        dist.all_gather_into_tensor(out, buf)
-        buf = out
-    allv = buf.cpu().numpy()
+    world = dist.get_world_size() if (dist is not None and dist.is_initialized()) else 1
+    ws = workspace if workspace is not None else {}
+    if ws.get("cap") != cap or ws.get("world") != world:
+        ws["cap"], ws["world"] = cap, world
+        ws["send"] = torch.empty(cap, dtype=torch.float64, device=device)
+        ws["recv"] = torch.empty(world * cap, dtype=torch.float64, device=device) if world > 1 else ws["send"]
+        pin = torch.device(device).type == "cuda"
+        ws["host"] = torch.empty(world * cap, dtype=torch.float64, pin_memory=pin)
+    send, recv, host = ws["send"], ws["recv"], ws["host"]
+    send[:v.numel()].copy_(v)
+    if v.numel() < cap:
+        send[v.numel():].fill_(float("nan"))
+    if world > 1:
+        dist.all_gather_into_tensor(recv, send)
+    host.copy_(recv)                     # one device -> host copy (synchronises)
+    allv = host.numpy()
     allv = allv[allv == allv]
     if allv.size == 0:
         return float("nan")
     r = max(1, min(allv.size, int(math.ceil(q * allv.size))))
     return float(np.partition(allv, r - 1)[r - 1]) + 0.0
+
+
+def fleet_quantile_device(values, q, cap, rollup, dist=None, workspace=None):
+    """As fleet_quantile_small, but the selection runs on the GPU and nothing is read back: the gathered,
+    NaN-padded values are handed to ``Rollup.series_rollup_dev`` as ONE series (NaN = no value there too), so
+    the nearest-rank quantile is the library's own exact order statistic.  Returns a 1-element CUDA tensor
+    that is valid once the current stream has run; a caller in a loop reads it when it needs it instead of
+    synchronising every step.  ``values``: CUDA float64 tensor, at most ``cap`` entries, same ``cap`` on
+    every rank."""
+    import torch
+    assert 0 < cap <= SMALL_FLEET_CAP and values.is_cuda and values.dtype == torch.float64
+    v = values.reshape(-1)
+    assert v.numel() <= cap
+    world = dist.get_world_size() if (dist is not None and dist.is_initialized()) else 1
+    ws = workspace if workspace is not None else {}
+    if ws.get("dcap") != cap or ws.get("dworld") != world:
+        ws["dcap"], ws["dworld"] = cap, world
+        ws["dsend"] = torch.empty(cap, dtype=torch.float64, device=v.device)
+        ws["drecv"] = torch.empty(world * cap, dtype=torch.float64, device=v.device) if world > 1 else ws["dsend"]
+        ws["doffs"] = torch.tensor([0, world * cap], dtype=torch.int64, device=v.device)
+        ws["dq"] = torch.empty(1, dtype=torch.float64, device=v.device)
+    send, recv = ws["dsend"], ws["drecv"]
+    send[:v.numel()].copy_(v)
+    if v.numel() < cap:
+        send[v.numel():].fill_(float("nan"))
+    if world > 1:
+        dist.all_gather_into_tensor(recv, send)
+    rollup.series_rollup_dev(recv.data_ptr(), ws["doffs"].data_ptr(), 1, [q], d_quant=ws["dq"].data_ptr(),
+                             stream=torch.cuda.current_stream().cuda_stream)
+    return ws["dq"]
 
 
 def fleet_topk(local_keys, local_global_idx, k, dist=None, device="cpu"):
