@@ -239,3 +239,26 @@ def test_fleet_quantile_single_process(rollup):
         assert np.float64(got).view(np.uint64) == np.float64(exp).view(np.uint64)
     h = rollup.key_histogram(v, 48, 0, 0)
     assert np.array_equal(h, ro.key_histogram_np(v, 48, 0, 0))
+
+
+def test_fleet_quantile_selected_on_the_gpu():
+    """fleet.fleet_quantile_device with one rank: NaN-padded values as one series through the library's own
+    exact selection; same answer as the host path and the oracle."""
+    import torch
+    from kubeoperator_b200 import Rollup, fleet
+    from oracle import rollup_oracle as ro
+    r = Rollup(0)
+    try:
+        rng = np.random.default_rng(41)
+        for n, cap in ((100, 100), (37, 64), (1, 8), (3000, 4096)):
+            v = rng.beta(2, 5, n)
+            v[rng.random(n) < 0.1] = np.nan
+            ws = {}
+            for q in (0.5, 0.95, 1.0):
+                d = fleet.fleet_quantile_device(torch.from_numpy(v).cuda(), q, cap, r, None, ws)
+                got = float(d.cpu()[0])
+                exp = ro.fleet_quantile([v], q)
+                assert (got != got and exp != exp) or got == exp
+                assert fleet.fleet_quantile_small(v, q, cap) == exp or (exp != exp)
+    finally:
+        r.close()
