@@ -3087,6 +3087,14 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
 
 bool g_attr_done = false;
 
+// Host-pointer calls run one launch sequence per staged chunk on the same scratch: the counters a caller wants to
+// see (series that needed the second attempt / the slow path, device error flag) are added up here per chunk.
+__global__ void series_tally(const int* counters, int* tally) {
+    tally[0] += counters[4];
+    tally[1] += counters[6];
+    tally[2] |= counters[2];
+}
+
 constexpr int PLAN_CAP_CTX = 16384;      // plan window of the context's scratch (9 MB)
 constexpr int PLAN_CAP_STATIC = 2048;    // ... of the static scratch of ko_series_rollup_static (1.1 MB)
 // counters + the two series lists, rounded so that the plans behind them are 256-byte aligned
@@ -3274,7 +3282,7 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
     if ((rc = ko_buf_reserve(&ctx->in_small, off_bytes))) return rc;
     if ((rc = ko_buf_reserve(&ctx->out_small, col * 6 + ko_align_up((size_t)n_series * 8 * (nq ? nq : 1), 256))))
         return rc;
-    if ((rc = ko_buf_reserve(&ctx->scratch, ko_series_scratch_bytes(n_series)))) return rc;
+    if ((rc = ko_buf_reserve(&ctx->scratch, ko_series_scratch_bytes(n_series) + 64))) return rc;   // + the tally
     (void)ncols;
     int64_t* d_off = (int64_t*)ctx->in_small.p;
     unsigned char* ob = (unsigned char*)ctx->out_small.p;
@@ -3308,6 +3316,9 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
 
     KO_CUDA(cudaMemcpyAsync(d_off, offsets, off_bytes, cudaMemcpyHostToDevice, ctx->stream));
     ctx->counters.h2d_bytes += (int64_t)off_bytes;
+    int* d_tally = reinterpret_cast<int*>(reinterpret_cast<unsigned char*>(ctx->scratch.p) +
+                                          ko_series_scratch_bytes(n_series));   // 4 ints behind the scratch
+    KO_CUDA(cudaMemsetAsync(d_tally, 0, 4 * sizeof(int), ctx->stream));
     int64_t s0 = 0;
     int c = 0;
     while (s0 < n_series) {
@@ -3339,6 +3350,8 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
             cudaStreamSynchronize(ctx->copy_stream);
             return rc;
         }
+        series_tally<<<1, 1, 0, ctx->stream>>>((const int*)ctx->scratch.p, d_tally);
+        ctx->counters.kernel_launches += 1;
         KO_CUDA(cudaEventRecord(ctx->ev_done[b], ctx->stream));
         // the scratch (work list / counters) is shared by consecutive chunks: they run in stream order
         s0 = s1;
@@ -3353,13 +3366,13 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
     if (out_count) KO_CUDA(cudaMemcpyAsync(out_count, d_cnt, nb, cudaMemcpyDeviceToHost, ctx->stream));
     if (out_quantiles && nq)
         KO_CUDA(cudaMemcpyAsync(out_quantiles, d_q, nb * nq, cudaMemcpyDeviceToHost, ctx->stream));
-    int flags[6] = {0, 0, 0, 0, 0, 0};
-    KO_CUDA(cudaMemcpyAsync(flags, (int*)ctx->scratch.p, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
+    int flags[4] = {0, 0, 0, 0};   // over all chunks: second attempts, slow-path series, device error flag
+    KO_CUDA(cudaMemcpyAsync(flags, d_tally, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
     KO_CUDA(cudaStreamSynchronize(ctx->stream));
     int nout = (out_sum != 0) + (out_mean != 0) + (out_min != 0) + (out_max != 0) + (out_last != 0) +
                (out_count != 0) + ((out_quantiles && nq) ? nq : 0);
     ctx->counters.d2h_bytes += (int64_t)nb * nout + (int64_t)sizeof(flags);
-    ctx->counters.series_fallback = flags[4];  // series the fast path handed to the exact slow path
+    ctx->counters.series_fallback = flags[0];  // series the first attempt of the fast path could not finish
     if (flags[2]) {
         ko_set_error("ko_series_rollup: device reported error flag %d", flags[2]);
         return KO_ECUDA;

@@ -275,6 +275,29 @@ def test_chunked_host_pipeline_matches_device_path(rollup):
     assert np.all(q[:, 2] <= got["max"])
 
 
+def test_counters_add_up_over_staged_chunks(rollup):
+    """A host-pointer call larger than one 256 MB staging buffer runs chunk by chunk on the same scratch:
+    series_fallback (and the device error flag) must cover every chunk, not only the last one."""
+    n, L = 820, 40320                                    # 264 MB of ordinary series ...
+    vals, offs, _ = synth.make_series_torch("c2", 19, "cuda", n_series_override=n)
+    body = vals.cpu().numpy()
+    rng = np.random.default_rng(19)
+    long30 = rng.beta(2.0, 5.0, 172800)                  # ... behind one 30-day series the fast path must defer
+    tail = rng.beta(2.0, 5.0, 12 * L)                    # and enough after them to open a second chunk
+    values = np.concatenate([long30, body, tail])
+    offsets = np.concatenate([[0], 172800 + offs.cpu().numpy(),
+                              172800 + n * L + np.arange(1, 13, dtype=np.int64) * L]).astype(np.int64)
+    assert values.nbytes > 256 * 1024 * 1024
+    got = rollup.series_rollup(values, offsets, QS)
+    assert rollup.counters()["series_fallback"] >= 1     # the 30-day series sits in the FIRST chunk
+    pick = np.array([0, 1, n // 2, n, n + 12])
+    sub_off = np.concatenate([[0], np.cumsum(offsets[pick + 1] - offsets[pick])]).astype(np.int64)
+    sub_val = np.concatenate([values[offsets[i]:offsets[i + 1]] for i in pick])
+    exp = c_oracle.series_rollup(sub_val, sub_off, QS, nthreads=8)
+    sub = {k: v[pick] for k, v in got.items()}
+    assert_series_parity(sub, exp, sub_val, sub_off, QS)
+
+
 def test_errors_are_loud(rollup):
     from kubeoperator_b200 import KoRollupError
     with pytest.raises(KoRollupError):
