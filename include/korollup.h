@@ -111,7 +111,10 @@ int ko_stable_desc_order(ko_ctx* ctx, const int32_t* keys, int64_t n, int64_t* o
 int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t* offsets, int64_t n_series,
                      const double* q, int nq, double* out_sum, double* out_mean, double* out_min,
                      double* out_max, double* out_last, int64_t* out_count, double* out_quantiles);
-/* Same with DEVICE pointers (q stays a host array); enqueues on `stream` and returns. */
+/* Same with DEVICE pointers (q stays a host array); enqueues on `stream` and returns.  The offsets are then
+ * checked on the GPU only: a series whose offsets decrease is skipped (its outputs are left untouched) and
+ * nothing is reported, so validate offsets that come from an untrusted source before the call.  Scratch of the
+ * context is reused by every call: calls on one context must not overlap on the GPU. */
 int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_offsets,
                          int64_t n_series, const double* q, int nq, double* d_out_sum,
                          double* d_out_mean, double* d_out_min, double* d_out_max, double* d_out_last,
