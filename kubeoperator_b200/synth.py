@@ -90,6 +90,42 @@ def make_ragged(seed, lengths):
     return dict(values=values, offsets=offsets)
 
 
+def make_stress(seed):
+    """Randomised batch for parity stress: a mixture of series kinds (the four of the configs plus quantised
+    values of both signs, heavy tails, random staleness rates, integer random walks, stray infinities), lengths
+    from empty to 70 000 samples, optional odd alignment, and a random set of up to four quantiles."""
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(20, 200))
+    series = []
+    for _ in range(n):
+        L = int(rng.choice([rng.integers(0, 40), rng.integers(200, 1100), rng.integers(1025, 9000),
+                            rng.integers(9000, 70000), 40320]))
+        kind = int(rng.integers(0, 8))
+        if kind < 4:
+            v = _one_series(rng, kind, L) if L > 0 else np.zeros(0)
+        elif kind == 4:
+            v = np.round(rng.normal(0, 1, L), int(rng.integers(0, 3)))
+        elif kind == 5:
+            v = rng.standard_cauchy(L) * 10.0 ** rng.integers(-5, 6)
+        elif kind == 6:
+            v = np.where(rng.random(L) < rng.random(), np.nan, rng.random(L))
+        else:
+            v = np.cumsum(rng.integers(-1, 2, L)).astype(np.float64)
+        if L > 10 and rng.random() < 0.1:
+            v[rng.integers(0, L, 3)] = [np.inf, -np.inf, np.nan]
+        series.append(np.asarray(v, np.float64))
+    offsets = np.concatenate([[0], np.cumsum([len(x) for x in series])]).astype(np.int64)
+    values = np.concatenate(series) if series else np.zeros(0)
+    if rng.random() < 0.5:
+        values = np.concatenate([[0.5], values])
+        offsets = np.concatenate([[0], offsets + 1])
+    nq = int(rng.integers(0, 5))
+    grid = [0.0, 0.01, 0.05, 0.25, 0.5, 0.75, 0.9, 0.95, 0.99, 0.999, 1.0]
+    qs = sorted(set(np.round(rng.choice(grid, nq), 3).tolist()))
+    rng.shuffle(qs)
+    return dict(values=values, offsets=offsets, qs=qs)
+
+
 def make_pods(seed, n_pods):
     """Columnar pod list: Poisson(0.3) restarts per container, 3 % not ready, 2 % pods not Running."""
     rng = np.random.default_rng(seed)

@@ -298,6 +298,16 @@ def test_counters_add_up_over_staged_chunks(rollup):
     assert_series_parity(sub, exp, sub_val, sub_off, QS)
 
 
+@pytest.mark.parametrize("seed", range(24))
+def test_randomised_mixtures(rollup, seed):
+    """synth.make_stress: random kinds, lengths, alignment and quantile sets (scripts/stress_parity.py runs
+    the same generator over hundreds of seeds)."""
+    d = synth.make_stress(seed)
+    got = rollup.series_rollup(d["values"], d["offsets"], d["qs"])
+    exp = c_oracle.series_rollup(d["values"], d["offsets"], d["qs"], nthreads=8)
+    assert_series_parity(got, exp, d["values"], d["offsets"], d["qs"])
+
+
 def test_errors_are_loud(rollup):
     from kubeoperator_b200 import KoRollupError
     with pytest.raises(KoRollupError):
