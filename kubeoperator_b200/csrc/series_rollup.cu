@@ -2113,13 +2113,15 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
             if (!rare4(t, x[0], x[1], x[2], x[3], acc.mn, acc.mx)) {
                 acc.sum += t;
                 acc.nvalid += 4;
-            } else {
-                Stats4 st = {acc.sum, acc.mn, acc.mx, acc.nvalid};
-                st = rare_nan4(st, x[0], x[1], x[2], x[3]);
-                acc.sum = st.sum;
-                acc.mn = st.mn;
-                acc.mx = st.mx;
-                acc.nvalid = st.nv;
+            } else {   // a stale sample or a new record among the four: per sample, in line
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const bool ok = x[e] == x[e];
+                    acc.sum += ok ? x[e] : 0.0;
+                    acc.nvalid += ok ? 1u : 0u;
+                    acc.mn = fmin(acc.mn, x[e]);   // fmin / fmax ignore a NaN operand
+                    acc.mx = fmax(acc.mx, x[e]);
+                }
             }
         } else if (t == t) {
             acc.sum += t;
