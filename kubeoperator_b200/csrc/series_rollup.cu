@@ -2161,12 +2161,12 @@ __device__ __forceinline__ void pipe_elems4(const double (&x)[4], PAcc& acc, con
         cap_tail<(1 << (4 * NB + 2))>(x[2], fr.tT, acc.p[NB], acc.pend[NB], ovm);
         cap_tail<(1 << (4 * NB + 3))>(x[3], fr.tT, acc.p[NB], acc.pend[NB], ovm);
     }
-    if (ovm) {
-#pragma unroll
-        for (int i = 0; i < NB + (TAIL ? 1 : 0); ++i)
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                if ((ovm >> (4 * i + e)) & 1u) pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, i, x[e]);
+    while (ovm) {   // one round per set bit (a warp rarely has more than two or three in one lane)
+        const int b = __ffs((int)ovm) - 1;
+        ovm &= ovm - 1u;
+        const int e = b & 3;
+        const double xe = e == 0 ? x[0] : (e == 1 ? x[1] : (e == 2 ? x[2] : x[3]));
+        pipe_overflow(c.ovn32, c.ovcnt32, c.ovq32, c.ovtag32, b >> 2, xe);
     }
     (void)lane;
 }
