@@ -2001,20 +2001,6 @@ __device__ __forceinline__ void sts_u8(uint32_t addr, unsigned c) {
 // Helpers of the stream loop.  The compare chains are PTX so that the compiler does not rewrite them into a
 // min/max tree, and the rare updates are out-of-line calls so that they stay behind a real branch instead of
 // being predicated into every iteration.
-__device__ __forceinline__ bool any_lt4(double a, double b, double c, double d, double m) {
-    unsigned r;
-    asm("{\n.reg .pred p;\nsetp.lt.f64 p, %1, %5;\nsetp.lt.or.f64 p, %2, %5, p;\nsetp.lt.or.f64 p, %3, %5, p;\n"
-        "setp.lt.or.f64 p, %4, %5, p;\nselp.u32 %0, 1, 0, p;\n}"
-        : "=r"(r) : "d"(a), "d"(b), "d"(c), "d"(d), "d"(m));
-    return r != 0;
-}
-__device__ __forceinline__ bool any_gt4(double a, double b, double c, double d, double m) {
-    unsigned r;
-    asm("{\n.reg .pred p;\nsetp.gt.f64 p, %1, %5;\nsetp.gt.or.f64 p, %2, %5, p;\nsetp.gt.or.f64 p, %3, %5, p;\n"
-        "setp.gt.or.f64 p, %4, %5, p;\nselp.u32 %0, 1, 0, p;\n}"
-        : "=r"(r) : "d"(a), "d"(b), "d"(c), "d"(d), "d"(m));
-    return r != 0;
-}
 // t is NaN, or one of a..d is below mn or above mx: one predicate for the three rare events of a step
 __device__ __forceinline__ bool rare4(double t, double a, double b, double c, double d, double mn, double mx) {
     unsigned r;
@@ -2026,12 +2012,6 @@ __device__ __forceinline__ bool rare4(double t, double a, double b, double c, do
         "or.pred p, p, q;\nor.pred p, p, n;\nselp.u32 %0, 1, 0, p;\n}"
         : "=r"(r) : "d"(t), "d"(a), "d"(b), "d"(c), "d"(d), "d"(mn), "d"(mx));
     return r != 0;
-}
-__device__ __noinline__ double rare_min4(double m, double a, double b, double c, double d) {
-    return fmin(fmin(m, fmin(a, b)), fmin(c, d));
-}
-__device__ __noinline__ double rare_max4(double m, double a, double b, double c, double d) {
-    return fmax(fmax(m, fmax(a, b)), fmax(c, d));
 }
 struct Stats4 {
     double sum, mn, mx;
@@ -2083,7 +2063,7 @@ __device__ __forceinline__ void cap_tail(double x, double tT, uint32_t& p, uint3
         : "+r"(p), "+r"(ovm) : "d"(x), "d"(tT), "r"(pend), "n"(P_NS * 8), "n"(BIT) : "memory");
 }
 // A capture that found the thread's private slots full: claim an entry of the shared overflow queue.
-__device__ __noinline__ void pipe_overflow(uint32_t ovn32, uint32_t ovcnt32, uint32_t ovq32, uint32_t ovtag32,
+__device__ __forceinline__ void pipe_overflow(uint32_t ovn32, uint32_t ovcnt32, uint32_t ovq32, uint32_t ovtag32,
                                            int i, double x) {
     unsigned pos;
     asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(pos) : "r"(ovn32) : "memory");
@@ -2239,18 +2219,18 @@ __device__ __forceinline__ void sts_u16(uint32_t addr, unsigned c) {
 __device__ __forceinline__ void pipe_levels4(const double (&x)[4], PAcc& acc, uint32_t thr32, uint32_t col32) {
     {
         const double t = (x[0] + x[1]) + (x[2] + x[3]);
-        if (t == t) {
+        if (!rare4(t, x[0], x[1], x[2], x[3], acc.mn, acc.mx)) {
             acc.sum += t;
             acc.nvalid += 4;
-            if (any_lt4(x[0], x[1], x[2], x[3], acc.mn)) acc.mn = rare_min4(acc.mn, x[0], x[1], x[2], x[3]);
-            if (any_gt4(x[0], x[1], x[2], x[3], acc.mx)) acc.mx = rare_max4(acc.mx, x[0], x[1], x[2], x[3]);
-        } else {
-            Stats4 st = {acc.sum, acc.mn, acc.mx, acc.nvalid};
-            st = rare_nan4(st, x[0], x[1], x[2], x[3]);
-            acc.sum = st.sum;
-            acc.mn = st.mn;
-            acc.mx = st.mx;
-            acc.nvalid = st.nv;
+        } else {   // a stale sample or a new record among the four: per sample, in line
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const bool ok = x[e] == x[e];
+                acc.sum += ok ? x[e] : 0.0;
+                acc.nvalid += ok ? 1u : 0u;
+                acc.mn = fmin(acc.mn, x[e]);
+                acc.mx = fmax(acc.mx, x[e]);
+            }
         }
     }
     uint32_t g8[4] = {0u, 0u, 0u, 0u};   // 8 * (thresholds <= x)
