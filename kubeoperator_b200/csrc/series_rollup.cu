@@ -2585,7 +2585,9 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
         }
         group_sync(grp, G);
         KO_FT(27);
-        // ---- exact order statistic inside each short list by rank counting (doubles compare like their keys)
+        // ---- exact order statistic inside each short list by rank counting (doubles compare like their keys).
+        // A list holds a few dozen candidates, i.e. work for two warps: the second rank of the interval is taken by
+        // the threads counted from the other end of the group, so that both ranks are counted at the same time.
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
             const int j = jj ? fi.j1 : fi.j0;
@@ -2593,14 +2595,15 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                 const int n = (int)min(sel->list_cnt[j], (unsigned)P_LIST);
                 const unsigned rho = sel->rho[j];
                 const uint32_t l32 = smem_u32(&sel->list[j][0]);
-                for (int idx = gt; idx < n; idx += G) {
+                for (int idx = jj ? G - 1 - gt : gt; idx < n; idx += G) {
                     const double e = lds_f64(l32 + (uint32_t)idx * 8u);
                     unsigned lt = 0, le = 0;
 #pragma unroll 4
                     for (int m = 0; m < n; ++m) {
                         const double v = lds_f64(l32 + (uint32_t)m * 8u);
-                        lt += (v < e) ? 1u : 0u;
-                        le += (v <= e) ? 1u : 0u;
+                        asm("{\n.reg .pred p, q;\nsetp.lt.f64 p, %2, %3;\nsetp.le.f64 q, %2, %3;\n"
+                            "@p add.u32 %0, %0, 1;\n@q add.u32 %1, %1, 1;\n}"
+                            : "+r"(lt), "+r"(le) : "d"(v), "d"(e));
                     }
                     if (lt < rho && rho <= le) sel->val[j] = e;   // all writers hold the same value
                 }
