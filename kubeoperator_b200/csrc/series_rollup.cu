@@ -1511,12 +1511,16 @@ struct PipeSel {             // scratch of the finish warps
     double list[NI_MAX][P_LIST];               // candidates of the chosen sub-bracket per quantile
     unsigned tot[P_NI][64];                    // sums of the counters per group
     unsigned char dummy[4][P_NF];              // counters of absent samples
-    unsigned list_cnt[NI_MAX];
     int bin[NI_MAX];                           // chosen sub-bracket per quantile
     unsigned rho[NI_MAX];                      // rank inside it
     unsigned nlist[NI_MAX];                    // candidates inside it
-    int fail;
-    double val[NI_MAX];
+    // What finish thread 0 still reads after the last barrier of a series (and then resets): two copies, used by
+    // alternate series, so that the other finish threads can start on the next series without waiting for it.
+    struct Out {
+        unsigned list_cnt[NI_MAX];   // entries of list[j]
+        int fail;                    // bit j: quantile j could not be answered
+        double val[NI_MAX];          // the selected order statistics
+    } o[2];
 };
 
 __host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) / 16 * 16; }
@@ -2410,8 +2414,9 @@ __device__ __forceinline__ void fin_for_rows(uint32_t pool32, uint32_t ovq32, co
 // holds more than P_LIST candidates (skewed data, heavy tie groups) is cut into 64 again, until the candidates
 // fit the list or the sub-bracket is a single key (then that key is the answer).
 template <int NG>
-__device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult* res, PipeSel* sel, uint32_t pool32,
-                                           uint32_t ovq32, const FinIv& fi, int grp, int gt, int ftid) {
+__device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult* res, PipeSel* sel,
+                                           PipeSel::Out* so, uint32_t pool32, uint32_t ovq32, const FinIv& fi,
+                                           int grp, int gt, int ftid) {
     constexpr int G = fin_group_size(NG);
     constexpr int GW = G / 4;            // 32-bit words of one sub-bracket's counters inside the group
     const bool use = fi.j0 >= 0;
@@ -2465,7 +2470,7 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                         sel->nlist[j] = m1 ? h1 : h0;
                     }
                     if (hit == 0u && lane == 0) {   // cannot happen while the counts are consistent
-                        atomicOr(&sel->fail, 1 << j);
+                        atomicOr(&so->fail, 1 << j);
                         sel->bin[j] = 0;
                         sel->nlist[j] = 0;
                         KO_COUNT(5, 0);
@@ -2542,7 +2547,7 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
             }
             if (sel->nlist[j] > (unsigned)P_LIST) {   // a single key holds the rank
                 direct[jj] = true;
-                if (gt == 0) sel->val[j] = ko_key2d(lo[jj]);
+                if (gt == 0) so->val[j] = ko_key2d(lo[jj]);
             }
         }
         KO_FT(26);
@@ -2551,7 +2556,7 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
             const int ja = direct[0] ? -1 : fi.j0, jb = direct[1] ? -1 : fi.j1;
             const unsigned long long la = lo[0], lb = lo[1];
             const int sa = sh[0], sb = sh[1];
-            const uint32_t cnt0 = smem_u32(&sel->list_cnt[ja < 0 ? 0 : ja]), cnt1 = smem_u32(&sel->list_cnt[jb < 0 ? 0 : jb]);
+            const uint32_t cnt0 = smem_u32(&so->list_cnt[ja < 0 ? 0 : ja]), cnt1 = smem_u32(&so->list_cnt[jb < 0 ? 0 : jb]);
             const uint32_t l0 = smem_u32(&sel->list[ja < 0 ? 0 : ja][0]), l1 = smem_u32(&sel->list[jb < 0 ? 0 : jb][0]);
             // the sub-brackets as ranges of doubles (doubles order like their keys): [dla, dha) and [dlb, dhb); an
             // upper end beyond +inf is a NaN, which no comparison passes
@@ -2592,7 +2597,7 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
         for (int jj = 0; jj < 2; ++jj) {
             const int j = jj ? fi.j1 : fi.j0;
             if (j >= 0 && !direct[jj]) {
-                const int n = (int)min(sel->list_cnt[j], (unsigned)P_LIST);
+                const int n = (int)min(so->list_cnt[j], (unsigned)P_LIST);
                 const unsigned rho = sel->rho[j];
                 const uint32_t l32 = smem_u32(&sel->list[j][0]);
                 for (int idx = jj ? G - 1 - gt : gt; idx < n; idx += G) {
@@ -2605,7 +2610,7 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
                             "@p add.u32 %0, %0, 1;\n@q add.u32 %1, %1, 1;\n}"
                             : "+r"(lt), "+r"(le) : "d"(v), "d"(e));
                     }
-                    if (lt < rho && rho <= le) sel->val[j] = e;   // all writers hold the same value
+                    if (lt < rho && rho <= le) so->val[j] = e;   // all writers hold the same value
                 }
             }
         }
@@ -2615,8 +2620,8 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
 
 // Returns (meaningful on finish thread 0) the mask of quantiles that a later attempt has to answer; 0 = all done.
 __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
-                                            const unsigned char* pool, const double* ovq, int ftid, int fwarp,
-                                            int lane) {
+                                            PipeSel::Out* so, const unsigned char* pool, const double* ovq, int ftid,
+                                            int fwarp, int lane) {
     (void)fwarp;
     const int ni = pp->ni, nq = a.nq, nb = pp->nb, qsel = pp->qsel;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
@@ -2743,22 +2748,22 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
         const uint32_t pool32 = smem_u32(pool), ovq32 = smem_u32(ovq);
         if (!member) {
         } else if (ncapi == 1) {
-            fin_groups<1>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+            fin_groups<1>(pp, res, sel, so, pool32, ovq32, fi, grp, gt, ftid);
         } else if (ncapi == 2) {
-            fin_groups<2>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+            fin_groups<2>(pp, res, sel, so, pool32, ovq32, fi, grp, gt, ftid);
         } else {
-            fin_groups<3>(pp, res, sel, pool32, ovq32, fi, grp, gt, ftid);
+            fin_groups<3>(pp, res, sel, so, pool32, ovq32, fi, grp, gt, ftid);
         }
     }
     KO_FT(14);
     fin_sync();
     KO_FT(7);
     if (ftid == 0) {
-        failmask |= sel->fail;
+        failmask |= so->fail;
         double out[NI_MAX];
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) {
-            out[j] = act_iv[j] >= 0 ? sel->val[j] : dval[j];
+            out[j] = act_iv[j] >= 0 ? so->val[j] : dval[j];
             if (act_iv[j] >= 0 && !(out[j] == out[j])) {
                 if (!((failmask >> j) & 1)) KO_COUNT(6, a.wide);
                 failmask |= 1 << j;   // no candidate carried the rank
@@ -2778,7 +2783,8 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
 // Finish of a levels plan: total the per-thread gap counters, then every rank must fall on a listed level, i.e.
 // (#valid samples < v) < rank <= (#valid samples <= v); otherwise the series goes to the slow path.
 __device__ __forceinline__ int pipe_finish_levels(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
-                                                const unsigned char* pool, int ftid, int fwarp, int lane) {
+                                                PipeSel::Out* so, const unsigned char* pool, int ftid, int fwarp,
+                                                int lane) {
     const int nq = a.nq;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
     const uint32_t pool32 = smem_u32(pool);
@@ -2833,7 +2839,7 @@ __device__ __forceinline__ int pipe_finish_levels(const SeriesArgs& a, const Pip
                 fail |= 1 << j;   // the rank fell on a value that is not listed
                 KO_COUNT(7, a.wide);
             }
-        sel->fail = fail;
+        so->fail = fail;
         {
             const int sid = pp->sid;
             if (a.out_sum) a.out_sum[sid] = s;
@@ -2851,7 +2857,7 @@ __device__ __forceinline__ int pipe_finish_levels(const SeriesArgs& a, const Pip
         }
     }
     fin_sync();
-    return sel->fail;
+    return so->fail;
 }
 
 // ------------------------------------------------------------------------------------------ kernel
@@ -2879,10 +2885,12 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
         }
         {
             PipeSel* sl = sm.sel();
-            sl->fail = 0;
-            for (int j = 0; j < NI_MAX; ++j) {
-                sl->list_cnt[j] = 0;
-                sl->val[j] = __longlong_as_double(0x7FF8000000000000LL);
+            for (int o = 0; o < 2; ++o) {
+                sl->o[o].fail = 0;
+                for (int j = 0; j < NI_MAX; ++j) {
+                    sl->o[o].list_cnt[j] = 0;
+                    sl->o[o].val[j] = __longlong_as_double(0x7FF8000000000000LL);
+                }
             }
         }
         mbar_fence_init();
@@ -3034,19 +3042,21 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
             if (!pp->defer) {
                 const uint32_t pool = c & 1u;
                 { KO_PT0(); mbar_wait_sleep(sm.bars() + B_POOL_FULL + pool, (c >> 1) & 1u); KO_PT1(12, ftid == 0); }
-                { KO_PT0(); todo = pp->vals ? pipe_finish_levels(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), ftid, fwarp, lane)
-                                          : pipe_finish(a, pp, sm.res(pool), sm.sel(), sm.pool(pool), sm.ovq(pool), ftid, fwarp, lane); KO_PT1(10, ftid == 0); }
-                fin_sync();
+                PipeSel::Out* so = &sm.sel()->o[pool];   // scratch copy of this series (alternates like the pools)
+                { KO_PT0(); todo = pp->vals ? pipe_finish_levels(a, pp, sm.res(pool), sm.sel(), so, sm.pool(pool), ftid, fwarp, lane)
+                                          : pipe_finish(a, pp, sm.res(pool), sm.sel(), so, sm.pool(pool), sm.ovq(pool), ftid, fwarp, lane); KO_PT1(10, ftid == 0); }
+                // Both finish routines end behind a barrier of the finish warps, after which only thread 0 still
+                // reads this series' pool, hand-off and scratch copy: it resets them and releases the pool while
+                // the other threads go on to the next series (other pool, other scratch copy) without waiting.
                 if (ftid == 0) {
                     PipeResult* r0 = sm.res(pool);
-                    PipeSel* sl = sm.sel();
                     r0->t_nvalid = 0;
                     r0->ovn = 0;
                     for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
-                    sl->fail = 0;
+                    so->fail = 0;
                     for (int j = 0; j < NI_MAX; ++j) {
-                        sl->list_cnt[j] = 0;
-                        sl->val[j] = __longlong_as_double(0x7FF8000000000000LL);
+                        so->list_cnt[j] = 0;
+                        so->val[j] = __longlong_as_double(0x7FF8000000000000LL);
                     }
                     mbar_arrive(sm.bars() + B_POOL_FREE + pool);
                 }
@@ -3063,7 +3073,6 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                     }
                 }
             }
-            fin_sync();
             if (ftid == 0) mbar_arrive(sm.bars() + B_PLAN_FREE + slot);
         }
     }
