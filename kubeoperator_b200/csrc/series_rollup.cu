@@ -2237,18 +2237,23 @@ __device__ __forceinline__ void pipe_levels4(const double (&x)[4], PAcc& acc, ui
             }
         }
     }
-    uint32_t g8[4] = {0u, 0u, 0u, 0u};   // 8 * (thresholds <= x)
-#pragma unroll
-    for (int step = 16; step >= 1; step >>= 1) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            const double t = lds_f64(thr32 + g8[e] + (uint32_t)(step - 1) * 8u);
-            g8[e] += (x[e] >= t) ? (uint32_t)step * 8u : 0u;
-        }
+    // ga = address of thr[number of thresholds <= x so far]: load, compare, predicated add per step
+    uint32_t ga[4] = {thr32, thr32, thr32, thr32};
+#define KO_LEVEL_STEP(STEP)                                                                                  \
+    _Pragma("unroll") for (int e = 0; e < 4; ++e) {                                                          \
+        const double t = lds_f64(ga[e] + (uint32_t)((STEP)-1) * 8u);                                         \
+        asm("{\n.reg .pred p;\nsetp.ge.f64 p, %1, %2;\n@p add.u32 %0, %0, %3;\n}"                            \
+            : "+r"(ga[e]) : "d"(x[e]), "d"(t), "n"((STEP)*8));                                               \
     }
+    KO_LEVEL_STEP(16)
+    KO_LEVEL_STEP(8)
+    KO_LEVEL_STEP(4)
+    KO_LEVEL_STEP(2)
+    KO_LEVEL_STEP(1)
+#undef KO_LEVEL_STEP
 #pragma unroll
     for (int e = 0; e < 4; ++e) {   // one after another: two samples of a thread often share a gap
-        const uint32_t addr = col32 + g8[e] * (uint32_t)(P_NS * 2 / 8);
+        const uint32_t addr = col32 + (ga[e] - thr32) * (uint32_t)(P_NS * 2 / 8);
         sts_u16(addr, lds_u16(addr) + 1u);
     }
 }
