@@ -1493,10 +1493,28 @@ struct alignas(16) PipePlan {
     double thr[P_NTHR + 1];
 };
 
+// What the finish warps need to agree on before their first scan: valid count, extremes, which bracket holds which
+// rank.  It follows from the stream warps' totals alone, so the last stream warp to hand off works it out once.
+struct FinPro {
+    unsigned n;                              // valid samples
+    int ncapi;                               // capturing intervals
+    int failmask;                            // quantiles this attempt cannot answer (bracket missed, queue full)
+    unsigned arrived_pad;
+    double sum, mn, mx;
+    unsigned long long kA[P_NI];             // effective bracket start per interval
+    int ish[P_NI];                           // (key - kA) >> ish is the sub-bracket
+    int ord[P_NI];                           // ordinal among the capturing intervals (-1: none)
+    double dval[NI_MAX];                     // quantiles answered by counts alone
+    int act_iv[NI_MAX];                      // interval in which quantile j is to be selected (-1: not)
+    unsigned rho[NI_MAX];                    // its rank inside that bracket
+};
+
 struct PipeResult {          // what the stream warps hand to the finish warps, one per pool
     double sum[P_SW], mn[P_SW], mx[P_SW];          // per stream warp (summed in warp order: reproducible)
     // totals over all stream warps, added with shared-memory reductions, cleared by the finish warps
     unsigned t_nvalid, t_cA[P_NI], t_cin[P_NI], t_ncap[P_NI];
+    unsigned arrived;                    // stream warps that have handed off (the last one fills pro)
+    FinPro pro;
     unsigned ovcnt[P_NI];                // captures that found the thread's private slots full, per interval
     unsigned ovn;                        // ... and in total: entries claimed in the shared overflow queue
     unsigned char ovtag[P_OVQ];          // interval of each overflow queue entry
@@ -2623,6 +2641,95 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
     }
 }
 
+// Run by one thread (lane 0 of the last stream warp to hand off) once all totals of the series are in *res.
+__device__ __noinline__ void fin_prologue(const PipePlan* pp, PipeResult* res, int nq, double q0, double q1, double q2,
+                                          double q3, int wide) {
+    (void)wide;
+    FinPro* pro = &res->pro;
+    const int ni = pp->ni, nb = pp->nb, qsel = pp->qsel;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    const unsigned n = res->t_nvalid;
+    double s = 0.0, mn = INFINITY, mx = -INFINITY;
+    for (int w = 0; w < P_SW; ++w) {   // in warp order: reproducible
+        s += res->sum[w];
+        mn = fmin(mn, res->mn[w]);
+        mx = fmax(mx, res->mx[w]);
+    }
+    pro->n = n;
+    pro->sum = s;
+    pro->mn = mn;
+    pro->mx = mx;
+    unsigned cAt[P_NI], nin[P_NI];
+    unsigned long long kA[P_NI], kB[P_NI];
+    bool capm[P_NI];
+    const bool ovbad = res->ovn > (unsigned)P_OVQ;
+    int ncapi = 0;
+#pragma unroll
+    for (int i = 0; i < P_NI; ++i) {
+        cAt[i] = nin[i] = 0;
+        kA[i] = 0;
+        kB[i] = 1;
+        capm[i] = false;
+        int ish = 0, ord = -1;
+        if (i < ni) {
+            nin[i] = res->t_ncap[i] + res->ovcnt[i] + res->t_cin[i];
+            cAt[i] = (i < nb) ? res->t_cA[i] : n - nin[i];   // upper tail: everything outside is below
+            kA[i] = pp->kA[i];
+            kB[i] = pp->kB[i];
+            if (kB[i] > KO_KEY_PINF) kB[i] = ko_okey(mx + 0.0) + 1;   // upper tail: nothing lies above the maximum
+            const unsigned long long span = kB[i] - kA[i] - 1;        // kB > kA
+            const int bits = span ? 64 - __clzll((long long)span) : 0;
+            ish = bits > 6 ? bits - 6 : 0;
+            capm[i] = pp->mode[i] == M_CAPTURE;
+            if (capm[i]) ord = ncapi++;
+        }
+        pro->kA[i] = kA[i];
+        pro->ish[i] = ish;
+        pro->ord[i] = ord;
+    }
+    pro->ncapi = ncapi;
+    int failmask = 0;
+    const double qs[NI_MAX] = {q0, q1, q2, q3};
+#pragma unroll
+    for (int j = 0; j < NI_MAX; ++j) {
+        double dval = nan;
+        int act = -1;
+        unsigned rho = 0;
+        if (j < nq && n > 0 && (qsel < 0 || j == qsel)) {
+            const int i = pp->q_iv[j];
+            const unsigned r = nearest_rank_dev(n, qs[j]);
+            unsigned cA = cAt[0], nn = nin[0];
+            unsigned long long ka = kA[0], kb = kB[0];
+            bool cm = capm[0];
+#pragma unroll
+            for (int t = 1; t < P_NI; ++t)
+                if (i == t) {
+                    cA = cAt[t];
+                    nn = nin[t];
+                    ka = kA[t];
+                    kb = kB[t];
+                    cm = capm[t];
+                }
+            if (r <= cA || r > cA + nn) {
+                failmask |= 1 << j;       // the bracket missed the rank
+                KO_COUNT(3, wide);
+            } else if (!cm || kb - ka == 1) {
+                dval = ko_key2d(ka);      // a single value: answered by the counts
+            } else if (ovbad) {
+                failmask |= 1 << j;       // more candidates than shared memory holds
+                KO_COUNT(4, wide);
+            } else {
+                act = i;
+                rho = r - cA;
+            }
+        }
+        pro->dval[j] = dval;
+        pro->act_iv[j] = act;
+        pro->rho[j] = rho;
+    }
+    pro->failmask = failmask;
+}
+
 // Returns (meaningful on finish thread 0) the mask of quantiles that a later attempt has to answer; 0 = all done.
 __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* pp, PipeResult* res, PipeSel* sel,
                                             PipeSel::Out* so, const unsigned char* pool, const double* ovq, int ftid,
@@ -2633,90 +2740,41 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
 #ifdef KO_PHASE_TIMING
     unsigned long long _ft = clock64();
 #endif
-    // ---- prologue, redundantly in every thread (all values uniform)
-    const unsigned n = res->t_nvalid;
-    double mx = lane < P_SW ? res->mx[lane] : -INFINITY;
-    mx = warp_max(mx);
+    // ---- what the last stream warp worked out (fin_prologue)
+    const FinPro* pro = &res->pro;
+    const unsigned n = pro->n;
     if (ftid == 32) {   // the plain statistics do not depend on the selection: written here, off the critical path
-        double s = 0.0, mn = INFINITY;
-        for (int w = 0; w < P_SW; ++w) {
-            s += res->sum[w];
-            mn = fmin(mn, res->mn[w]);
-        }
         const int sid = pp->sid;
+        const double s = pro->sum;
         if (a.out_sum) a.out_sum[sid] = s;
         if (a.out_mean) a.out_mean[sid] = n > 0 ? s / (double)n : 0.0;
-        if (a.out_min) a.out_min[sid] = n > 0 ? mn + 0.0 : nan;
-        if (a.out_max) a.out_max[sid] = n > 0 ? mx + 0.0 : nan;
+        if (a.out_min) a.out_min[sid] = n > 0 ? pro->mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = n > 0 ? pro->mx + 0.0 : nan;
         if (a.out_last) a.out_last[sid] = pp->last;
         if (a.out_count) a.out_count[sid] = (int64_t)n;
     }
-    unsigned cAt[P_NI], nin[P_NI];
-    unsigned long long kA[P_NI], kB[P_NI];
+    unsigned long long kA[P_NI];
     int ish[P_NI], ord[P_NI];
-    bool capm[P_NI], ovbad[P_NI];
-    int ncapi = 0;
 #pragma unroll
     for (int i = 0; i < P_NI; ++i) {
-        cAt[i] = nin[i] = 0;
-        kA[i] = 0;
-        kB[i] = 1;
-        ish[i] = 0;
-        ord[i] = -1;
-        capm[i] = ovbad[i] = false;
-        if (i < ni) {
-            nin[i] = res->t_ncap[i] + res->ovcnt[i] + res->t_cin[i];
-            cAt[i] = (i < nb) ? res->t_cA[i] : n - nin[i];   // upper tail: everything outside is below
-            kA[i] = pp->kA[i];
-            kB[i] = pp->kB[i];
-            if (kB[i] > KO_KEY_PINF) kB[i] = ko_okey(mx + 0.0) + 1;   // upper tail: nothing lies above the maximum
-            const unsigned long long span = kB[i] - kA[i] - 1;        // kB > kA
-            const int bits = span ? 64 - __clzll((long long)span) : 0;
-            ish[i] = bits > 6 ? bits - 6 : 0;
-            capm[i] = pp->mode[i] == M_CAPTURE;
-            ovbad[i] = res->ovn > (unsigned)P_OVQ;
-            if (capm[i]) ord[i] = ncapi++;
-        }
+        kA[i] = pro->kA[i];
+        ish[i] = pro->ish[i];
+        ord[i] = pro->ord[i];
     }
-    int failmask = 0;   // quantiles this attempt cannot answer
+    const int ncapi = pro->ncapi;
+    int failmask = pro->failmask;   // quantiles this attempt cannot answer
     double dval[NI_MAX];
     int act_iv[NI_MAX];
     unsigned rho[NI_MAX];
 #pragma unroll
     for (int j = 0; j < NI_MAX; ++j) {
-        dval[j] = nan;
-        act_iv[j] = -1;
-        rho[j] = 0;
-        if (j < nq && n > 0 && (qsel < 0 || j == qsel)) {
-            const int i = pp->q_iv[j];
-            const unsigned r = nearest_rank_dev(n, a.q[j]);
-            unsigned cA = cAt[0], nn = nin[0];
-            unsigned long long ka = kA[0], kb = kB[0];
-            bool cm = capm[0], ob = ovbad[0];
-#pragma unroll
-            for (int t = 1; t < P_NI; ++t)
-                if (i == t) {
-                    cA = cAt[t];
-                    nn = nin[t];
-                    ka = kA[t];
-                    kb = kB[t];
-                    cm = capm[t];
-                    ob = ovbad[t];
-                }
-            if (r <= cA || r > cA + nn) {
-                failmask |= 1 << j;       // the bracket missed the rank
-                if (ftid == 0) KO_COUNT(3, a.wide);
-            } else if (!cm || kb - ka == 1) {
-                dval[j] = ko_key2d(ka);   // a single value: answered by the counts
-            } else if (ob) {
-                failmask |= 1 << j;       // more candidates than shared memory holds
-                if (ftid == 0) KO_COUNT(4, a.wide);
-            } else {
-                act_iv[j] = i;
-                rho[j] = r - cA;
-            }
-        }
+        dval[j] = pro->dval[j];
+        act_iv[j] = pro->act_iv[j];
+        rho[j] = pro->rho[j];
     }
+    (void)ni;
+    (void)nb;
+    (void)lane;
     KO_FT(13);
     bool any_act = false;
 #pragma unroll
@@ -2886,6 +2944,7 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
             PipeResult* r0 = sm.res(s);
             r0->t_nvalid = 0;
             r0->ovn = 0;
+            r0->arrived = 0;
             for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
         }
         {
@@ -3025,6 +3084,16 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                     red_shared_add(&res->t_cA[1], ca1);
 #pragma unroll
                     for (int i = 0; i < P_NI; ++i) red_shared_add(&res->t_ncap[i], wpc[i]);
+                }
+                if (lane == 0) {   // the last stream warp to get here prepares the finish warps' common ground
+                    __threadfence_block();
+                    const unsigned before = atom_shared_add(&res->arrived, 1u);
+                    if (before == (unsigned)P_SW - 1u) {
+                        __threadfence_block();
+                        res->arrived = 0;
+                        if (!pp->vals) fin_prologue(pp, res, a.nq, a.q[0], a.q[1], a.q[2], a.q[3], a.wide);
+                        __threadfence_block();
+                    }
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(sm.bars() + B_POOL_FULL + pool);
