@@ -1582,38 +1582,65 @@ __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n
 // A packed key is (22-bit position of the sample's key inside the sample's own key range) << 10 | sample index:
 // fine enough to place the brackets, half the registers and instructions of a 64-bit sort; the exact bracket
 // ends are re-read from the series through the index.
+// Bitonic sort in the "flip" form: the first step of every merge pairs i with i ^ (k - 1), the later ones i with
+// i ^ j, and the smaller key always goes to the lower index.  No step needs a direction, so a pair of registers
+// costs one min and one max.
 template <int J>
-__device__ __forceinline__ void planner_stage_regs(unsigned (&r)[32], int k, int lane) {
+__device__ __forceinline__ void planner_stage_regs(unsigned (&r)[32]) {
 #pragma unroll
     for (int e = 0; e < 32; ++e) {
         if ((e & J) == 0) {
-            const bool up = (((lane << 5) | e) & k) == 0;
             const unsigned lo = min(r[e], r[e | J]), hi = max(r[e], r[e | J]);
-            r[e] = up ? lo : hi;
-            r[e | J] = up ? hi : lo;
+            r[e] = lo;
+            r[e | J] = hi;
         }
     }
+    if constexpr (J > 1) planner_stage_regs<J / 2>(r);
+}
+template <int K>   // runs of K / 2 keys inside a lane's registers -> runs of K
+__device__ __forceinline__ void planner_merge_regs(unsigned (&r)[32]) {
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+        const int p = e ^ (K - 1);
+        if (e < p) {
+            const unsigned lo = min(r[e], r[p]), hi = max(r[e], r[p]);
+            r[e] = lo;
+            r[p] = hi;
+        }
+    }
+    if constexpr (K >= 4) planner_stage_regs<K / 4>(r);
 }
 __device__ __forceinline__ void planner_sort(unsigned (&r)[32], int lane) {
+    planner_merge_regs<2>(r);
+    planner_merge_regs<4>(r);
+    planner_merge_regs<8>(r);
+    planner_merge_regs<16>(r);
+    planner_merge_regs<32>(r);
 #pragma unroll 1
-    for (int k = 2; k <= P_SAMPLE; k <<= 1) {
+    for (int k = 64; k <= P_SAMPLE; k <<= 1) {
+        {   // flip step: lane ^ (k / 32 - 1), register 31 - e
+            const int mask = (k >> 5) - 1;
+            const bool lower = (lane & (k >> 6)) == 0;
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+                const unsigned x = r[e], y = r[31 - e];
+                const unsigned ox = __shfl_xor_sync(0xffffffffu, y, mask);
+                const unsigned oy = __shfl_xor_sync(0xffffffffu, x, mask);
+                r[e] = lower ? min(x, ox) : max(x, ox);
+                r[31 - e] = lower ? min(y, oy) : max(y, oy);
+            }
+        }
 #pragma unroll 1
-        for (int j = k >> 1; j >= 32; j >>= 1) {  // partner in another lane
+        for (int j = k >> 2; j >= 32; j >>= 1) {  // partner in another lane
             const int m = j >> 5;
             const bool lower = (lane & m) == 0;
-            const bool up = ((lane << 5) & k) == 0;   // k >= 64 here: the bit lies in the lane part
-            const bool take_min = (lower == up);
 #pragma unroll
             for (int e = 0; e < 32; ++e) {
                 const unsigned o = __shfl_xor_sync(0xffffffffu, r[e], m);
-                r[e] = take_min ? min(r[e], o) : max(r[e], o);
+                r[e] = lower ? min(r[e], o) : max(r[e], o);
             }
         }
-        if (k > 16) planner_stage_regs<16>(r, k, lane);
-        if (k > 8) planner_stage_regs<8>(r, k, lane);
-        if (k > 4) planner_stage_regs<4>(r, k, lane);
-        if (k > 2) planner_stage_regs<2>(r, k, lane);
-        planner_stage_regs<1>(r, k, lane);
+        planner_stage_regs<16>(r);
     }
 }
 
@@ -1954,8 +1981,14 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
 // ------------------------------------------------------------------------------------------ plan kernel
 // One warp per work item, ahead of series_pipe: the plans are about 5 000 instructions of straight-line code per
 // series, which inside the pipelined kernel kept evicting the stream and finish loops from the instruction caches.
-constexpr int PLAN_WARPS = 8;
-__global__ void __launch_bounds__(PLAN_WARPS * 32) series_plan(SeriesArgs a) {
+#ifndef KO_PLAN_WARPS
+#define KO_PLAN_WARPS 8
+#endif
+constexpr int PLAN_WARPS = KO_PLAN_WARPS;
+#ifndef KO_PLAN_GRID
+#define KO_PLAN_GRID 8   // CTAs per SM in the grid: finer than the two resident ones, so that constant and tie-heavy series do not leave warps idle
+#endif
+__global__ void __launch_bounds__(PLAN_WARPS * 32, 16 / PLAN_WARPS) series_plan(SeriesArgs a) {
     __shared__ PipePlan sp[PLAN_WARPS];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const long long n_items = (long long)a.counters[a.work_cnt] * (a.wide ? a.nq : 1);
@@ -3205,7 +3238,7 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
         const int64_t cnt = n_long - w0 < plan_cap ? n_long - w0 : plan_cap;
         a.w_begin = w0;
         const int pg = (int)((cnt + PLAN_WARPS - 1) / PLAN_WARPS);
-        series_plan<<<pg < 4 * num_sms ? pg : 4 * num_sms, PLAN_WARPS * 32, 0, st>>>(a);
+        series_plan<<<pg < KO_PLAN_GRID * num_sms ? pg : KO_PLAN_GRID * num_sms, PLAN_WARPS * 32, 0, st>>>(a);
         if (w0 == 0 && ev_p0) cudaEventRecord(ev_p0, st);
         series_pipe<<<(int64_t)pgrid < cnt ? pgrid : (int)cnt, P_THREADS, PIPE_SMEM_BYTES, st>>>(a);
         if (w0 == 0 && ev_p1) cudaEventRecord(ev_p1, st);
