@@ -1464,6 +1464,11 @@ constexpr int P_NI = 3;                        // at most 2 brackets + 1 upper t
 static_assert(P_NF >= 192 && P_NF % 64 == 0 && P_NS % 64 == 0, "group sizes");
 __host__ __device__ constexpr int fin_group_size(int ng) { return ng == 3 ? 64 : P_NF / ng; }
 constexpr int P_LIST = 256;                    // candidates of one sub-bracket kept for the final rank counting
+// Second attempt: brackets WIDE_MULT times as wide in rank space.  It works from the same pre-sample, so what it
+// has to cover is a sample that was off by more than CSIG sigma; 1.5 x CSIG leaves that 1 in 400 while the
+// candidates of a median bracket still fit a thread's 24 slots with room (2 x CSIG filled the overflow queue on a
+// few series per 10 000, and each of those then cost a 0.2 ms trip through series_long).
+constexpr double WIDE_MULT = 1.5;
 constexpr int P_SAMPLE = 1024;
 constexpr int P_CROW = P_NF + 4;               // bytes per row of the finish warps' counters
 constexpr int P_LEVELS = 15;                   // distinct values a "levels" plan can list
@@ -1788,7 +1793,7 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
                 const double q = a.q[j];
                 const double pos = q * (double)valid_s;
                 const double sig = sqrt(fmax(q * (1.0 - q), 0.0) * (double)valid_s);
-                const int m = (int)ceil((a.wide ? 2.0 * CSIG : CSIG) * sig) + 2;
+                const int m = (int)ceil((a.wide ? WIDE_MULT * CSIG : CSIG) * sig) + 2;
                 int aj = (int)floor(pos) - m - 1, bj = (int)ceil(pos) + m;
                 if (aj < 0) aj = -1;
                 if (bj > valid_s) bj = valid_s;
@@ -1870,7 +1875,10 @@ __device__ __forceinline__ void planner_build(PipePlan* pp, const SeriesArgs& a,
         }
         if (nb > 2 || total > P_SLOTS) soft = 1;
         if (tail && !last_is_tail) soft = 1;
-        if ((soft || ties) && !defer) {
+        // First attempt: repeated values at a bracket end send the series to a levels plan.  Second attempt: one
+        // quantile has all the slots, so a capture plan that fits is taken first -- it also finds a value the
+        // pre-sample never saw, which is what a levels plan fails on.
+        if ((soft || (ties && !a.wide)) && !defer) {
             // Levels plan, preferred whenever it applies (tie-heavy brackets overflow the capture slots): list the distinct values the pre-sample shows inside the intervals.  Distinctness is
             // judged on the packed keys; whatever this misses only makes the finish warps defer the series.
             unsigned prev_last = __shfl_up_sync(0xffffffffu, r[31], 1);

@@ -1,14 +1,15 @@
 """Diagnostic (debug build only): why series leave the fast path, on the bench workload."""
 import ctypes, os, sys
 sys.path.insert(0, ".")
-os.environ["KOROLLUP_LIB"] = os.path.abspath("scripts/libkorollup_dbg.so")
+os.environ["KOROLLUP_LIB"] = os.path.abspath(os.environ.get("KO_DBG_LIB", "scripts/libkorollup_dbg.so"))
 import torch
 from kubeoperator_b200 import Rollup, synth, korollup
 QS = [0.5, 0.95, 0.99]
 r = Rollup(0)
 lib = korollup.load_library()
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 10400
-vals, offs, kinds = synth.make_series_torch("c2", 1, "cuda", n_series_override=n)
+seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+vals, offs, kinds = synth.make_series_torch("c2", seed, "cuda", n_series_override=n)
 n = len(kinds)
 q = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
 s = torch.zeros(n, dtype=torch.float64, device="cuda")
