@@ -165,6 +165,24 @@ __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_
         "l"(src), "r"(bytes), "r"(smem_u32(bar))
         : "memory");
 }
+// Bulk prefetch into L2: no shared memory, no completion to wait for (SASS: UBLKPF).
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+// One look at a barrier, no waiting.
+__device__ __forceinline__ bool mbar_test(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, P1;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return done != 0;
+}
 __device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity) {
     asm volatile(
         "{\n"
@@ -1457,6 +1475,10 @@ constexpr uint32_t P_PLAN_LOG = 2;
 constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW) * 32;   // planners, producer, stream, finish
 constexpr int P_TILE = 4 * P_NS;               // 1536 doubles (12 KB) per ring stage
 constexpr int P_STAGES = 3;
+#ifndef KO_P_PF
+#define KO_P_PF 4
+#endif
+constexpr int P_PF = KO_P_PF;                   // tiles asked into L2 ahead of the ring
 constexpr int P_SLOTS = 24;                    // thread-private candidate slots per stream thread
 constexpr int P_OVQ = 640;                     // overflow queue entries per pool
 constexpr int P_NI = 3;                        // at most 2 brackets + 1 upper tail
@@ -3041,6 +3063,11 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                 if (!pp->defer) {
                     const int ntiles = pp->ntiles, body = pp->body;
                     const double* vbody = pp->v + pp->head;
+                    // The ring holds 3 tiles, which is less than HBM latency and warp skew need.  L2 is the rest of
+                    // the ring: every tile is asked into L2 P_PF tiles before its copy, across the end of the
+                    // series into the next one when that plan has arrived.
+                    const PipePlan* np = nullptr;
+                    bool looked = false;
                     for (int t = 0; t < ntiles; ++t) {
                         const uint32_t gg = g + (uint32_t)t;
                         const uint32_t s = gg % P_STAGES;
@@ -3049,6 +3076,23 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
                         mbar_expect_tx(sm.bars() + B_RING_FULL + s, bytes);
                         tma_bulk_g2s(sm.ring() + (size_t)s * P_TILE, vbody + (size_t)t * P_TILE, bytes,
                                      sm.bars() + B_RING_FULL + s);
+                        const int tp = t + P_PF;
+                        if (tp < ntiles) {
+                            bulk_prefetch_l2(vbody + (size_t)tp * P_TILE, (uint32_t)min(P_TILE, body - tp * P_TILE) * 8u);
+                        } else {
+                            if (!looked) {
+                                looked = true;
+                                const uint32_t k1 = k + 1, slot1 = k1 & (P_PLANS - 1);
+                                if (mbar_test(sm.bars() + B_PLAN_FULL + slot1, (k1 >> P_PLAN_LOG) & 1u)) {
+                                    const PipePlan* q = sm.plan(slot1);
+                                    if (q->sid >= 0 && !q->defer) np = q;
+                                }
+                            }
+                            const int u = tp - ntiles;
+                            if (np && u < np->ntiles)
+                                bulk_prefetch_l2(np->v + np->head + (size_t)u * P_TILE,
+                                                 (uint32_t)min(P_TILE, np->body - u * P_TILE) * 8u);
+                        }
                     }
                     g += (uint32_t)ntiles;
                 }
