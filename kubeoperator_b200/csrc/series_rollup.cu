@@ -2267,9 +2267,11 @@ __device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const
         double x[4];
         lds_v2f64(base, x[0], x[1]);
         lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
+        // the samples are in registers: the stage goes back to the producer before they are worked on (a warp's
+        // shared-memory loads and its barrier arrival are carried out in order)
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
         if (++s == P_STAGES) {
             s = 0;
             par ^= 1u;
@@ -2283,9 +2285,9 @@ __device__ __forceinline__ void pipe_stream(const PipePlan* pp, PAcc& acc, const
         x[0] = x[1] = x[2] = x[3] = nan;
         if (stid < rem2) lds_v2f64(base, x[0], x[1]);
         if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        pipe_elems4<NB, TAIL>(x, acc, fr, c, lane);
     }
     g += (uint32_t)ntiles;
 }
@@ -2366,9 +2368,11 @@ __device__ __forceinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc
         double x[4];
         lds_v2f64(base, x[0], x[1]);
         lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        pipe_levels4(x, acc, thr32, col32);
+        // the samples are in registers: the stage goes back to the producer before they are worked on (a warp's
+        // shared-memory loads and its barrier arrival are carried out in order)
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        pipe_levels4(x, acc, thr32, col32);
         if (++s == P_STAGES) {
             s = 0;
             par ^= 1u;
@@ -2382,9 +2386,9 @@ __device__ __forceinline__ void pipe_stream_levels(const PipePlan* pp, PAcc& acc
         x[0] = x[1] = x[2] = x[3] = nan;
         if (stid < rem2) lds_v2f64(base, x[0], x[1]);
         if (stid + P_NS < rem2) lds_v2f64(base + P_NS * 16, x[2], x[3]);
-        pipe_levels4(x, acc, thr32, col32);
         __syncwarp();
         if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
+        pipe_levels4(x, acc, thr32, col32);
     }
     g += (uint32_t)ntiles;
 }
