@@ -157,6 +157,23 @@ __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) 
         __nanosleep(400);
     }
 }
+// Wait that suspends inside try_wait and is woken by the barrier: no polling sleep, no busy loop.
+__device__ __forceinline__ void mbar_wait_hint(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    for (;;) {
+        uint32_t done;
+        asm volatile(
+            "{\n"
+            ".reg .pred P1;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2, %3;\n"
+            "selp.u32 %0, 1, 0, P1;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(addr), "r"(parity), "r"(20000u)
+            : "memory");
+        if (done) break;
+    }
+}
 // TMA bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP).
 __device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile(
@@ -1472,7 +1489,7 @@ constexpr int P_NF = P_FW * 32;                // 128 finish threads
 constexpr int P_PW = 1;                        // plan loader warp
 constexpr int P_PLANS = 4;                     // plan slots
 constexpr uint32_t P_PLAN_LOG = 2;
-constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW) * 32;   // planners, producer, stream, finish
+constexpr int P_THREADS = (P_PW + 1 + P_SW + P_FW + 1) * 32;   // plan loader, producer, stream, finish, prologue
 constexpr int P_TILE = 4 * P_NS;               // 1536 doubles (12 KB) per ring stage
 constexpr int P_STAGES = 3;
 #ifndef KO_P_PF
@@ -1521,7 +1538,7 @@ struct alignas(16) PipePlan {
 };
 
 // What the finish warps need to agree on before their first scan: valid count, extremes, which bracket holds which
-// rank.  It follows from the stream warps' totals alone, so the last stream warp to hand off works it out once.
+// rank.  It follows from the stream warps' totals alone, so one thread (the prologue warp) works it out once per series.
 struct FinPro {
     unsigned n;                              // valid samples
     int ncapi;                               // capturing intervals
@@ -1540,7 +1557,6 @@ struct PipeResult {          // what the stream warps hand to the finish warps, 
     double sum[P_SW], mn[P_SW], mx[P_SW];          // per stream warp (summed in warp order: reproducible)
     // totals over all stream warps, added with shared-memory reductions, cleared by the finish warps
     unsigned t_nvalid, t_cA[P_NI], t_cin[P_NI], t_ncap[P_NI];
-    unsigned arrived;                    // stream warps that have handed off (the last one fills pro)
     FinPro pro;
     unsigned ovcnt[P_NI];                // captures that found the thread's private slots full, per interval
     unsigned ovn;                        // ... and in total: entries claimed in the shared overflow queue
@@ -1599,7 +1615,7 @@ struct PipeSmem {
     __device__ __forceinline__ uint64_t* bars() const { return reinterpret_cast<uint64_t*>(base + PO_BARS); }
 };
 
-enum { B_RING_FULL = 0, B_RING_EMPTY = 5, B_PLAN_FULL = 10, B_PLAN_FREE = 18, B_POOL_FULL = 26, B_POOL_FREE = 28 };
+enum { B_RING_FULL = 0, B_RING_EMPTY = 5, B_PLAN_FULL = 10, B_PLAN_FREE = 18, B_POOL_FULL = 26, B_POOL_FREE = 28, B_HANDOFF = 30 };
 static_assert(P_PLANS == (1 << P_PLAN_LOG) && B_PLAN_FREE - B_PLAN_FULL >= P_PLANS && B_POOL_FULL - B_PLAN_FREE >= P_PLANS, "barrier slots");
 
 __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(P_NF) : "memory"); }
@@ -2708,7 +2724,7 @@ __device__ __forceinline__ void fin_groups(const PipePlan* pp, const PipeResult*
     }
 }
 
-// Run by one thread (lane 0 of the last stream warp to hand off) once all totals of the series are in *res.
+// Run by one thread (lane 0 of the prologue warp) once all totals of the series are in *res.
 __device__ __noinline__ void fin_prologue(const PipePlan* pp, PipeResult* res, int nq, double q0, double q1, double q2,
                                           double q3, int wide) {
     (void)wide;
@@ -2807,7 +2823,7 @@ __device__ __forceinline__ int pipe_finish(const SeriesArgs& a, const PipePlan* 
 #ifdef KO_PHASE_TIMING
     unsigned long long _ft = clock64();
 #endif
-    // ---- what the last stream warp worked out (fin_prologue)
+    // ---- what the prologue warp worked out (fin_prologue)
     const FinPro* pro = &res->pro;
     const unsigned n = pro->n;
     if (ftid == 32) {   // the plain statistics do not depend on the selection: written here, off the critical path
@@ -3003,15 +3019,15 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
         }
         for (int s = 0; s < P_PLANS; ++s) {
             mbar_init(sm.bars() + B_PLAN_FULL + s, 1);
-            mbar_init(sm.bars() + B_PLAN_FREE + s, P_SW + 2);   // stream warps + finish + producer
+            mbar_init(sm.bars() + B_PLAN_FREE + s, P_SW + 3);   // stream warps + finish + producer + prologue
         }
         for (int s = 0; s < 2; ++s) {
-            mbar_init(sm.bars() + B_POOL_FULL + s, P_SW);
+            mbar_init(sm.bars() + B_POOL_FULL + s, 1);      // the prologue warp, after ...
+            mbar_init(sm.bars() + B_HANDOFF + s, P_SW);     // ... every stream warp has handed off
             mbar_init(sm.bars() + B_POOL_FREE + s, 1);
             PipeResult* r0 = sm.res(s);
             r0->t_nvalid = 0;
             r0->ovn = 0;
-            r0->arrived = 0;
             for (int i = 0; i < P_NI; ++i) r0->ovcnt[i] = r0->t_cA[i] = r0->t_cin[i] = r0->t_ncap[i] = 0;
         }
         {
@@ -3174,22 +3190,35 @@ __global__ void __launch_bounds__(P_THREADS, 1) series_pipe(SeriesArgs a) {
 #pragma unroll
                     for (int i = 0; i < P_NI; ++i) red_shared_add(&res->t_ncap[i], wpc[i]);
                 }
-                if (lane == 0) {   // the last stream warp to get here prepares the finish warps' common ground
-                    __threadfence_block();
-                    const unsigned before = atom_shared_add(&res->arrived, 1u);
-                    if (before == (unsigned)P_SW - 1u) {
-                        __threadfence_block();
-                        res->arrived = 0;
-                        if (!pp->vals) fin_prologue(pp, res, a.nq, a.q[0], a.q[1], a.q[2], a.q[3], a.wide);
-                        __threadfence_block();
-                    }
-                }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(sm.bars() + B_POOL_FULL + pool);
+                if (lane == 0) mbar_arrive(sm.bars() + B_HANDOFF + pool);
                 ++c;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(sm.bars() + B_PLAN_FREE + slot);
+        }
+    } else if (warp == P_PW + 1 + P_SW + P_FW) {
+        // ================================================================ PROLOGUE
+        // One lane between the stream warps and the finish warps: once every stream warp has handed a series off,
+        // it works out what all finish threads need first (totals, nearest ranks, which interval answers which
+        // quantile) and only then opens the pool to them.  The stream warps are the slower side and go straight
+        // on to the next series; the finish warps work a series behind and have the time.
+        if (lane == 0) {
+            uint32_t c = 0;
+            for (uint32_t k = 0;; ++k) {
+                const uint32_t slot = k & (P_PLANS - 1);
+                mbar_wait_sleep(sm.bars() + B_PLAN_FULL + slot, (k >> P_PLAN_LOG) & 1u);
+                const PipePlan* pp = sm.plan(slot);
+                if (pp->sid < 0) break;
+                if (!pp->defer) {
+                    const uint32_t pool = c & 1u;
+                    mbar_wait_hint(sm.bars() + B_HANDOFF + pool, (c >> 1) & 1u);
+                    if (!pp->vals) fin_prologue(pp, sm.res(pool), a.nq, a.q[0], a.q[1], a.q[2], a.q[3], a.wide);
+                    mbar_arrive(sm.bars() + B_POOL_FULL + pool);
+                    ++c;
+                }
+                mbar_arrive(sm.bars() + B_PLAN_FREE + slot);
+            }
         }
     } else {
         // ================================================================ FINISH
