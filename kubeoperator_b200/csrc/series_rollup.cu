@@ -10,10 +10,11 @@
 //   series_plan       — one warp per long series: a strided 1024-point pre-sample, sorted in registers with
 //                       shuffles, gives a value bracket per quantile (or a list of distinct levels for
 //                       integer-valued series); the plan goes to a window in scratch
-//   series_pipe       — persistent, one CTA of 22 warps per SM, warp-specialised: plan loader, TMA producer
-//                       (cp.async.bulk + mbarrier ring), 12 stream warps that fuse the statistics with "count
-//                       below the bracket, keep what is inside it" in ONE pass, 8 finish warps that select the
-//                       exact order statistic among the kept candidates of the previous series meanwhile
+//   series_pipe       — persistent, one CTA of 23 warps per SM, warp-specialised: plan loader, TMA producer
+//                       (cp.async.bulk + mbarrier ring, tiles asked into L2 ahead of it), 12 stream warps that
+//                       fuse the statistics with "count below the bracket, keep what is inside it" in ONE pass,
+//                       a prologue warp, 8 finish warps that select the exact order statistic among the kept
+//                       candidates of the previous series meanwhile
 //   series_pipe again — second attempt with wide brackets over the few quantiles the first could not answer
 //   series_long       — exact multi-pass slow path (histogram refinement in key space) over what is left
 // Every bracket is verified by exact counts, so the result is always the oracle's value.
