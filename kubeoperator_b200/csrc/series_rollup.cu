@@ -1544,7 +1544,7 @@ struct FinPro {
     unsigned n;                              // valid samples
     int ncapi;                               // capturing intervals
     int failmask;                            // quantiles this attempt cannot answer (bracket missed, queue full)
-    unsigned arrived_pad;
+    unsigned pad;
     double sum, mn, mx;
     unsigned long long kA[P_NI];             // effective bracket start per interval
     int ish[P_NI];                           // (key - kA) >> ish is the sub-bracket
