@@ -112,13 +112,20 @@ int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t* offsets, 
                      const double* q, int nq, double* out_sum, double* out_mean, double* out_min,
                      double* out_max, double* out_last, int64_t* out_count, double* out_quantiles);
 /* Same with DEVICE pointers (q stays a host array); enqueues on `stream` and returns.  The offsets are then
- * checked on the GPU only: a series whose offsets decrease is skipped (its outputs are left untouched) and
- * nothing is reported, so validate offsets that come from an untrusted source before the call.  Scratch of the
+ * checked on the GPU only: a series whose offsets decrease is skipped (its outputs are left untouched) and the
+ * device error flag is raised: read it with ko_series_status() after the call.  Scratch of the
  * context is reused by every call: calls on one context must not overlap on the GPU. */
 int ko_series_rollup_dev(ko_ctx* ctx, const double* d_values, const int64_t* d_offsets,
                          int64_t n_series, const double* q, int nq, double* d_out_sum,
                          double* d_out_mean, double* d_out_min, double* d_out_max, double* d_out_last,
                          int64_t* d_out_count, double* d_out_quantiles, void* stream);
+
+/* Outcome of the most recent ko_series_rollup_dev on this ctx as the GPU saw it (waits for that call's kernels):
+ * out[0] = long series (> 1024 samples) of the call, out[1] = series whose first one-pass attempt had to be repeated
+ * with wider intervals, out[2] = series that went on to the exact multi-pass slow path, out[3] = device error flag
+ * (non-zero: at least one series had decreasing offsets or a length >= 2^31 and was skipped).  The host-pointer
+ * ko_series_rollup reports the same through its return code and ko_counters.  No counterpart in the reference. */
+int ko_series_status(ko_ctx* ctx, int32_t* out4);
 
 /* Same kernels and results as ko_series_rollup_dev, for callers that must not allocate device memory when
  * they ask for a rollup: a worker whose GPU memory belongs entirely to another component's pool, a request

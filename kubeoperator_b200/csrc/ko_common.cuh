@@ -47,6 +47,8 @@ struct ko_ctx {
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the long-series kernels of the last series rollup
     cudaEvent_t ev_p0 = nullptr, ev_p1 = nullptr;  // around its first series_pipe launch alone (roofline timing)
     bool k_timed = false;
+    cudaStream_t last_series_stream = nullptr;  // stream of the last ko_series_rollup_dev
+    int* last_series_scratch = nullptr;         // its counters (device)
     KoBuf scratch;       // work lists / counters / sort buffers (kernel scratch)
     KoBuf stage[2];      // double-buffered device staging of series values
     KoBuf in_small;      // small inputs (offsets, node columns, ...)

@@ -1,0 +1,1490 @@
+// series_flow — window statistics + exact nearest-rank quantiles of long series (> 1024 samples) in ONE pass over
+// HBM.  BUILD-DEFINED semantics (oracle/rollup_oracle.py series_stats; include/korollup.h): the reference only
+// ships PromQL strings for range windows (core/apps/kubeops_api/prometheus_client.py:90-111).
+//
+// One persistent CTA per SM, 28 warps, warp-specialised; three series are in flight per CTA:
+//   PLANNER   (4 warps)  series k+1: strided pre-sample of up to 4096 points (2048 aligned pairs), two rounds of
+//                        256-bin histograms over the 32-bit "high keys" (top half of the order-preserving image of
+//                        an f64) give, per wanted quantile, a key interval [A, A+W] that holds its rank with
+//                        ~3 sigma; heavy tie levels at the interval ends are listed so that they are counted instead
+//                        of stored.
+//   PRODUCER  (1 lane)   series k: cp.async.bulk (TMA, SASS UBLKCP) of 16 KB groups into a 6-group ring, completion
+//                        on mbarrier transaction counts, groups asked into L2 ahead of the ring.
+//   STREAM    (15 warps) series k: each warp owns whole 4 KB stages.  Per sample: sum (f64), and on the high key
+//                        alone (integer pipe) the running-extreme / NaN filter, "count below A" per interval
+//                        (sub.cc / subc) and the in-interval test; the in-interval flags go to a bitmap ring
+//                        (vote.ballot).  Samples are never compared as doubles on the common path, and nothing
+//                        irregular happens here.
+//   COLLECTOR (4 warps)  series k, one ring group behind: reads the bitmaps of a scanned group, copies the flagged
+//                        samples from the ring to the candidate pool (shared memory, spilling to global scratch) and
+//                        only then hands the ring group back to the producer.
+//   FINISH    (4 warps)  series k-1: combines the warps' partial statistics, checks every interval by exact counts
+//                        and selects the wanted order statistics among the candidates by 256-bin histogram refinement
+//                        in 64-bit key space; writes the outputs.
+// Whatever the plan cannot guarantee (a rank outside its interval, an overflowing pool, a pre-sample with almost no
+// valid points) is detected from exact counts and the series goes to the next attempt's list: a second series_flow
+// launch with 5-sigma intervals, then series_long.  The results are therefore always the oracle's.
+#include "series_common.cuh"
+
+namespace {
+
+constexpr int F_NS = 11;                       // stream warps (28 warps: registers are granted per 4 warps)
+constexpr int F_NP = 8;                        // planner warps
+constexpr int F_NC = 4;                        // collector warps
+constexpr int F_NF = 8;                        // finish warps
+constexpr int F_WARPS = 1 + F_NP + F_NC + F_NF + F_NS;
+constexpr int F_THREADS = F_WARPS * 32;        // 896
+// The scheduler prefers the warp with the highest id: the serial roles (whose latency everything else waits for)
+// come last, the stream warps (throughput, always something to do) first.
+constexpr int F_W_STREAM = 0;                  // first stream warp
+constexpr int F_W_FIN = F_W_STREAM + F_NS;     // first finish warp
+constexpr int F_W_COLL = F_W_FIN + F_NF;       // first collector warp
+constexpr int F_W_PLAN = F_W_COLL + F_NC;      // first planner warp
+constexpr int F_W_PROD = F_W_PLAN + F_NP;      // the producer warp
+constexpr int F_STAGE = 512;                   // samples per ring stage (4 KB): 4 warp steps of 128 samples
+constexpr int F_STAGE_BYTES = F_STAGE * 8;
+constexpr int F_GS = 4;                        // stages per ring group: one TMA copy and one pair of barriers (16 KB)
+constexpr int F_GROUP_BYTES = F_GS * F_STAGE_BYTES;
+constexpr int F_NGROUPS = 7;
+constexpr int F_NSTAGES = F_NGROUPS * F_GS;
+constexpr int F_BG = 8;                        // groups of the bitmap ring (64 words each)
+constexpr int F_PF = 3;                        // groups asked into L2 ahead of the ring
+constexpr int F_ND = 4;                        // series slots (descriptor + plan + partials)
+constexpr int F_SMAX = 4096;                   // largest pre-sample
+constexpr int F_POOL = 7168;                   // candidate keys held in shared memory
+constexpr int F_NH = 8;                        // heavy tie levels per plan
+constexpr int F_LIST = 64;                     // candidates selected by direct rank counting
+constexpr int F_NT = 2 * NI_MAX;               // interval ends refined in the planner's second round
+constexpr int F_DOUBLE_MAXL = 49152;           // longest series for which two series share the candidate pool
+constexpr int F_MIN_SAMPLE = 64;               // fewer valid pre-sample points: the series is deferred
+constexpr uint32_t HK_PINF = 0xFFF00000u;      // high key of +inf; anything above is a (positive) NaN
+constexpr uint32_t HK_NINF = 0x000FFFFFu;      // high key of -inf; anything below is a (negative) NaN
+constexpr uint32_t HK_NONE = 0xFFFFFFFFu;      // a sample that takes no part (stale or outside the series)
+constexpr uint32_t HK_UNUSED = 0xFFFFFFFEu;    // A of an unused interval (W = 0): no key equals it, HK_NONE is above
+
+enum { FB_FULL = 0, FB_EMPTY = FB_FULL + F_NGROUPS, FB_BMFULL = FB_EMPTY + F_NGROUPS, FB_BMEMPTY = FB_BMFULL + F_BG,
+       FB_DESC = FB_BMEMPTY + F_BG, FB_PLAN = FB_DESC + F_ND, FB_FREE = FB_PLAN + F_ND, FB_SDONE = FB_FREE + F_ND,
+       FB_CDONE = FB_SDONE + F_ND, FB_START = FB_CDONE + F_ND, FB_POOL = FB_START + F_ND, FB_COUNT = FB_POOL + 2 };
+
+struct alignas(16) FlowSlot {
+    // descriptor (planner thread 0)
+    int sid;                 // < 0: no more work
+    int L;
+    int lead;                // elements in front of the series inside its first stage (0 or 1: 16-byte alignment)
+    int nstages;
+    uint32_t g0;             // ring stage counter of the series' first stage (a multiple of F_GS)
+    uint32_t total_bytes;    // TMA bytes of the whole series (a multiple of 16)
+    int tail_fix;            // the last element is stored by hand (it ends the whole array on an odd element)
+    int depth1;              // long series: the planner stays one series ahead only (L2 footprint of its gather)
+    const double* src;       // 16-byte aligned address of stage 0
+    long long start;         // element index of the series in values
+    // plan (planner)
+    int ni;                  // capture intervals, ascending and disjoint
+    int defer;               // the plan gives up: the series goes to the next attempt
+    int konst;               // the pre-sample holds one single value: no capture, the finish checks min == max
+    int nheavy;
+    uint32_t A[NI_MAX], W[NI_MAX];   // interval i holds the samples with A <= high key <= A + W
+    int qiv[NI_MAX];         // interval of quantile j
+    double mn_seed, mx_seed; // valid samples of the series (or +inf / -inf): start of the running extremes
+    unsigned long long heavy[F_NH];  // keys of heavy tie levels (zero canonical)
+};
+
+struct alignas(16) FlowPartial {
+    double sum, mn, mx;
+    unsigned nan;
+    unsigned c[NI_MAX];
+    unsigned pad[3];
+};
+
+struct PlanScratch {      // planner scratch
+    unsigned long long kmin, kmax;
+    unsigned nvalid;
+    int work;
+    int tbin[F_NT];          // round-1 bin of interval end t (A ends even, B ends odd), -1: open end
+    unsigned trank[F_NT];    // sample rank looked for at that end (1-based, relative to its bin after round 1)
+    unsigned tsub[F_NT];     // sub-bin found in round 2
+    unsigned tcum[F_NT];     // sample keys below that sub-bin (whole sample)
+    unsigned tcnt[F_NT];     // sample keys inside that sub-bin
+    unsigned long long hmin[F_NT], hmax[F_NT];   // smallest / largest sample key of that sub-bin (tie level check)
+};
+
+struct FinState {
+    double sum, mn, mx, last;
+    unsigned nvalid;
+    unsigned cb[NI_MAX];
+    int fail;
+    int why;                 // first reason of a failure: 0 plan deferred, 1 rank below, 2 rank above, 3 pool overflow,
+                             // 4 constant sample but not constant series, 5 no interval, 6 selection
+    int pending;
+    int st[NI_MAX];          // per quantile: 0 histogram round, 1 collect, 2 done, 3 failed
+    int sh[NI_MAX];
+    unsigned rho[NI_MAX];
+    unsigned long long lo[NI_MAX];
+    unsigned long long ans[NI_MAX];
+    unsigned list_n[NI_MAX];
+};
+enum { Q_HIST = 0, Q_COLLECT = 1, Q_DONE = 2, Q_FAIL = 3 };
+
+// Development aid (-DKO_FLOW_TIMING): cycles CTA 0 spends in each phase of each role, read by ko_debug_flow_phases.
+#ifdef KO_FLOW_TIMING
+__device__ unsigned long long g_flow_phase[64];
+#define FT_BEGIN(cond)                     \
+    unsigned long long _ft = clock64();    \
+    const bool _ftc = (cond)
+#define FT_MARK(slot)                                            \
+    do {                                                         \
+        if (_ftc) {                                              \
+            const unsigned long long _t = clock64();             \
+            atomicAdd(&g_flow_phase[slot], _t - _ft);            \
+            _ft = _t;                                            \
+        }                                                        \
+    } while (0)
+#else
+#define FT_BEGIN(cond) do { } while (0)
+#define FT_MARK(slot) do { } while (0)
+#endif
+
+constexpr size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+constexpr size_t FO_RING = 0;
+constexpr size_t FO_POOL = FO_RING + (size_t)F_NSTAGES * F_STAGE_BYTES;
+constexpr size_t FO_HK = FO_POOL + (size_t)F_POOL * 8;
+constexpr size_t FO_HIST1 = FO_HK + (size_t)F_SMAX * 8;
+constexpr size_t FO_CUM = FO_HIST1 + 256 * 4;
+constexpr size_t FO_HIST2 = FO_CUM + 272 * 4;
+constexpr size_t FO_LUT = FO_HIST2 + (size_t)F_NT * 256 * 4;
+constexpr size_t FO_FBINS = FO_LUT + 256;
+constexpr size_t FO_FLISTK = FO_FBINS + (size_t)NI_MAX * 256 * 4;
+constexpr size_t FO_FLISTM = FO_FLISTK + (size_t)NI_MAX * F_LIST * 8;
+constexpr size_t FO_BITMAP = FO_FLISTM + (size_t)NI_MAX * F_LIST * 4;
+constexpr size_t FO_SLOTS = FO_BITMAP + (size_t)F_BG * F_GS * 64;
+constexpr size_t FO_PART = FO_SLOTS + align_up(F_ND * sizeof(FlowSlot), 16);
+constexpr size_t FO_PS = FO_PART + (size_t)F_ND * F_NS * sizeof(FlowPartial);
+constexpr size_t FO_FS = FO_PS + align_up(sizeof(PlanScratch), 16);
+constexpr size_t FO_PSTATE = FO_FS + align_up(sizeof(FinState), 16);   // csm[2][F_NC], cgl[2][F_NC], ovf[2], hcnt[2][F_NH]
+constexpr int F_PSTATE_WORDS = 4 * F_NC + 2 + 2 * F_NH;
+constexpr size_t FO_BARS = FO_PSTATE + align_up(F_PSTATE_WORDS * 4, 16);
+constexpr size_t FLOW_SMEM_BYTES = FO_BARS + (size_t)FB_COUNT * 8;
+static_assert(FLOW_SMEM_BYTES <= 232448, "series_flow must fit the 227 KB of one SM");
+static_assert(sizeof(FlowPartial) == 64, "partials are 64 bytes");
+
+struct FlowSmem {
+    unsigned char* base;
+    __device__ __forceinline__ unsigned char* ring() const { return base + FO_RING; }
+    __device__ __forceinline__ unsigned long long* pool() const { return reinterpret_cast<unsigned long long*>(base + FO_POOL); }
+    __device__ __forceinline__ unsigned long long* skeys() const { return reinterpret_cast<unsigned long long*>(base + FO_HK); }
+    __device__ __forceinline__ unsigned* hist1() const { return reinterpret_cast<unsigned*>(base + FO_HIST1); }
+    __device__ __forceinline__ unsigned* cum() const { return reinterpret_cast<unsigned*>(base + FO_CUM); }
+    __device__ __forceinline__ unsigned* hist2() const { return reinterpret_cast<unsigned*>(base + FO_HIST2); }
+    __device__ __forceinline__ unsigned char* lut() const { return base + FO_LUT; }
+    __device__ __forceinline__ unsigned* fbins() const { return reinterpret_cast<unsigned*>(base + FO_FBINS); }
+    __device__ __forceinline__ unsigned long long* flistk() const { return reinterpret_cast<unsigned long long*>(base + FO_FLISTK); }
+    __device__ __forceinline__ unsigned* flistm() const { return reinterpret_cast<unsigned*>(base + FO_FLISTM); }
+    __device__ __forceinline__ unsigned char* bitmap() const { return base + FO_BITMAP; }
+    __device__ __forceinline__ FlowSlot* slot(int d) const { return reinterpret_cast<FlowSlot*>(base + FO_SLOTS) + d; }
+    __device__ __forceinline__ FlowPartial* part(int d, int w) const {
+        return reinterpret_cast<FlowPartial*>(base + FO_PART) + d * F_NS + w;
+    }
+    __device__ __forceinline__ PlanScratch* ps() const { return reinterpret_cast<PlanScratch*>(base + FO_PS); }
+    __device__ __forceinline__ FinState* fs() const { return reinterpret_cast<FinState*>(base + FO_FS); }
+    __device__ __forceinline__ unsigned* csm() const { return reinterpret_cast<unsigned*>(base + FO_PSTATE); }   // [2][F_NC]
+    __device__ __forceinline__ unsigned* cgl() const { return csm() + 2 * F_NC; }                               // [2][F_NC]
+    __device__ __forceinline__ unsigned* ovf() const { return cgl() + 2 * F_NC; }
+    __device__ __forceinline__ unsigned* hcnt() const { return ovf() + 2; }   // [2][F_NH]
+    __device__ __forceinline__ uint64_t* bar(int i) const { return reinterpret_cast<uint64_t*>(base + FO_BARS) + i; }
+};
+
+// Where one series' candidates live: a window of the shared-memory pool and a window of the CTA's global spill,
+// each cut into F_NC equal parts, one per collector warp (no atomics between them).  Counters and spill windows
+// alternate with the series number; the shared-memory pool is halved the same way when series are short enough
+// (two series in flight), otherwise it is one window that the next series may only enter once the finish warps are
+// done with the previous one -- until then its candidates go to the spill.
+struct PoolWin {
+    uint32_t s_base, s_sub;     // entries: collector c owns pool[s_base + c * s_sub ...)
+    uint32_t g_base, g_sub;     //          and spill[g_base + c * g_sub ...)
+    int buf;                    // k & 1: which set of counters / spill half
+    int bar;                    // FB_POOL + bar guards the shared-memory window
+    uint32_t use;               // how often that window has been used before
+};
+__device__ __forceinline__ PoolWin pool_window(bool single, uint32_t k, int spill_cap) {
+    PoolWin w;
+    w.buf = (int)(k & 1u);
+    w.g_sub = (uint32_t)spill_cap / 2 / F_NC;
+    w.g_base = w.buf * ((uint32_t)spill_cap / 2);
+    if (single) {
+        w.bar = 0;
+        w.use = k;
+        w.s_base = 0;
+        w.s_sub = F_POOL / F_NC;
+    } else {
+        w.bar = w.buf;
+        w.use = k >> 1;
+        w.s_sub = F_POOL / 2 / F_NC;
+        w.s_base = w.buf * (F_POOL / 2);
+    }
+    return w;
+}
+
+__device__ __forceinline__ void plan_sync() { asm volatile("bar.sync 3, %0;" ::"n"(F_NP * 32) : "memory"); }
+__device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(F_NF * 32) : "memory"); }
+
+__device__ __forceinline__ uint32_t hi_key(uint32_t h) {   // top half of ko_okey()
+    return h ^ (((uint32_t)((int32_t)h >> 31)) | 0x80000000u);
+}
+__device__ __forceinline__ bool bits_nan(uint32_t h, uint32_t l) {
+    const uint32_t ah = h & 0x7FFFFFFFu;
+    return ah > 0x7FF00000u || (ah == 0x7FF00000u && l != 0u);
+}
+__device__ __forceinline__ uint64_t createpolicy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+// TMA bulk copy with an L2 eviction hint: the streamed samples are read once and should not push out the lines
+// the planner gathered for the next series.
+__device__ __forceinline__ void tma_bulk_g2s_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar,
+                                                  uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::
+            "r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+        : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_cg_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u32f(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts_f64(uint32_t addr, double x) {
+    asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(x) : "memory");
+}
+__device__ __forceinline__ void sts_v4u32(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void red_shared_max_u64(const void* p, unsigned long long v) {
+    asm volatile("red.shared.max.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
+}
+__device__ __forceinline__ void red_shared_min_u64(const void* p, unsigned long long v) {
+    asm volatile("red.shared.min.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ double ld_cg_f64(const double* p) {
+    double v;
+    asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(p));
+    return v;
+}
+// 16 bytes global -> shared without passing through registers (LDGSTS): the planner's gather
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void lds_v2u32(uint32_t addr, uint32_t& a, uint32_t& b) {
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
+}
+__device__ __forceinline__ void sts_u32f(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// Locate the bin whose cumulative count first reaches rho (1-based) in a 256-bin histogram; one full warp.
+// Returns false when the histogram holds fewer than rho entries.  total = all entries.
+__device__ __forceinline__ bool warp_find_bin(const unsigned* hist, unsigned rho, int lane, int& bin, unsigned& before,
+                                              unsigned& cnt, unsigned& total) {
+    unsigned c[8];
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        c[i] = hist[lane * 8 + i];
+        s += c[i];
+    }
+    unsigned incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    total = __shfl_sync(0xffffffffu, incl, 31);
+    const unsigned ballot = __ballot_sync(0xffffffffu, incl >= rho);
+    if (ballot == 0u || rho == 0u) return false;
+    const int src = __ffs(ballot) - 1;
+    int d = 0;
+    unsigned b = 0, n = 0;
+    if (lane == src) {
+        unsigned run = incl - s;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (n == 0u && run + c[i] >= rho) {
+                d = i;
+                b = run;
+                n = c[i];
+            }
+            if (n == 0u) run += c[i];
+        }
+        d += lane * 8;
+    }
+    bin = __shfl_sync(0xffffffffu, d, src);
+    before = __shfl_sync(0xffffffffu, b, src);
+    cnt = __shfl_sync(0xffffffffu, n, src);
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------ planner
+__device__ __forceinline__ int sample_size(int L) {
+    int s = 256;
+    while (s < F_SMAX && s * 8 <= L) s <<= 1;   // about L/8 .. L/16 points, 256 .. 4096
+    return s;
+}
+// The pre-sample is taken as S/4 aligned runs of four neighbouring samples: one 32-byte request fetches four points,
+// and what bounds the gather is the number of memory requests an SM gets through (about one in five cycles beside
+// the bulk stream), not their size.  For samples that are independent from one 15 s step to the next this is as good
+// as S separate points; for a smooth series the four are correlated and the intervals come out narrower than the
+// sigma they claim -- that costs such a series a second attempt now and then (the exact counts notice), never a
+// wrong result.
+__device__ __forceinline__ int quad_pos(int j, int L, int nquad, int lead4) {
+    int p = (int)(((2LL * j + 1) * (long long)L) / (2LL * nquad));
+    p -= (lead4 + p) & 3;
+    if (p < 0) p += 4;
+    if (p + 3 >= L) p -= 4;
+    return p;
+}
+
+// All planner threads (ptid in [0, F_NP * 32)).  Fills the plan fields of the slot.
+__device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem& sm, FlowSlot* sl, int ptid, bool single,
+                                             uint32_t kser) {
+    constexpr int NT = F_NP * 32;
+    PlanScratch* ps = sm.ps();
+    const int lane = ptid & 31;
+    const int L = sl->L;
+    const double* v = a.values + sl->start;
+    const int nq = a.nq;
+    FT_BEGIN(blockIdx.x == 0 && ptid == 0);
+    const double pinf = __longlong_as_double(0x7FF0000000000000LL);
+    if (ptid == 0) {
+        sl->ni = 0;
+        sl->defer = 0;
+        sl->konst = 0;
+        sl->nheavy = 0;
+        sl->mn_seed = pinf;
+        sl->mx_seed = -pinf;
+        ps->kmin = ~0ull;
+        ps->kmax = 0ull;
+        ps->nvalid = 0;
+    }
+    if (nq == 0) {
+        plan_sync();
+        return;
+    }
+    const int S = sample_size(L);
+    const int nquad = S / 4;
+    const int qper = (nquad + NT - 1) / NT;   // runs of four per thread: 1 (a 256-point sample uses half the threads) .. 8
+    const int per = S / NT;          // sample keys per thread in the histogram rounds
+    const int lead4 = (int)((reinterpret_cast<uintptr_t>(v) >> 3) & 3u);
+    unsigned long long* sk = sm.skeys();
+    plan_sync();
+    // ---- gather: all 32-byte loads of a thread in flight together, raw bits to shared memory; then a compact loop
+    // turns the thread's own entries into order-preserving 64-bit keys (code size matters more than ILP here: the
+    // serial roles run through their code once per series and live on instruction-cache misses otherwise)
+    {
+        unsigned long long kmn = ~0ull, kmx = 0ull;
+        unsigned nv = 0;
+        {
+            const uint32_t sk32 = smem_u32(sk);
+#pragma unroll 1
+            for (int u = 0; u < qper; ++u) {
+                const int j = ptid + u * NT;
+                if (j < nquad) {
+                    const double* src = v + quad_pos(j, L, nquad, lead4);
+                    cp_async16(sk32 + (uint32_t)j * 32u, src);
+                    cp_async16(sk32 + (uint32_t)j * 32u + 16u, src + 2);
+                }
+            }
+            cp_async_wait_all();
+        }
+        __syncwarp();
+#pragma unroll 1
+        for (int u = 0; u < qper * 4; ++u) {
+            const int idx = 4 * (ptid + (u >> 2) * NT) + (u & 3);
+            if (idx < S) {
+                const double xx = __longlong_as_double((long long)sk[idx]);
+                const bool ok = (xx == xx);
+                const unsigned long long k = ok ? ko_okey(xx + 0.0) : KO_KEY_NAN;
+                sk[idx] = k;
+                if (ok) {
+                    kmn = k < kmn ? k : kmn;
+                    kmx = k > kmx ? k : kmx;
+                    nv++;
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long a0 = __shfl_xor_sync(0xffffffffu, kmn, o);
+            const unsigned long long a1 = __shfl_xor_sync(0xffffffffu, kmx, o);
+            kmn = a0 < kmn ? a0 : kmn;
+            kmx = a1 > kmx ? a1 : kmx;
+        }
+        nv = __reduce_add_sync(0xffffffffu, nv);
+        if (lane == 0 && nv) {
+            red_shared_min_u64(&ps->kmin, kmn);
+            red_shared_max_u64(&ps->kmax, kmx);
+            red_shared_add(&ps->nvalid, nv);
+        }
+        for (int i = ptid; i < 256; i += NT) sm.hist1()[i] = 0;
+        for (int i = ptid; i < F_NT * 256; i += NT) sm.hist2()[i] = 0;
+        for (int i = ptid; i < 256 / 4; i += NT) reinterpret_cast<uint32_t*>(sm.lut())[i] = 0;
+    }
+    plan_sync();
+    FT_MARK(10);   // gather
+    const unsigned ns = ps->nvalid;
+    const unsigned long long kmin64 = ps->kmin, kmax64 = ps->kmax;
+    const uint32_t hkmin = (uint32_t)(kmin64 >> 32), hkmax = (uint32_t)(kmax64 >> 32);
+    if (ns < (unsigned)F_MIN_SAMPLE || kmin64 == kmax64 || hkmin == hkmax) {
+        // almost no valid points or a spread below the resolution of the high key (not for this kernel: deferred),
+        // or one single value (no capture; the finish warps check min == max over the whole series)
+        if (ptid == 0) {
+            if (ns >= (unsigned)F_MIN_SAMPLE && kmin64 == kmax64) sl->konst = 1;
+            else sl->defer = 1;
+            if (ns) {
+                sl->mn_seed = ko_key2d(kmin64);
+                sl->mx_seed = ko_key2d(kmax64);
+            }
+        }
+        plan_sync();
+        return;
+    }
+    // ---- round 1: 256 bins over [hkmin, hkmax]
+    const uint32_t R = hkmax - hkmin;
+    const int sh1 = max(0, 32 - __clz((int)R) - 8);
+    const int sh2 = sh1 >= 8 ? sh1 - 8 : 0;
+    const uint32_t submask = (1u << (sh1 - sh2)) - 1u;
+#pragma unroll 1
+    for (int i = 0; i < per; ++i) {
+        const uint32_t k = (uint32_t)(sk[ptid + i * NT] >> 32);
+        if (k != HK_NONE) red_shared_add(&sm.hist1()[(k - hkmin) >> sh1], 1u);
+    }
+    plan_sync();
+    if (ptid < 32) {   // exclusive prefix of the 256 bins -> cum[0..256]
+        unsigned c[8];
+        unsigned sum8 = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            c[i] = sm.hist1()[lane * 8 + i];
+            sum8 += c[i];
+        }
+        unsigned incl = sum8;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        unsigned run = incl - sum8;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            sm.cum()[lane * 8 + i] = run;
+            run += c[i];
+        }
+        if (lane == 31) sm.cum()[256] = run;
+        __syncwarp();
+        // interval ends in sample ranks; lane t handles end t (A ends even, B ends odd)
+        int tb = -1;
+        if (lane < F_NT) {
+            const int j = lane >> 1;
+            unsigned tr = 0;
+            if (j < nq) {
+                const double z = a.wide ? 5.0 : 3.0;
+                const double p = a.q[j];
+                const double n = (double)ns;
+                double fpc = 1.0 - (double)S / (double)L;
+                fpc = fpc < 0.05 ? 0.05 : fpc;
+                const double t = p * n;
+                const double dl = z * sqrt(p * (1.0 - p) * n * fpc) + 2.0;
+                const long long r = (lane & 1) ? (long long)ceil(t + dl) + 1 : (long long)floor(t - dl);
+                if (r >= 1 && r <= (long long)ns) {
+                    // the bin holding sample rank r: cum[b] < r <= cum[b + 1]
+                    int lo = 0, hi = 255;
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) >> 1;
+                        if (sm.cum()[mid] < (unsigned)r) lo = mid;
+                        else hi = mid - 1;
+                    }
+                    tb = lo;
+                    tr = (unsigned)r - sm.cum()[lo];
+                }
+            }
+            ps->tbin[lane] = tb;
+            ps->trank[lane] = tr;
+            ps->tsub[lane] = 0;
+            ps->tcum[lane] = 0;
+            ps->tcnt[lane] = 0;
+            ps->hmin[lane] = ~0ull;
+            ps->hmax[lane] = 0ull;
+        }
+        // the look-up table "which ends live in this bin": byte-wide OR through 32-bit atomics
+        if (lane < F_NT && tb >= 0)
+            atomicOr(reinterpret_cast<unsigned*>(sm.lut()) + (tb >> 2), (1u << lane) << ((tb & 3) * 8));
+    }
+    plan_sync();
+    FT_MARK(11);   // round 1 + targets
+    // ---- round 2: 256 sub-bins inside the bins that hold an interval end
+#pragma unroll 1
+    for (int i = 0; i < per; ++i) {
+        const uint32_t k = (uint32_t)(sk[ptid + i * NT] >> 32);
+        if (k == HK_NONE) continue;
+        const uint32_t d = k - hkmin;
+        unsigned m = sm.lut()[d >> sh1];
+        const uint32_t sub = (d >> sh2) & submask;
+        while (m) {
+            const int t = __ffs(m) - 1;
+            m &= m - 1;
+            red_shared_add(&sm.hist2()[t * 256 + sub], 1u);
+        }
+    }
+    plan_sync();
+    // planner warp w resolves the ends w, w + F_NP, ...
+    unsigned heavy_any = 0;
+    for (int t = ptid >> 5; t < F_NT; t += F_NP) {
+        const int tb = ps->tbin[t];
+        if (tb >= 0) {
+            int bin;
+            unsigned before, cnt, total;
+            const bool ok = warp_find_bin(sm.hist2() + t * 256, ps->trank[t], lane, bin, before, cnt, total);
+            if (lane == 0) {
+                if (!ok) {   // cannot happen: rank r lies in this bin by construction
+                    bin = (t & 1) ? (int)submask : 0;
+                    before = (t & 1) ? total : 0;
+                    cnt = 0;
+                }
+                ps->tsub[t] = (unsigned)bin;
+                ps->tcum[t] = sm.cum()[tb] + before;
+                ps->tcnt[t] = cnt;
+            }
+        }
+    }
+    plan_sync();
+    FT_MARK(12);   // round 2
+    // ---- heavy tie levels: a sub-bin at an interval end that holds many sample points may be one repeated value
+    // (an integer-valued gauge, a clamp).  It is, when the smallest and the largest sample key inside it are equal.
+    const unsigned heavy_min = 16;
+#pragma unroll
+    for (int t = 0; t < F_NT; ++t) heavy_any |= (ps->tbin[t] >= 0 && ps->tcnt[t] >= heavy_min) ? (1u << t) : 0u;
+    if (heavy_any) {
+        for (int i = 0; i < per; ++i) {
+            const unsigned long long key = sk[ptid + i * NT];
+            const uint32_t k = (uint32_t)(key >> 32);
+            if (k == HK_NONE) continue;
+            const uint32_t d = k - hkmin;
+            unsigned m = sm.lut()[d >> sh1] & heavy_any;
+            const uint32_t sub = (d >> sh2) & submask;
+            while (m) {
+                const int t = __ffs(m) - 1;
+                m &= m - 1;
+                if (ps->tsub[t] == sub) {
+                    red_shared_min_u64(&ps->hmin[t], key);
+                    red_shared_max_u64(&ps->hmax[t], key);
+                }
+            }
+        }
+        plan_sync();
+    }
+    FT_MARK(13);   // heavy levels
+    // ---- thread 0: intervals (quantiles ascend, so do their interval ends), heavy list, capacity check
+    if (ptid == 0) {
+        int ni = 0;
+        uint32_t cA = 0, cB = 0;
+        unsigned ca = 0, cb = 0, pts = 0;
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            if (j < nq) {
+                const int ta = 2 * j, tb = 2 * j + 1;
+                uint32_t A = 0u, B = HK_PINF;
+                unsigned ra = 0u, rb = ns;
+                if (ps->tbin[ta] >= 0) {
+                    A = hkmin + ((uint32_t)ps->tbin[ta] << sh1) + (ps->tsub[ta] << sh2);
+                    ra = ps->tcum[ta];
+                }
+                if (ps->tbin[tb] >= 0) {
+                    const unsigned long long bb = (unsigned long long)hkmin + ((unsigned long long)ps->tbin[tb] << sh1) +
+                                                  ((unsigned long long)ps->tsub[tb] << sh2) + ((1ull << sh2) - 1ull);
+                    B = bb > (unsigned long long)HK_PINF ? HK_PINF : (uint32_t)bb;
+                    rb = ps->tcum[tb] + ps->tcnt[tb];
+                }
+                if (B < A) B = A;   // cannot happen (ranks ascend); keep the interval well formed
+                if (ni > 0 && (A <= cB || A - cB == 1u)) {   // overlaps or touches the current interval: widen it
+                    if (A < cA) {
+                        cA = A;
+                        ca = ra;
+                    }
+                    if (B > cB) {
+                        cB = B;
+                        cb = rb;
+                    }
+                } else {
+                    if (ni > 0) {
+                        sl->A[ni - 1] = cA;
+                        sl->W[ni - 1] = cB - cA;
+                        pts += cb - ca;
+                    }
+                    ++ni;
+                    cA = A;
+                    cB = B;
+                    ca = ra;
+                    cb = rb;
+                }
+                sl->qiv[j] = ni - 1;
+            }
+        }
+        if (ni > 0) {
+            sl->A[ni - 1] = cA;
+            sl->W[ni - 1] = cB - cA;
+            pts += cb - ca;
+        }
+        for (int i = ni; i < NI_MAX; ++i) {
+            sl->A[i] = HK_UNUSED;
+            sl->W[i] = 0u;
+        }
+        int nh = 0;
+        unsigned heavy_pts = 0;
+        for (int t = 0; t < F_NT; ++t) {
+            if (!((heavy_any >> t) & 1u) || ps->hmin[t] != ps->hmax[t]) continue;
+            bool dup = false;
+            for (int h = 0; h < nh; ++h) dup = dup || (sl->heavy[h] == ps->hmin[t]);
+            if (dup || nh >= F_NH) continue;
+            sl->heavy[nh++] = ps->hmin[t];
+            heavy_pts += ps->tcnt[t];
+        }
+        pts = pts > heavy_pts ? pts - heavy_pts : 0u;
+        const PoolWin pw = pool_window(single, kser, a.spill_cap);
+        // the candidates are spread over F_NC collector windows (stage groups go round); leave room for skew
+        const double expect = (double)pts * (double)L / (double)S * 1.4 + 256.0;
+        sl->ni = ni;
+        sl->nheavy = nh;
+        sl->mn_seed = ko_key2d(kmin64);
+        sl->mx_seed = ko_key2d(kmax64);
+        if (expect > (double)((pw.s_sub + pw.g_sub) * F_NC)) {
+            sl->defer = 1;
+            sl->ni = 0;
+            sl->nheavy = 0;
+        }
+    }
+    FT_MARK(14);   // thread 0
+    plan_sync();
+}
+
+// ------------------------------------------------------------------------------------------------ stream
+struct StreamAcc {
+    double s0, s1, s2, s3, mn, mx;
+    uint32_t rlo, rhi;       // fast path while every high key lies strictly between them
+    unsigned nan;
+    unsigned c[NI_MAX];      // MINUS the number of samples below A[i] (see stream_step)
+};
+
+__device__ __forceinline__ void acc_bounds(StreamAcc& acc) {
+    const uint32_t kx = (uint32_t)(ko_okey(acc.mx) >> 32), kn = (uint32_t)(ko_okey(acc.mn) >> 32);
+    acc.rhi = kx < HK_PINF ? kx : HK_PINF;
+    acc.rlo = kn > HK_NINF ? kn : HK_NINF;
+}
+
+// Two warp steps at once: 8 samples per lane (two independent groups of four keep the pipes busy).
+// NI intervals.  addr: the lane's 16 bytes of the first step.  Slots of a stage that lie outside the series have been
+// overwritten with NaN before (patch_stage_edges), so every slot is either a sample or NaN here.
+template <int NI>
+__device__ __forceinline__ void stream_step2(uint32_t addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
+                                             const uint32_t (&W)[NI_MAX], uint32_t bm_addr, int lane) {
+    double x[8];
+    lds_v2f64(addr, x[0], x[1]);
+    lds_v2f64(addr + 512u, x[2], x[3]);
+    lds_v2f64(addr + 1024u, x[4], x[5]);
+    lds_v2f64(addr + 1536u, x[6], x[7]);
+    uint32_t k[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) k[e] = hi_key((uint32_t)__double2hiint(x[e]));
+    const uint32_t kmx = max(max(max(k[0], k[1]), max(k[2], k[3])), max(max(k[4], k[5]), max(k[6], k[7])));
+    const uint32_t kmn = min(min(min(k[0], k[1]), min(k[2], k[3])), min(min(k[4], k[5]), min(k[6], k[7])));
+    const bool rare = (kmx >= acc.rhi) || (kmn <= acc.rlo);
+    if (__any_sync(0xffffffffu, rare)) {
+        // Somewhere in the warp: a NaN (stale sample), an infinity, or a candidate for a new extreme.  The running
+        // extremes are the WARP's (kept equal in all lanes), so new extremes die out like 1 / samples seen.
+        bool changed = false;
+        if (rare) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                const uint32_t h = (uint32_t)__double2hiint(x[e]), l = (uint32_t)__double2loint(x[e]);
+                if (bits_nan(h, l)) {
+                    acc.nan += 1u;
+                    x[e] = 0.0;
+                    k[e] = HK_NONE;
+                } else {
+                    if (x[e] < acc.mn) {
+                        acc.mn = x[e];
+                        changed = true;
+                    }
+                    if (x[e] > acc.mx) {
+                        acc.mx = x[e];
+                        changed = true;
+                    }
+                }
+            }
+        }
+        if (__any_sync(0xffffffffu, changed)) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                acc.mn = fmin(acc.mn, __shfl_xor_sync(0xffffffffu, acc.mn, o));
+                acc.mx = fmax(acc.mx, __shfl_xor_sync(0xffffffffu, acc.mx, o));
+            }
+            acc_bounds(acc);
+        }
+    }
+    acc.s0 += x[0];
+    acc.s1 += x[1];
+    acc.s2 += x[2];
+    acc.s3 += x[3];
+    acc.s0 += x[4];
+    acc.s1 += x[5];
+    acc.s2 += x[6];
+    acc.s3 += x[7];
+    if (NI > 0) {
+        uint32_t b[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            bool q = false;
+#pragma unroll
+            for (int i = 0; i < NI; ++i) {
+                uint32_t d;
+                // d = k - A, and c -= (k < A): sub.cc / subc is the borrow chain of a two-word subtraction,
+                // so c goes down by the borrow whatever polarity the carry flag has in hardware
+                asm("sub.cc.u32 %0, %2, %3;\n\tsubc.u32 %1, %1, 0;" : "=r"(d), "+r"(acc.c[i]) : "r"(k[e]), "r"(A[i]));
+                q = q || (d <= W[i]);
+            }
+            b[e] = __ballot_sync(0xffffffffu, q);
+        }
+        if (lane == 0) {
+            sts_v4u32(bm_addr, b[0], b[1], b[2], b[3]);
+            sts_v4u32(bm_addr + 16u, b[4], b[5], b[6], b[7]);
+        }
+    }
+}
+
+template <int NI>
+__device__ __forceinline__ void stream_stage(uint32_t stage_addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
+                                             const uint32_t (&W)[NI_MAX], uint32_t bm_addr, int lane) {
+#pragma unroll 1
+    for (int t = 0; t < 2; ++t)
+        stream_step2<NI>(stage_addr + (uint32_t)t * 2048u + (uint32_t)lane * 16u, acc, A, W, bm_addr + t * 32u, lane);
+}
+
+// First / last stage of a series: the slots in front of the series (16-byte alignment) and behind its end hold
+// bytes that are not the series'.  They are overwritten with NaN, which the scan skips; the finish warps know how
+// many such slots a series has and take them out of the stale-sample count again.
+__device__ __forceinline__ void patch_stage_edges(uint32_t stage_addr, int lane, int first_valid, int end_valid) {
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    for (int i = lane; i < first_valid; i += 32) sts_f64(stage_addr + (uint32_t)i * 8u, nan);
+    for (int i = end_valid + lane; i < F_STAGE; i += 32) sts_f64(stage_addr + (uint32_t)i * 8u, nan);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the next writer of these bytes is a TMA copy
+    __syncwarp();
+}
+
+// Stage g = g0 + j of a series belongs to stream warp g % F_NS and to ring group (g / F_GS) % F_NGROUPS.  A series
+// starts on a group boundary; the stage numbers that pad its last group are visited too (wait, release, no work),
+// so that every group gets its F_GS releases.  cg0: bitmap-ring group number of the series' first group (groups of
+// series without capture intervals do not use the bitmap ring and are not counted).
+template <int NI>
+__device__ __forceinline__ void stream_series(const FlowSmem& sm, const FlowSlot* sl, StreamAcc& acc, int ws, int lane,
+                                              uint32_t cg0) {
+    uint32_t A[NI_MAX], W[NI_MAX];
+#pragma unroll
+    for (int i = 0; i < NI_MAX; ++i) {
+        A[i] = sl->A[i];
+        W[i] = sl->W[i];
+    }
+    const int L = sl->L, lead = sl->lead, n = sl->nstages;
+    const int npad = (n + F_GS - 1) / F_GS * F_GS;
+    const uint32_t g0 = sl->g0;
+    const uint32_t bm0 = smem_u32(sm.bitmap());
+    const uint32_t ring0 = smem_u32(sm.ring());
+    const uint32_t full0 = smem_u32(sm.bar(FB_FULL)), empty0 = smem_u32(sm.bar(FB_EMPTY));
+    const uint32_t bmfull0 = smem_u32(sm.bar(FB_BMFULL)), bmempty0 = smem_u32(sm.bar(FB_BMEMPTY));
+    FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
+    int j = (int)(((uint32_t)ws + F_NS - (g0 % F_NS)) % F_NS);
+    for (; j < npad; j += F_NS) {
+        const uint32_t g = g0 + (uint32_t)j;
+        const uint32_t grp = g / F_GS;
+        const uint32_t s = grp % F_NGROUPS, par = (grp / F_NGROUPS) & 1u;
+        const uint32_t stage_addr = ring0 + s * (uint32_t)F_GROUP_BYTES + (g % F_GS) * (uint32_t)F_STAGE_BYTES;
+        const uint32_t cgi = cg0 + (uint32_t)(j / F_GS);
+        const uint32_t bs = cgi % F_BG, buse = cgi / F_BG;
+        const uint32_t bm_addr = bm0 + bs * (uint32_t)(F_GS * 64) + (g % F_GS) * 64u;
+        if (NI > 0 && buse > 0u) mbar_wait_addr(bmempty0 + bs * 8u, (buse - 1u) & 1u);   // the collector has read it
+        FT_MARK(34);   // stream warp 0: waiting for the bitmap slot
+        mbar_wait_addr(full0 + s * 8u, par);
+        FT_MARK(32);   // stream warp 0: waiting for a full stage
+        if (j < n) {
+            if (j == 0 || j == n - 1) {
+                const int end_valid = L + lead - j * F_STAGE;
+                patch_stage_edges(stage_addr, lane, j == 0 ? lead : 0, end_valid < F_STAGE ? end_valid : F_STAGE);
+            }
+            stream_stage<NI>(stage_addr, acc, A, W, bm_addr, lane);
+        } else if (NI > 0) {
+            if (lane < 16) sts_u32f(bm_addr + (uint32_t)lane * 4u, 0u);
+        }
+        FT_MARK(33);   // stream warp 0: scan
+        __syncwarp();
+        if (lane == 0) {
+            mbar_arrive_addr(empty0 + s * 8u);
+            if (NI > 0) mbar_arrive_addr(bmfull0 + bs * 8u);
+        }
+    }
+}
+
+__device__ __forceinline__ double shfl_xor_f64(double v, int o) { return __shfl_xor_sync(0xffffffffu, v, o); }
+
+// ------------------------------------------------------------------------------------------------ collector
+// The flagged samples of one lane's two bitmap words (64 samples of one stage: words wi and wi + 1).
+// Bit b of word w flags the sample at stage offset (w >> 2) * 128 + ((w & 2) ? 64 : 0) + 2 * b + (w & 1).
+struct LaneBits {
+    uint32_t w0, w1;
+    __device__ __forceinline__ bool any() const { return (w0 | w1) != 0u; }
+    // offset (in samples, from the stage's first slot) of the next flagged sample; removes it
+    __device__ __forceinline__ int pop(int wi) {
+        int w, b;
+        if (w0) {
+            b = __ffs(w0) - 1;
+            w0 &= w0 - 1;
+            w = wi;
+        } else {
+            b = __ffs(w1) - 1;
+            w1 &= w1 - 1;
+            w = wi + 1;
+        }
+        return (w >> 2) * 128 + ((w & 2) ? 64 : 0) + 2 * b + (w & 1);
+    }
+};
+
+// ------------------------------------------------------------------------------------------------ finish
+// All finish threads (ftid in [0, 128)).  Returns nothing; outputs are written here.
+__device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSmem& sm, const FlowSlot* sl, int d, int ftid,
+                              const PoolWin& pw, const unsigned long long* spill) {
+    FinState* fs = sm.fs();
+    const int lane = ftid & 31, fw = ftid >> 5;
+    const int nq = a.nq, ni = sl->ni;
+    const int L = sl->L, sid = sl->sid;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    // ---- A. partial statistics (warp 0, fixed order) and the last valid sample (warp 1)
+    if (fw == 0) {
+        const FlowPartial* p = sm.part(d, lane < F_NS ? lane : 0);
+        double s = lane < F_NS ? p->sum : 0.0;
+        double mn = p->mn, mx = p->mx;
+        unsigned nn = lane < F_NS ? p->nan : 0u;
+        unsigned c[NI_MAX];
+#pragma unroll
+        for (int i = 0; i < NI_MAX; ++i) c[i] = lane < F_NS ? p->c[i] : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            s += shfl_xor_f64(s, o);
+            mn = fmin(mn, shfl_xor_f64(mn, o));
+            mx = fmax(mx, shfl_xor_f64(mx, o));
+        }
+        nn = __reduce_add_sync(0xffffffffu, nn);
+#pragma unroll
+        for (int i = 0; i < NI_MAX; ++i) c[i] = __reduce_add_sync(0xffffffffu, c[i]);
+        if (lane == 0) {
+            fs->sum = s;
+            fs->mn = mn;
+            fs->mx = mx;
+            // nn counts the NaN slots of all stages: stale samples plus the slots outside the series
+            fs->nvalid = (unsigned)L - (nn - ((unsigned)sl->nstages * F_STAGE - (unsigned)L));
+#pragma unroll
+            for (int i = 0; i < NI_MAX; ++i) fs->cb[i] = c[i];
+            fs->fail = sl->defer;
+            fs->why = 0;
+            fs->pending = 0;
+        }
+    } else if (ftid == 32) {
+        const double* v = a.values + sl->start;
+        double lastv = nan;
+        for (int i = L - 1; i >= 0; --i) {
+            const double x = v[i];
+            if (x == x) {
+                lastv = x;
+                break;
+            }
+        }
+        fs->last = lastv;
+    }
+    fin_sync();
+    const unsigned nvalid = fs->nvalid;
+    unsigned npool_raw = 0;
+#pragma unroll
+    for (int c = 0; c < F_NC; ++c)
+        npool_raw += ni > 0 ? sm.csm()[pw.buf * F_NC + c] + sm.cgl()[pw.buf * F_NC + c] : 0u;
+    const bool overflow = ni > 0 && sm.ovf()[pw.buf] != 0u;
+    const unsigned npool = overflow ? 0u : npool_raw;
+    const int nheavy = sl->nheavy;
+    // ---- B. per-quantile start state
+    if (ftid < NI_MAX) {
+        const int j = ftid;
+        int st = Q_DONE;
+        unsigned long long ans = ~0ull;   // "NaN"
+        if (j < nq && nvalid > 0 && !fs->fail) {
+            if (sl->konst) {
+                if (ko_okey(fs->mn + 0.0) == ko_okey(fs->mx + 0.0)) ans = ko_okey(fs->mn + 0.0);
+                else {
+                    st = Q_FAIL;
+                    fs->why = 4;
+                }
+            } else if (ni == 0 || overflow) {
+                st = Q_FAIL;
+                fs->why = overflow ? 3 : 5;
+            } else {
+                const int iv = sl->qiv[j];
+                const unsigned r = nearest_rank_dev(nvalid, a.q[j]);
+                const unsigned cb = fs->cb[iv];
+                if (r <= cb) {
+                    st = Q_FAIL;   // the rank lies below its interval
+                    fs->why = 1;
+                } else {
+                    const unsigned long long range = ((unsigned long long)sl->W[iv] << 32) | 0xFFFFFFFFull;
+                    fs->lo[j] = (unsigned long long)sl->A[iv] << 32;
+                    fs->sh[j] = max(0, 64 - __clzll((long long)range) - 8);
+                    fs->rho[j] = r - cb;
+                    st = Q_HIST;
+                }
+            }
+        } else if (j < nq && fs->fail) {
+            st = Q_FAIL;
+        }
+        fs->st[j] = st;
+        fs->ans[j] = ans;
+        fs->list_n[j] = 0;
+        if (st == Q_HIST) atomicAdd(&fs->pending, 1);
+        if (st == Q_FAIL) fs->fail = 1;
+    }
+    fin_sync();
+    // ---- C. rounds: histogram refinement, then direct selection among <= F_LIST candidates
+    int guard = 0;
+    while (fs->pending > 0 && !fs->fail && guard++ < 24) {
+        for (int i = ftid; i < NI_MAX * 256; i += F_NF * 32) sm.fbins()[i] = 0;
+        fin_sync();
+        int stj[NI_MAX], shj[NI_MAX];
+        unsigned long long loj[NI_MAX];
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            stj[j] = j < nq ? fs->st[j] : Q_DONE;
+            shj[j] = fs->sh[j];
+            loj[j] = fs->lo[j];
+        }
+        auto visit = [&](unsigned long long key, unsigned mult) {
+#pragma unroll
+            for (int j = 0; j < NI_MAX; ++j) {
+                if (stj[j] > Q_COLLECT || key < loj[j]) continue;
+                const unsigned long long dd = (key - loj[j]) >> shj[j];
+                if (stj[j] == Q_HIST) {
+                    if (dd < 256ull) red_shared_add(&sm.fbins()[j * 256 + (unsigned)dd], mult);
+                } else if (dd == 0ull) {
+                    const unsigned pos = atom_shared_add(&fs->list_n[j], 1u);
+                    if (pos < (unsigned)F_LIST) {
+                        sm.flistk()[j * F_LIST + pos] = key;
+                        sm.flistm()[j * F_LIST + pos] = mult;
+                    }
+                }
+            }
+        };
+#pragma unroll 1
+        for (int c = 0; c < F_NC; ++c) {
+            const unsigned nsm = npool > 0u ? sm.csm()[pw.buf * F_NC + c] : 0u;
+            const unsigned ng = npool > 0u ? sm.cgl()[pw.buf * F_NC + c] : 0u;
+            const unsigned long long* wbase = sm.pool() + pw.s_base + (uint32_t)c * pw.s_sub;
+#pragma unroll 1
+            for (unsigned i = ftid; i < nsm; i += F_NF * 32) visit(wbase[i], 1u);
+            if (ng > 0u) {   // spilled part: global loads, four in flight
+                const unsigned long long* gbase = spill + pw.g_base + (uint32_t)c * pw.g_sub;
+#pragma unroll 1
+                for (unsigned i = ftid; i < ng; i += 4u * (F_NF * 32)) {
+                    unsigned long long kk[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        kk[u] = i + u * (F_NF * 32) < ng ? ld_cg_u64(gbase + i + u * (F_NF * 32)) : ~0ull;
+#pragma unroll 1
+                    for (int u = 0; u < 4; ++u)
+                        if (i + u * (F_NF * 32) < ng) visit(u == 0 ? kk[0] : u == 1 ? kk[1] : u == 2 ? kk[2] : kk[3], 1u);
+                }
+            }
+        }
+        if (ftid < nheavy) {
+            const unsigned mult = sm.hcnt()[pw.buf * F_NH + ftid];
+            if (mult) visit(sl->heavy[ftid], mult);
+        }
+        fin_sync();
+        // warp j settles quantile j
+        if (fw < nq && fs->st[fw] <= Q_COLLECT) {
+            const int j = fw;
+            if (fs->st[j] == Q_HIST) {
+                int bin;
+                unsigned before, cnt, total;
+                const bool ok = warp_find_bin(sm.fbins() + j * 256, fs->rho[j], lane, bin, before, cnt, total);
+                if (!ok) {   // the rank lies above its interval
+                    if (lane == 0) {
+                        fs->st[j] = Q_FAIL;
+                        fs->fail = 1;
+                        fs->why = 2;
+                        atomicSub(&fs->pending, 1);
+                    }
+                } else {
+                    const int sh = fs->sh[j];
+                    const unsigned long long nlo = fs->lo[j] + ((unsigned long long)bin << sh);
+                    // one listed tie level filling the whole bin settles it
+                    bool hv = false;
+                    if (lane < nheavy) {
+                        const unsigned long long hk = sl->heavy[lane];
+                        hv = hk >= nlo && ((hk - nlo) >> sh) == 0ull && sm.hcnt()[pw.buf * F_NH + lane] == cnt;
+                    }
+                    const unsigned hb = __ballot_sync(0xffffffffu, hv);
+                    if (lane == 0) {
+                        fs->lo[j] = nlo;
+                        fs->rho[j] -= before;
+                        if (sh == 0) {
+                            fs->ans[j] = nlo;
+                            fs->st[j] = Q_DONE;
+                            atomicSub(&fs->pending, 1);
+                        } else if (hb) {
+                            fs->ans[j] = sl->heavy[__ffs(hb) - 1];
+                            fs->st[j] = Q_DONE;
+                            atomicSub(&fs->pending, 1);
+                        } else if (cnt <= (unsigned)F_LIST) {
+                            fs->st[j] = Q_COLLECT;     // keys with (key - lo) >> sh == 0
+                            fs->list_n[j] = 0;
+                        } else {
+                            fs->sh[j] = sh >= 8 ? sh - 8 : 0;
+                        }
+                    }
+                }
+            } else {   // Q_COLLECT: rank counting among the listed (key, multiplicity) pairs
+                const unsigned n = min(fs->list_n[j], (unsigned)F_LIST);
+                const unsigned rho = fs->rho[j];
+                const unsigned long long* lk = sm.flistk() + j * F_LIST;
+                const unsigned* lm = sm.flistm() + j * F_LIST;
+                unsigned long long found = 0ull;
+                bool got = false;
+                for (unsigned c0 = 0; c0 < n; c0 += 32) {
+                    const unsigned c = c0 + lane;
+                    unsigned less = 0, eq = 0;
+                    const unsigned long long kc = c < n ? lk[c] : 0ull;
+                    for (unsigned e = 0; e < n; ++e) {
+                        const unsigned long long ke = lk[e];
+                        const unsigned me = lm[e];
+                        less += ke < kc ? me : 0u;
+                        eq += ke == kc ? me : 0u;
+                    }
+                    const bool hit = c < n && less < rho && rho <= less + eq;
+                    const unsigned hb = __ballot_sync(0xffffffffu, hit);
+                    if (hb && !got) {
+                        found = __shfl_sync(0xffffffffu, kc, __ffs(hb) - 1);
+                        got = true;
+                    }
+                }
+                if (lane == 0) {
+                    if (got) {
+                        fs->ans[j] = found;
+                        fs->st[j] = Q_DONE;
+                    } else {   // cannot happen: the bin count said the rank is among these
+                        fs->st[j] = Q_FAIL;
+                        fs->fail = 1;
+                        fs->why = 6;
+                    }
+                    atomicSub(&fs->pending, 1);
+                }
+            }
+        }
+        fin_sync();
+    }
+    // ---- D. outputs
+    if (ftid == 0) {
+        const bool fail = fs->fail != 0 || fs->pending > 0;
+        if (a.out_sum) a.out_sum[sid] = fs->sum;
+        if (a.out_mean) a.out_mean[sid] = nvalid > 0 ? fs->sum / (double)nvalid : 0.0;
+        if (a.out_min) a.out_min[sid] = nvalid > 0 ? fs->mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = nvalid > 0 ? fs->mx + 0.0 : nan;
+        if (a.out_last) a.out_last[sid] = fs->last;
+        if (a.out_count) a.out_count[sid] = (int64_t)nvalid;
+        if (fail) {
+            const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
+            a.out_list[pos] = sid;
+            atomicAdd(&a.counters[9 + (fs->why & 7)], 1);
+        } else if (a.out_quant) {
+            for (int j = 0; j < nq; ++j)
+                a.out_quant[(int64_t)sid * nq + a.qcol[j]] = fs->ans[j] == ~0ull ? nan : ko_key2d(fs->ans[j]);
+        }
+    }
+    if (ftid < F_NH) sm.hcnt()[pw.buf * F_NH + ftid] = 0u;
+    if (ftid >= 32 && ftid < 32 + F_NC) {
+        sm.csm()[pw.buf * F_NC + (ftid - 32)] = 0u;
+        sm.cgl()[pw.buf * F_NC + (ftid - 32)] = 0u;
+    }
+    if (ftid == 64) sm.ovf()[pw.buf] = 0u;
+    fin_sync();
+}
+
+// ------------------------------------------------------------------------------------------------ kernel
+__global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
+    extern __shared__ __align__(128) unsigned char flow_smem[];
+    FlowSmem sm;
+    sm.base = flow_smem;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < F_NGROUPS; ++s) {
+            mbar_init(sm.bar(FB_FULL + s), 1);
+            mbar_init(sm.bar(FB_EMPTY + s), F_GS + 1);   // the four scanning warps and the group's collector
+        }
+        for (int s = 0; s < F_BG; ++s) {
+            mbar_init(sm.bar(FB_BMFULL + s), F_GS);
+            mbar_init(sm.bar(FB_BMEMPTY + s), 1);
+        }
+        for (int d = 0; d < F_ND; ++d) {
+            mbar_init(sm.bar(FB_DESC + d), 1);
+            mbar_init(sm.bar(FB_PLAN + d), 1);
+            mbar_init(sm.bar(FB_FREE + d), 1);
+            mbar_init(sm.bar(FB_SDONE + d), F_NS);
+            mbar_init(sm.bar(FB_CDONE + d), F_NC);
+            mbar_init(sm.bar(FB_START + d), 1);
+        }
+        mbar_init(sm.bar(FB_POOL + 0), 1);
+        mbar_init(sm.bar(FB_POOL + 1), 1);
+        mbar_fence_init();
+    }
+    if (tid < F_PSTATE_WORDS) sm.csm()[tid] = 0u;
+    __syncthreads();
+    const int n_work = a.counters[a.work_cnt];
+    const bool single = a.wide != 0 || a.counters[8] > F_DOUBLE_MAXL;
+    unsigned long long* spill = a.spill + (size_t)blockIdx.x * (size_t)a.spill_cap;
+
+    if (warp == F_W_PROD) {
+        // =============================== PRODUCER ===============================
+        if (lane == 0) {
+            const uint64_t policy = createpolicy_evict_first();
+            const uint32_t ring0 = smem_u32(sm.ring());
+            FT_BEGIN(blockIdx.x == 0);
+            for (uint32_t k = 0;; ++k) {
+                const int d = (int)(k % F_ND);
+                mbar_wait_hint(sm.bar(FB_DESC + d), (k / F_ND) & 1u);
+                FT_MARK(0);   // producer: waiting for a descriptor
+                const FlowSlot* sl = sm.slot(d);
+                if (sl->sid < 0) break;
+                const int n = sl->nstages;
+                const int ngroups = (n + F_GS - 1) / F_GS;
+                const uint32_t grp0 = sl->g0 / F_GS;
+                const uint32_t total = sl->total_bytes;
+                const unsigned char* src = reinterpret_cast<const unsigned char*>(sl->src);
+                for (int gi = 1; gi < F_PF && gi < ngroups; ++gi) {
+                    const uint32_t off = (uint32_t)gi * F_GROUP_BYTES;
+                    const uint32_t pb = total > off ? min(total - off, (uint32_t)F_GROUP_BYTES) : 0u;
+                    if (pb) bulk_prefetch_l2(src + off, pb);
+                }
+                for (int gi = 0; gi < ngroups; ++gi) {
+                    const uint32_t grp = grp0 + (uint32_t)gi;
+                    const uint32_t s = grp % F_NGROUPS, u = grp / F_NGROUPS;
+                    FT_MARK(2);   // producer: issuing
+                    if (u > 0) mbar_wait(sm.bar(FB_EMPTY + s), (u - 1u) & 1u);
+                    FT_MARK(1);   // producer: waiting for a free group
+                    const uint32_t off = (uint32_t)gi * F_GROUP_BYTES;
+                    const uint32_t bytes = total > off ? min(total - off, (uint32_t)F_GROUP_BYTES) : 0u;
+                    const uint32_t dst = ring0 + s * (uint32_t)F_GROUP_BYTES;
+                    if (gi + F_PF < ngroups) {
+                        const uint32_t poff = (uint32_t)(gi + F_PF) * F_GROUP_BYTES;
+                        const uint32_t pb = total > poff ? min(total - poff, (uint32_t)F_GROUP_BYTES) : 0u;
+                        if (pb) bulk_prefetch_l2(src + poff, pb);
+                    }
+                    if (gi == ngroups - 1 && sl->tail_fix) {   // the array's very last element, read on its own
+                        const int e = sl->L + sl->lead - 1 - gi * (F_GS * F_STAGE);
+                        const double x = a.values[sl->start + sl->L - 1];
+                        sts_f64(dst + (uint32_t)e * 8u, x);
+                    }
+                    if (bytes) {
+                        mbar_expect_tx(sm.bar(FB_FULL + s), bytes);
+                        tma_bulk_g2s_hint(dst, src + off, bytes, smem_u32(sm.bar(FB_FULL + s)), policy);
+                    } else {
+                        mbar_arrive(sm.bar(FB_FULL + s));
+                    }
+                }
+            }
+        }
+    } else if (warp >= F_W_PLAN) {
+        // =============================== PLANNER ===============================
+        const int ptid = tid - F_W_PLAN * 32;
+        PlanScratch* ps = sm.ps();
+        uint32_t g = 0;
+        const long long arr_end = a.offsets[a.n_series];
+        int prev_depth1 = 0;
+        FT_BEGIN(blockIdx.x == 0 && ptid == 0);
+        for (uint32_t k = 0;; ++k) {
+            const int d = (int)(k % F_ND);
+            FT_MARK(6);   // planner: planning
+            // slot reuse: the finish of series k - F_ND; long series: stay one series ahead of the stream warps only
+            if (k >= (uint32_t)F_ND) mbar_wait_hint(sm.bar(FB_FREE + d), ((k / F_ND) - 1u) & 1u);
+            if (prev_depth1 && k >= 1u) {   // the stream warps have begun series k - 1
+                const uint32_t kk = k - 1u;
+                mbar_wait_hint(sm.bar(FB_START + (int)(kk % F_ND)), (kk / F_ND) & 1u);
+            }
+            FT_MARK(5);   // planner: waiting for the finish warps (slot / depth)
+            FlowSlot* sl = sm.slot(d);
+            if (ptid == 0) {
+                const int w = atomicAdd(&a.counters[a.work_cur], 1);
+                if (w >= n_work) {
+                    sl->sid = -1;
+                } else {
+                    const int sid = a.work_list[w];
+                    const long long off0 = a.offsets[sid];
+                    const int L = (int)(a.offsets[sid + 1] - off0);
+                    const double* v = a.values + off0;
+                    const int lead = (int)((reinterpret_cast<uintptr_t>(v) >> 3) & 1u);
+                    const int tot = L + lead;
+                    const int n = (tot + F_STAGE - 1) / F_STAGE;
+                    const int rem = tot - (n - 1) * F_STAGE;
+                    const bool at_end = (off0 + L == arr_end);
+                    sl->sid = sid;
+                    sl->L = L;
+                    sl->lead = lead;
+                    sl->nstages = n;
+                    sl->g0 = g;
+                    sl->tail_fix = ((rem & 1) && at_end) ? 1 : 0;
+                    sl->total_bytes = (uint32_t)(n - 1) * F_STAGE_BYTES +
+                                      (uint32_t)(sl->tail_fix ? (rem - 1) : ((rem + 1) & ~1)) * 8u;
+                    sl->depth1 = L > 16384 ? 1 : 0;
+                    sl->src = v - lead;
+                    sl->start = off0;
+                }
+                ps->work = sl->sid;
+                mbar_arrive(sm.bar(FB_DESC + d));
+            }
+            plan_sync();
+            if (ps->work < 0) {
+                if (ptid == 0) mbar_arrive(sm.bar(FB_PLAN + d));
+                break;
+            }
+            g += (uint32_t)((sl->nstages + F_GS - 1) / F_GS * F_GS);   // every series starts a ring group
+            prev_depth1 = sl->depth1;
+            planner_plan(a, sm, sl, ptid, single, k);
+            if (ptid == 0) mbar_arrive(sm.bar(FB_PLAN + d));
+        }
+    } else if (warp >= F_W_COLL) {
+        // =============================== COLLECTOR ===============================
+        // Ring group grp belongs to collector grp % F_NC.  With capture intervals: wait until the group's four
+        // stages are scanned (bitmaps full), copy the flagged samples from the ring to the pool window, release the
+        // bitmaps and the ring group.  Without: just hand the ring group back.
+        const int cw = warp - F_W_COLL;
+        uint32_t cg = 0;   // bitmap-ring group counter (groups of series with capture intervals)
+        const uint32_t bm0 = smem_u32(sm.bitmap());
+        const uint32_t ring0 = smem_u32(sm.ring());
+        FT_BEGIN(blockIdx.x == 0 && cw == 0 && lane == 0);
+        for (uint32_t k = 0;; ++k) {
+            const int d = (int)(k % F_ND);
+            const uint32_t par = (k / F_ND) & 1u;
+            FT_MARK(41);   // collector 0: working
+            mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            FT_MARK(40);   // collector 0: waiting for the plan
+            const FlowSlot* sl = sm.slot(d);
+            if (sl->sid < 0) break;
+            const PoolWin pw = pool_window(single, k, a.spill_cap);
+            const int ngroups = (sl->nstages + F_GS - 1) / F_GS;
+            const uint32_t grp0 = sl->g0 / F_GS;
+            const int ni = sl->ni, nheavy = sl->nheavy;
+            unsigned long long hkey[F_NH];   // the listed tie levels, in registers (~0 never equals a key)
+#pragma unroll
+            for (int h = 0; h < F_NH; ++h) hkey[h] = h < nheavy ? sl->heavy[h] : ~0ull;
+            // the shared-memory window was last used by series k - 1 (one pool) or k - 2 (two halves); until the
+            // finish warps have released it this series' candidates go to the spill window
+            bool pool_ok = pw.use == 0u;
+            unsigned cs = 0, cgs = 0;   // entries of this collector in its shared-memory / spill window
+            bool over = false;
+            int gi = (int)(((uint32_t)cw + F_NC - (grp0 % F_NC)) % F_NC);
+            for (; gi < ngroups; gi += F_NC) {
+                const uint32_t grp = grp0 + (uint32_t)gi;
+                const uint32_t s = grp % F_NGROUPS, u = grp / F_NGROUPS;
+                if (ni == 0) {
+                    mbar_wait_hint(sm.bar(FB_FULL + s), u & 1u);   // the group's phase has begun
+                    if (lane == 0) mbar_arrive(sm.bar(FB_EMPTY + s));
+                    continue;
+                }
+                const uint32_t cgi = cg + (uint32_t)gi;
+                const uint32_t bs = cgi % F_BG, buse = cgi / F_BG;
+                mbar_wait_hint(sm.bar(FB_BMFULL + bs), buse & 1u);
+                mbar_wait_hint(sm.bar(FB_FULL + s), u & 1u);       // (complete long ago: the TMA bytes are visible)
+                FT_MARK(42);   // collector 0: waiting for bitmaps
+                LaneBits lb;
+                lds_v2u32(bm0 + bs * (uint32_t)(F_GS * 64) + (uint32_t)lane * 8u, lb.w0, lb.w1);
+                // lane: stage lane / 8 of the group, words (lane % 8) * 2 and + 1 of that stage
+                const uint32_t stage_addr = ring0 + s * (uint32_t)F_GROUP_BYTES + (uint32_t)(lane >> 3) * F_STAGE_BYTES;
+                const int wi = (lane & 7) * 2;
+                if (__any_sync(0xffffffffu, lb.any())) {
+                    // (compact loops on purpose: this code must stay in the instruction cache beside the scan loop)
+                    if (nheavy > 0) {   // samples on a listed tie level are counted, not stored
+                        LaneBits rest = lb;
+                        uint32_t k0 = lb.w0, k1 = lb.w1;
+#pragma unroll 1
+                        while (rest.any()) {
+                            const uint32_t p0 = rest.w0, p1 = rest.w1;
+                            const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)rest.pop(wi) * 8u) + 0.0);
+                            int hit = -1;
+#pragma unroll
+                            for (int h = 0; h < F_NH; ++h) hit = hkey[h] == key ? h : hit;
+                            if (hit >= 0) {
+                                red_shared_add(&sm.hcnt()[pw.buf * F_NH + hit], 1u);
+                                k0 &= ~(p0 ^ rest.w0);   // clear the bit just popped
+                                k1 &= ~(p1 ^ rest.w1);
+                            }
+                        }
+                        lb.w0 = k0;
+                        lb.w1 = k1;
+                    }
+                    const unsigned n = __popc(lb.w0) + __popc(lb.w1);
+                    unsigned incl = n;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += t;
+                    }
+                    const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
+                    FT_MARK(43);   // collector 0: counting
+                    if (!pool_ok) pool_ok = mbar_test(sm.bar(FB_POOL + pw.bar), (pw.use - 1u) & 1u);
+                    const unsigned avail = pool_ok ? pw.s_sub - cs : 0u;     // shared-memory entries left
+                    const unsigned take = total < avail ? total : avail;
+                    unsigned e = incl - n;                                       // this lane's first entry of the batch
+                    unsigned long long* wb = sm.pool() + pw.s_base + (uint32_t)cw * pw.s_sub + cs;
+                    unsigned long long* gb = spill + pw.g_base + (uint32_t)cw * pw.g_sub + cgs;
+#pragma unroll 1
+                    while (lb.any()) {
+                        const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lb.pop(wi) * 8u) + 0.0);
+                        if (e < take) wb[e] = key;
+                        else if (cgs + (e - take) < pw.g_sub) gb[e - take] = key;
+                        else over = true;
+                        ++e;
+                    }
+                    cs += take;
+                    cgs += total - take;
+                }
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive(sm.bar(FB_BMEMPTY + bs));
+                    mbar_arrive(sm.bar(FB_EMPTY + s));
+                }
+                FT_MARK(45);   // collector 0: storing candidates
+            }
+            if (ni > 0) cg += (uint32_t)ngroups;
+            over = __any_sync(0xffffffffu, over);
+            if (lane == 0) {
+                sm.csm()[pw.buf * F_NC + cw] = cs;
+                sm.cgl()[pw.buf * F_NC + cw] = cgs < pw.g_sub ? cgs : pw.g_sub;
+                if (over) sm.ovf()[pw.buf] = 1u;
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sm.bar(FB_CDONE + d));
+        }
+    } else if (warp >= F_W_FIN) {
+        // =============================== FINISH ===============================
+        const int ftid = tid - F_W_FIN * 32;
+        FT_BEGIN(blockIdx.x == 0 && ftid == 0);
+        for (uint32_t k = 0;; ++k) {
+            const int d = (int)(k % F_ND);
+            const uint32_t par = (k / F_ND) & 1u;
+            FT_MARK(22);   // finish: working
+            mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            FT_MARK(20);   // finish: waiting for the plan
+            const FlowSlot* sl = sm.slot(d);
+            if (sl->sid < 0) break;
+            mbar_wait_hint(sm.bar(FB_SDONE + d), par);
+            mbar_wait_hint(sm.bar(FB_CDONE + d), par);
+            FT_MARK(21);   // finish: waiting for the stream warps and the collectors
+            const PoolWin pw = pool_window(single, k, a.spill_cap);
+            finish_series(a, sm, sl, d, ftid, pw, spill);
+            if (ftid == 0) {
+                mbar_arrive(sm.bar(FB_POOL + pw.bar));
+                mbar_arrive(sm.bar(FB_FREE + d));
+            }
+        }
+    } else {
+        // =============================== STREAM ===============================
+        const int ws = warp - F_W_STREAM;
+        uint32_t cg = 0;   // bitmap-ring group counter, as in the collectors
+        FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
+        for (uint32_t k = 0;; ++k) {
+            const int d = (int)(k % F_ND);
+            const uint32_t par = (k / F_ND) & 1u;
+            FT_MARK(31);   // stream warp 0: working (scan + epilogue)
+            mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            FT_MARK(30);   // stream warp 0: waiting for the plan
+            const FlowSlot* sl = sm.slot(d);
+            if (sl->sid < 0) break;
+            if (ws == 0 && lane == 0) mbar_arrive(sm.bar(FB_START + d));
+            StreamAcc acc;
+            acc.s0 = 0.0;
+            acc.s1 = 0.0;
+            acc.s2 = 0.0;
+            acc.s3 = 0.0;
+            acc.mn = sl->mn_seed;
+            acc.mx = sl->mx_seed;
+            acc.nan = 0;
+#pragma unroll
+            for (int i = 0; i < NI_MAX; ++i) acc.c[i] = 0;
+            acc_bounds(acc);
+            const int ni = sl->ni;
+            switch (ni) {
+                case 0: stream_series<0>(sm, sl, acc, ws, lane, cg); break;
+                case 1: stream_series<1>(sm, sl, acc, ws, lane, cg); break;
+                case 2: stream_series<2>(sm, sl, acc, ws, lane, cg); break;
+                case 3: stream_series<3>(sm, sl, acc, ws, lane, cg); break;
+                default: stream_series<4>(sm, sl, acc, ws, lane, cg); break;
+            }
+            if (ni > 0) cg += (uint32_t)((sl->nstages + F_GS - 1) / F_GS);
+            // warp totals -> partial of (slot, warp)
+            double s = (acc.s0 + acc.s1) + (acc.s2 + acc.s3), mn = acc.mn, mx = acc.mx;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                s += shfl_xor_f64(s, o);
+                mn = fmin(mn, shfl_xor_f64(mn, o));
+                mx = fmax(mx, shfl_xor_f64(mx, o));
+            }
+            const unsigned nn = __reduce_add_sync(0xffffffffu, acc.nan);
+            unsigned c[NI_MAX];
+#pragma unroll
+            for (int i = 0; i < NI_MAX; ++i) c[i] = __reduce_add_sync(0xffffffffu, 0u - acc.c[i]);
+            __syncwarp();
+            if (lane == 0) {
+                FlowPartial* p = sm.part(d, ws);
+                p->sum = s;
+                p->mn = mn;
+                p->mx = mx;
+                p->nan = nn;
+#pragma unroll
+                for (int i = 0; i < NI_MAX; ++i) p->c[i] = c[i];
+                mbar_arrive(sm.bar(FB_SDONE + d));
+            }
+        }
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ host
+size_t ko_flow_smem_bytes() { return FLOW_SMEM_BYTES; }
+
+cudaError_t ko_flow_set_attributes() {
+    return cudaFuncSetAttribute(series_flow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FLOW_SMEM_BYTES);
+}
+
+#ifdef KO_FLOW_TIMING
+extern "C" int ko_debug_flow_phases(unsigned long long* out64, int reset) {
+    KO_CUDA(cudaMemcpyFromSymbol(out64, g_flow_phase, sizeof(unsigned long long) * 64));
+    if (reset) {
+        unsigned long long z[64] = {0};
+        KO_CUDA(cudaMemcpyToSymbol(g_flow_phase, z, sizeof(z)));
+    }
+    return KO_OK;
+}
+#endif
+
+// Enqueue one series_flow launch over the work list selected in `a` (grid <= one CTA per SM).
+cudaError_t ko_flow_launch(const void* args, int grid, cudaStream_t st) {
+    const SeriesArgs& a = *reinterpret_cast<const SeriesArgs*>(args);
+    series_flow<<<grid, F_THREADS, FLOW_SMEM_BYTES, st>>>(a);
+    return cudaGetLastError();
+}

@@ -39,6 +39,7 @@ ABI = {
     "ko_stable_desc_order": [_c_vp, _c_vp, _c_i64, _c_vp],
     "ko_series_rollup": [_c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_int] + [_c_vp] * 7,
     "ko_series_rollup_dev": [_c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_int] + [_c_vp] * 7 + [_c_vp],
+    "ko_series_status": [_c_vp, _c_vp],
     "ko_series_rollup_static": [_c_int, _c_vp, _c_vp, _c_i64, _c_vp, _c_int] + [_c_vp] * 7 + [_c_vp],
     "ko_available_rate": [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_vp],
     "ko_fleet_rollup": [_c_vp] + [_c_vp] * 6 + [_c_i64, _c_vp],
@@ -157,6 +158,13 @@ class Rollup:
         self._check(self._lib.ko_get_counters(self._ctx, ctypes.byref(c)))
         return dict(kernel_launches=c.kernel_launches, h2d_bytes=c.h2d_bytes, d2h_bytes=c.d2h_bytes,
                     series_fallback=c.series_fallback)
+
+    def series_status(self):
+        """Device-side outcome of the last ``series_rollup_dev`` (waits for it): long series, series repeated with
+        wide intervals, series that took the slow exact path, device error flag."""
+        out = (ctypes.c_int32 * 4)()
+        self._check(self._lib.ko_series_status(self._ctx, out))
+        return dict(long_series=out[0], second_attempt=out[1], slow_path=out[2], error_flag=out[3])
 
     def last_series_kernel_ms(self):
         ms = ctypes.c_float(0)
