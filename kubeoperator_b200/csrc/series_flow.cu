@@ -24,6 +24,8 @@
 // Whatever the plan cannot guarantee (a rank outside its interval, an overflowing pool, a pre-sample with almost no
 // valid points) is detected from exact counts and the series goes to the next attempt's list: a second series_flow
 // launch with 5-sigma intervals, then series_long.  The results are therefore always the oracle's.
+#include <stdio.h>
+
 #include "series_common.cuh"
 
 namespace {
@@ -64,7 +66,7 @@ constexpr uint32_t HK_UNUSED = 0xFFFFFFFEu;    // A of an unused interval (W = 0
 
 enum { FB_FULL = 0, FB_EMPTY = FB_FULL + F_NGROUPS, FB_BMFULL = FB_EMPTY + F_NGROUPS, FB_BMEMPTY = FB_BMFULL + F_BG,
        FB_DESC = FB_BMEMPTY + F_BG, FB_PLAN = FB_DESC + F_ND, FB_FREE = FB_PLAN + F_ND, FB_SDONE = FB_FREE + F_ND,
-       FB_CDONE = FB_SDONE + F_ND, FB_START = FB_CDONE + F_ND, FB_POOL = FB_START + F_ND, FB_COUNT = FB_POOL + 2 };
+       FB_CDONE = FB_SDONE + F_ND, FB_START = FB_CDONE + F_ND, FB_COUNT = FB_START + F_ND };
 
 struct alignas(16) FlowSlot {
     // descriptor (planner thread 0)
@@ -125,6 +127,22 @@ struct FinState {
 };
 enum { Q_HIST = 0, Q_COLLECT = 1, Q_DONE = 2, Q_FAIL = 3 };
 
+// Development aid (-DKO_FLOW_PROGRESS): where every role of every CTA currently is, readable while the kernel hangs.
+#ifdef KO_FLOW_PROGRESS
+__device__ unsigned g_flow_prog[256 * 8];
+__device__ unsigned g_flow_wide;
+__device__ unsigned g_flow_trap[16];
+__device__ __forceinline__ void flow_trap(unsigned who, unsigned k, unsigned grp, unsigned issued, unsigned extra) {
+    if (atomicAdd(&g_flow_trap[0], 1u) == 0u) {
+        g_flow_trap[1] = blockIdx.x; g_flow_trap[2] = who; g_flow_trap[3] = k; g_flow_trap[4] = grp;
+        g_flow_trap[5] = issued; g_flow_trap[6] = extra;
+    }
+}
+#define FP(role, k, phase) (reinterpret_cast<volatile unsigned*>(g_flow_prog)[blockIdx.x * 8 + (role)] = (g_flow_wide << 31) | ((unsigned)(k) << 12) | (unsigned)(phase))
+#else
+#define FP(role, k, phase) do { } while (0)
+#endif
+
 // Development aid (-DKO_FLOW_TIMING): cycles CTA 0 spends in each phase of each role, read by ko_debug_flow_phases.
 #ifdef KO_FLOW_TIMING
 __device__ unsigned long long g_flow_phase[64];
@@ -160,8 +178,8 @@ constexpr size_t FO_SLOTS = FO_BITMAP + (size_t)F_BG * F_GS * 64;
 constexpr size_t FO_PART = FO_SLOTS + align_up(F_ND * sizeof(FlowSlot), 16);
 constexpr size_t FO_PS = FO_PART + (size_t)F_ND * F_NS * sizeof(FlowPartial);
 constexpr size_t FO_FS = FO_PS + align_up(sizeof(PlanScratch), 16);
-constexpr size_t FO_PSTATE = FO_FS + align_up(sizeof(FinState), 16);   // csm[2][F_NC], cgl[2][F_NC], ovf[2], hcnt[2][F_NH]
-constexpr int F_PSTATE_WORDS = 4 * F_NC + 2 + 2 * F_NH;
+constexpr size_t FO_PSTATE = FO_FS + align_up(sizeof(FinState), 16);   // csm[F_ND][F_NC], cgl[F_ND][F_NC], ovf[F_ND], hcnt[F_ND][F_NH], rel[2]
+constexpr int F_PSTATE_WORDS = F_ND * (2 * F_NC + 1 + F_NH) + 2 + 2;   // ..., rel[2], issued, (pad)
 constexpr size_t FO_BARS = FO_PSTATE + align_up(F_PSTATE_WORDS * 4, 16);
 constexpr size_t FLOW_SMEM_BYTES = FO_BARS + (size_t)FB_COUNT * 8;
 static_assert(FLOW_SMEM_BYTES <= 232448, "series_flow must fit the 227 KB of one SM");
@@ -186,44 +204,55 @@ struct FlowSmem {
     }
     __device__ __forceinline__ PlanScratch* ps() const { return reinterpret_cast<PlanScratch*>(base + FO_PS); }
     __device__ __forceinline__ FinState* fs() const { return reinterpret_cast<FinState*>(base + FO_FS); }
-    __device__ __forceinline__ unsigned* csm() const { return reinterpret_cast<unsigned*>(base + FO_PSTATE); }   // [2][F_NC]
-    __device__ __forceinline__ unsigned* cgl() const { return csm() + 2 * F_NC; }                               // [2][F_NC]
-    __device__ __forceinline__ unsigned* ovf() const { return cgl() + 2 * F_NC; }
-    __device__ __forceinline__ unsigned* hcnt() const { return ovf() + 2; }   // [2][F_NH]
+    __device__ __forceinline__ unsigned* csm() const { return reinterpret_cast<unsigned*>(base + FO_PSTATE); }   // [F_ND][F_NC]
+    __device__ __forceinline__ unsigned* cgl() const { return csm() + F_ND * F_NC; }                            // [F_ND][F_NC]
+    __device__ __forceinline__ unsigned* ovf() const { return cgl() + F_ND * F_NC; }                            // [F_ND]
+    __device__ __forceinline__ unsigned* hcnt() const { return ovf() + F_ND; }                                  // [F_ND][F_NH]
+    __device__ __forceinline__ unsigned* rel() const { return hcnt() + F_ND * F_NH; }   // releases of pool window 0 / 1
+    // Ring groups the producer has issued so far.  TMA copies land in any order and a parity wait only tells a phase
+    // from its predecessor, so a consumer first makes sure that "its" use of a ring slot has been issued (which
+    // implies that the slot's previous use is complete) and only then waits for the barrier's parity.
+    __device__ __forceinline__ volatile unsigned* issued() const { return rel() + 2; }
     __device__ __forceinline__ uint64_t* bar(int i) const { return reinterpret_cast<uint64_t*>(base + FO_BARS) + i; }
 };
 
 // Where one series' candidates live: a window of the shared-memory pool and a window of the CTA's global spill,
 // each cut into F_NC equal parts, one per collector warp (no atomics between them).  Counters and spill windows
-// alternate with the series number; the shared-memory pool is halved the same way when series are short enough
-// (two series in flight), otherwise it is one window that the next series may only enter once the finish warps are
-// done with the previous one -- until then its candidates go to the spill.
+// belong to the series' slot (k % F_ND: a slot is reused only after the finish warps are done with it).  The
+// shared-memory pool is halved when series are short enough (two series in flight), otherwise it is one window;
+// either way the next series may only enter a window once the finish warps have released it (a release counter in
+// shared memory) -- until then its candidates go to the spill.
 struct PoolWin {
     uint32_t s_base, s_sub;     // entries: collector c owns pool[s_base + c * s_sub ...)
     uint32_t g_base, g_sub;     //          and spill[g_base + c * g_sub ...)
-    int buf;                    // k & 1: which set of counters / spill half
-    int bar;                    // FB_POOL + bar guards the shared-memory window
-    uint32_t use;               // how often that window has been used before
+    int d;                      // slot: which set of counters / spill window
+    int win;                    // which shared-memory window (0 / 1)
+    uint32_t use;               // releases of that window that must have happened before this series may enter it
 };
 __device__ __forceinline__ PoolWin pool_window(bool single, uint32_t k, int spill_cap) {
     PoolWin w;
-    w.buf = (int)(k & 1u);
-    w.g_sub = (uint32_t)spill_cap / 2 / F_NC;
-    w.g_base = w.buf * ((uint32_t)spill_cap / 2);
+    w.d = (int)(k % F_ND);
+    w.g_sub = (uint32_t)spill_cap / F_ND / F_NC;
+    w.g_base = (uint32_t)w.d * ((uint32_t)spill_cap / F_ND);
     if (single) {
-        w.bar = 0;
+        w.win = 0;
         w.use = k;
         w.s_base = 0;
         w.s_sub = F_POOL / F_NC;
     } else {
-        w.bar = w.buf;
+        w.win = (int)(k & 1u);
         w.use = k >> 1;
         w.s_sub = F_POOL / 2 / F_NC;
-        w.s_base = w.buf * (F_POOL / 2);
+        w.s_base = (uint32_t)w.win * (F_POOL / 2);
     }
     return w;
 }
 
+__device__ __forceinline__ void wait_group_full(const FlowSmem& sm, uint32_t grp) {
+    volatile unsigned* iss = sm.issued();
+    while (*iss <= grp) __nanosleep(64);
+    mbar_wait(sm.bar(FB_FULL + (int)(grp % F_NGROUPS)), (grp / F_NGROUPS) & 1u);
+}
 __device__ __forceinline__ void plan_sync() { asm volatile("bar.sync 3, %0;" ::"n"(F_NP * 32) : "memory"); }
 __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(F_NF * 32) : "memory"); }
 
@@ -446,6 +475,9 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         if (ptid == 0) {
             if (ns >= (unsigned)F_MIN_SAMPLE && kmin64 == kmax64) sl->konst = 1;
             else sl->defer = 1;
+#ifdef KO_FLOW_DEBUG
+            if (sl->defer) printf("plan deferred: sid %d L %d ns %u kmin %llx kmax %llx\n", sl->sid, L, ns, kmin64, kmax64);
+#endif
             if (ns) {
                 sl->mn_seed = ko_key2d(kmin64);
                 sl->mx_seed = ko_key2d(kmax64);
@@ -657,12 +689,19 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         pts = pts > heavy_pts ? pts - heavy_pts : 0u;
         const PoolWin pw = pool_window(single, kser, a.spill_cap);
         // the candidates are spread over F_NC collector windows (stage groups go round); leave room for skew
-        const double expect = (double)pts * (double)L / (double)S * 1.4 + 256.0;
+        const double expect = (double)pts * (double)L / (double)S * 1.25 + 256.0;
         sl->ni = ni;
         sl->nheavy = nh;
         sl->mn_seed = ko_key2d(kmin64);
         sl->mx_seed = ko_key2d(kmax64);
         if (expect > (double)((pw.s_sub + pw.g_sub) * F_NC)) {
+#ifdef KO_FLOW_DEBUG
+            printf("plan deferred (capacity): sid %d L %d pts %u heavy_pts %u S %d ns %u expect %f cap %u ni %d | A %x W %x | A %x W %x | "
+                   "A %x W %x | tcum %u %u %u %u %u %u tbin %d %d %d %d %d %d\n", sl->sid, L, pts,
+                   heavy_pts, S, ns, expect, (pw.s_sub + pw.g_sub) * F_NC, ni, sl->A[0], sl->W[0], sl->A[1], sl->W[1], sl->A[2],
+                   sl->W[2], ps->tcum[0], ps->tcum[1], ps->tcum[2], ps->tcum[3], ps->tcum[4], ps->tcum[5], ps->tbin[0],
+                   ps->tbin[1], ps->tbin[2], ps->tbin[3], ps->tbin[4], ps->tbin[5]);
+#endif
             sl->defer = 1;
             sl->ni = 0;
             sl->nheavy = 0;
@@ -815,10 +854,12 @@ __device__ __forceinline__ void stream_series(const FlowSmem& sm, const FlowSlot
         const uint32_t cgi = cg0 + (uint32_t)(j / F_GS);
         const uint32_t bs = cgi % F_BG, buse = cgi / F_BG;
         const uint32_t bm_addr = bm0 + bs * (uint32_t)(F_GS * 64) + (g % F_GS) * 64u;
+        if (lane == 0 && ws < 3) FP(5 + ws, 0, 16 + j);
+        wait_group_full(sm, grp);
+        FT_MARK(32);   // stream warp 0: waiting for a full stage
+        // (after the ring wait: the bitmap slot's previous group is then known to be older than this one)
         if (NI > 0 && buse > 0u) mbar_wait_addr(bmempty0 + bs * 8u, (buse - 1u) & 1u);   // the collector has read it
         FT_MARK(34);   // stream warp 0: waiting for the bitmap slot
-        mbar_wait_addr(full0 + s * 8u, par);
-        FT_MARK(32);   // stream warp 0: waiting for a full stage
         if (j < n) {
             if (j == 0 || j == n - 1) {
                 const int end_valid = L + lead - j * F_STAGE;
@@ -917,8 +958,8 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
     unsigned npool_raw = 0;
 #pragma unroll
     for (int c = 0; c < F_NC; ++c)
-        npool_raw += ni > 0 ? sm.csm()[pw.buf * F_NC + c] + sm.cgl()[pw.buf * F_NC + c] : 0u;
-    const bool overflow = ni > 0 && sm.ovf()[pw.buf] != 0u;
+        npool_raw += ni > 0 ? sm.csm()[pw.d * F_NC + c] + sm.cgl()[pw.d * F_NC + c] : 0u;
+    const bool overflow = ni > 0 && sm.ovf()[pw.d] != 0u;
     const unsigned npool = overflow ? 0u : npool_raw;
     const int nheavy = sl->nheavy;
     // ---- B. per-quantile start state
@@ -992,8 +1033,8 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
         };
 #pragma unroll 1
         for (int c = 0; c < F_NC; ++c) {
-            const unsigned nsm = npool > 0u ? sm.csm()[pw.buf * F_NC + c] : 0u;
-            const unsigned ng = npool > 0u ? sm.cgl()[pw.buf * F_NC + c] : 0u;
+            const unsigned nsm = npool > 0u ? sm.csm()[pw.d * F_NC + c] : 0u;
+            const unsigned ng = npool > 0u ? sm.cgl()[pw.d * F_NC + c] : 0u;
             const unsigned long long* wbase = sm.pool() + pw.s_base + (uint32_t)c * pw.s_sub;
 #pragma unroll 1
             for (unsigned i = ftid; i < nsm; i += F_NF * 32) visit(wbase[i], 1u);
@@ -1012,7 +1053,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
             }
         }
         if (ftid < nheavy) {
-            const unsigned mult = sm.hcnt()[pw.buf * F_NH + ftid];
+            const unsigned mult = sm.hcnt()[pw.d * F_NH + ftid];
             if (mult) visit(sl->heavy[ftid], mult);
         }
         fin_sync();
@@ -1037,7 +1078,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                     bool hv = false;
                     if (lane < nheavy) {
                         const unsigned long long hk = sl->heavy[lane];
-                        hv = hk >= nlo && ((hk - nlo) >> sh) == 0ull && sm.hcnt()[pw.buf * F_NH + lane] == cnt;
+                        hv = hk >= nlo && ((hk - nlo) >> sh) == 0ull && sm.hcnt()[pw.d * F_NH + lane] == cnt;
                     }
                     const unsigned hb = __ballot_sync(0xffffffffu, hv);
                     if (lane == 0) {
@@ -1091,6 +1132,11 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                         fs->st[j] = Q_FAIL;
                         fs->fail = 1;
                         fs->why = 6;
+#ifdef KO_FLOW_DEBUG
+                        printf("select failed: sid %d L %d q %d n %u list_n %u rho %u sh %d lo %llx nheavy %d\n", sid, L, j, n,
+                               fs->list_n[j], rho, fs->sh[j], fs->lo[j], nheavy);
+                        for (unsigned e = 0; e < n && e < 8; ++e) printf("   key %llx mult %u\n", lk[e], lm[e]);
+#endif
                     }
                     atomicSub(&fs->pending, 1);
                 }
@@ -1116,12 +1162,12 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                 a.out_quant[(int64_t)sid * nq + a.qcol[j]] = fs->ans[j] == ~0ull ? nan : ko_key2d(fs->ans[j]);
         }
     }
-    if (ftid < F_NH) sm.hcnt()[pw.buf * F_NH + ftid] = 0u;
+    if (ftid < F_NH) sm.hcnt()[pw.d * F_NH + ftid] = 0u;
     if (ftid >= 32 && ftid < 32 + F_NC) {
-        sm.csm()[pw.buf * F_NC + (ftid - 32)] = 0u;
-        sm.cgl()[pw.buf * F_NC + (ftid - 32)] = 0u;
+        sm.csm()[pw.d * F_NC + (ftid - 32)] = 0u;
+        sm.cgl()[pw.d * F_NC + (ftid - 32)] = 0u;
     }
-    if (ftid == 64) sm.ovf()[pw.buf] = 0u;
+    if (ftid == 64) sm.ovf()[pw.d] = 0u;
     fin_sync();
 }
 
@@ -1148,11 +1194,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             mbar_init(sm.bar(FB_CDONE + d), F_NC);
             mbar_init(sm.bar(FB_START + d), 1);
         }
-        mbar_init(sm.bar(FB_POOL + 0), 1);
-        mbar_init(sm.bar(FB_POOL + 1), 1);
         mbar_fence_init();
     }
     if (tid < F_PSTATE_WORDS) sm.csm()[tid] = 0u;
+#ifdef KO_FLOW_PROGRESS
+    if (tid == 0) g_flow_wide = (unsigned)a.wide;
+    if (tid < 8) reinterpret_cast<volatile unsigned*>(g_flow_prog)[blockIdx.x * 8 + tid] = ((unsigned)a.wide << 31) | 0xFFFu;
+#endif
     __syncthreads();
     const int n_work = a.counters[a.work_cnt];
     const bool single = a.wide != 0 || a.counters[8] > F_DOUBLE_MAXL;
@@ -1166,7 +1214,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             FT_BEGIN(blockIdx.x == 0);
             for (uint32_t k = 0;; ++k) {
                 const int d = (int)(k % F_ND);
+                FP(0, k, 1);
                 mbar_wait_hint(sm.bar(FB_DESC + d), (k / F_ND) & 1u);
+                FP(0, k, 2);
                 FT_MARK(0);   // producer: waiting for a descriptor
                 const FlowSlot* sl = sm.slot(d);
                 if (sl->sid < 0) break;
@@ -1184,6 +1234,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                     const uint32_t grp = grp0 + (uint32_t)gi;
                     const uint32_t s = grp % F_NGROUPS, u = grp / F_NGROUPS;
                     FT_MARK(2);   // producer: issuing
+                    FP(0, k, 16 + gi);
                     if (u > 0) mbar_wait(sm.bar(FB_EMPTY + s), (u - 1u) & 1u);
                     FT_MARK(1);   // producer: waiting for a free group
                     const uint32_t off = (uint32_t)gi * F_GROUP_BYTES;
@@ -1199,6 +1250,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                         const double x = a.values[sl->start + sl->L - 1];
                         sts_f64(dst + (uint32_t)e * 8u, x);
                     }
+                    *sm.issued() = grp + 1u;   // (after the wait for the slot: its previous use is over)
                     if (bytes) {
                         mbar_expect_tx(sm.bar(FB_FULL + s), bytes);
                         tma_bulk_g2s_hint(dst, src + off, bytes, smem_u32(sm.bar(FB_FULL + s)), policy);
@@ -1220,11 +1272,14 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const int d = (int)(k % F_ND);
             FT_MARK(6);   // planner: planning
             // slot reuse: the finish of series k - F_ND; long series: stay one series ahead of the stream warps only
+            if (ptid == 0) FP(1, k, 1);
             if (k >= (uint32_t)F_ND) mbar_wait_hint(sm.bar(FB_FREE + d), ((k / F_ND) - 1u) & 1u);
+            if (ptid == 0) FP(1, k, 2);
             if (prev_depth1 && k >= 1u) {   // the stream warps have begun series k - 1
                 const uint32_t kk = k - 1u;
                 mbar_wait_hint(sm.bar(FB_START + (int)(kk % F_ND)), (kk / F_ND) & 1u);
             }
+            if (ptid == 0) FP(1, k, 3);
             FT_MARK(5);   // planner: waiting for the finish warps (slot / depth)
             FlowSlot* sl = sm.slot(d);
             if (ptid == 0) {
@@ -1263,7 +1318,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             }
             g += (uint32_t)((sl->nstages + F_GS - 1) / F_GS * F_GS);   // every series starts a ring group
             prev_depth1 = sl->depth1;
+            if (ptid == 0) FP(1, k, 4);
             planner_plan(a, sm, sl, ptid, single, k);
+            if (ptid == 0) FP(1, k, 5);
             if (ptid == 0) mbar_arrive(sm.bar(FB_PLAN + d));
         }
     } else if (warp >= F_W_COLL) {
@@ -1280,7 +1337,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const int d = (int)(k % F_ND);
             const uint32_t par = (k / F_ND) & 1u;
             FT_MARK(41);   // collector 0: working
+            if (lane == 0) FP(2 + (cw & 1), k, 1);
             mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            if (lane == 0) FP(2 + (cw & 1), k, 2);
             FT_MARK(40);   // collector 0: waiting for the plan
             const FlowSlot* sl = sm.slot(d);
             if (sl->sid < 0) break;
@@ -1300,15 +1359,19 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             for (; gi < ngroups; gi += F_NC) {
                 const uint32_t grp = grp0 + (uint32_t)gi;
                 const uint32_t s = grp % F_NGROUPS, u = grp / F_NGROUPS;
+                if (lane == 0) FP(2 + (cw & 1), k, 16 + gi);
                 if (ni == 0) {
-                    mbar_wait_hint(sm.bar(FB_FULL + s), u & 1u);   // the group's phase has begun
+                    wait_group_full(sm, grp);   // the group's phase has begun
                     if (lane == 0) mbar_arrive(sm.bar(FB_EMPTY + s));
                     continue;
                 }
                 const uint32_t cgi = cg + (uint32_t)gi;
                 const uint32_t bs = cgi % F_BG, buse = cgi / F_BG;
+                // Order matters: a parity wait only tells this phase from the previous one.  Once the ring group is
+                // full, every earlier group has been handed back (the producer loads in order), so the bitmap slot's
+                // previous use is over and the second wait cannot mistake it for this one.
+                wait_group_full(sm, grp);
                 mbar_wait_hint(sm.bar(FB_BMFULL + bs), buse & 1u);
-                mbar_wait_hint(sm.bar(FB_FULL + s), u & 1u);       // (complete long ago: the TMA bytes are visible)
                 FT_MARK(42);   // collector 0: waiting for bitmaps
                 LaneBits lb;
                 lds_v2u32(bm0 + bs * (uint32_t)(F_GS * 64) + (uint32_t)lane * 8u, lb.w0, lb.w1);
@@ -1328,7 +1391,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
 #pragma unroll
                             for (int h = 0; h < F_NH; ++h) hit = hkey[h] == key ? h : hit;
                             if (hit >= 0) {
-                                red_shared_add(&sm.hcnt()[pw.buf * F_NH + hit], 1u);
+                                red_shared_add(&sm.hcnt()[pw.d * F_NH + hit], 1u);
                                 k0 &= ~(p0 ^ rest.w0);   // clear the bit just popped
                                 k1 &= ~(p1 ^ rest.w1);
                             }
@@ -1345,7 +1408,10 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                     }
                     const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
                     FT_MARK(43);   // collector 0: counting
-                    if (!pool_ok) pool_ok = mbar_test(sm.bar(FB_POOL + pw.bar), (pw.use - 1u) & 1u);
+                    if (!pool_ok) {
+                        pool_ok = *reinterpret_cast<volatile unsigned*>(&sm.rel()[pw.win]) >= pw.use;
+                        __threadfence_block();
+                    }
                     const unsigned avail = pool_ok ? pw.s_sub - cs : 0u;     // shared-memory entries left
                     const unsigned take = total < avail ? total : avail;
                     unsigned e = incl - n;                                       // this lane's first entry of the batch
@@ -1371,10 +1437,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             }
             if (ni > 0) cg += (uint32_t)ngroups;
             over = __any_sync(0xffffffffu, over);
+            if (cgs > 0u) __threadfence();   // spilled keys: in L2 before the finish warps read them
             if (lane == 0) {
-                sm.csm()[pw.buf * F_NC + cw] = cs;
-                sm.cgl()[pw.buf * F_NC + cw] = cgs < pw.g_sub ? cgs : pw.g_sub;
-                if (over) sm.ovf()[pw.buf] = 1u;
+                sm.csm()[pw.d * F_NC + cw] = cs;
+                sm.cgl()[pw.d * F_NC + cw] = cgs < pw.g_sub ? cgs : pw.g_sub;
+                if (over) sm.ovf()[pw.d] = 1u;
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(sm.bar(FB_CDONE + d));
@@ -1387,17 +1454,23 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const int d = (int)(k % F_ND);
             const uint32_t par = (k / F_ND) & 1u;
             FT_MARK(22);   // finish: working
+            if (ftid == 0) FP(4, k, 1);
             mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            if (ftid == 0) FP(4, k, 2);
             FT_MARK(20);   // finish: waiting for the plan
             const FlowSlot* sl = sm.slot(d);
             if (sl->sid < 0) break;
             mbar_wait_hint(sm.bar(FB_SDONE + d), par);
+            if (ftid == 0) FP(4, k, 3);
             mbar_wait_hint(sm.bar(FB_CDONE + d), par);
+            if (ftid == 0) FP(4, k, 4);
             FT_MARK(21);   // finish: waiting for the stream warps and the collectors
             const PoolWin pw = pool_window(single, k, a.spill_cap);
             finish_series(a, sm, sl, d, ftid, pw, spill);
-            if (ftid == 0) {
-                mbar_arrive(sm.bar(FB_POOL + pw.bar));
+            if (ftid == 0) FP(4, k, 5);
+            if (ftid == 0) {   // (finish_series ends with a barrier of the finish warps: all reads of the pool are done)
+                __threadfence_block();
+                atomicAdd(&sm.rel()[pw.win], 1u);
                 mbar_arrive(sm.bar(FB_FREE + d));
             }
         }
@@ -1410,7 +1483,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const int d = (int)(k % F_ND);
             const uint32_t par = (k / F_ND) & 1u;
             FT_MARK(31);   // stream warp 0: working (scan + epilogue)
+            if (lane == 0 && ws < 3) FP(5 + ws, k, 1);
             mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            if (lane == 0 && ws < 3) FP(5 + ws, k, 2);
             FT_MARK(30);   // stream warp 0: waiting for the plan
             const FlowSlot* sl = sm.slot(d);
             if (sl->sid < 0) break;
@@ -1470,6 +1545,21 @@ size_t ko_flow_smem_bytes() { return FLOW_SMEM_BYTES; }
 cudaError_t ko_flow_set_attributes() {
     return cudaFuncSetAttribute(series_flow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FLOW_SMEM_BYTES);
 }
+
+#ifdef KO_FLOW_PROGRESS
+extern "C" int ko_debug_flow_progress(unsigned* out2048) {
+    cudaStream_t st;
+    KO_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    void* p = nullptr;
+    KO_CUDA(cudaGetSymbolAddress(&p, g_flow_prog));
+    KO_CUDA(cudaMemcpyAsync(out2048, p, 2032 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    KO_CUDA(cudaGetSymbolAddress(&p, g_flow_trap));
+    KO_CUDA(cudaMemcpyAsync(out2048 + 2032, p, 16 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    KO_CUDA(cudaStreamSynchronize(st));
+    cudaStreamDestroy(st);
+    return KO_OK;
+}
+#endif
 
 #ifdef KO_FLOW_TIMING
 extern "C" int ko_debug_flow_phases(unsigned long long* out64, int reset) {

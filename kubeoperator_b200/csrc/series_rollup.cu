@@ -1304,7 +1304,7 @@ __global__ void series_tally(const int* counters, int* tally) {
 }
 
 constexpr int N_COUNTERS = 16;
-constexpr int SPILL_MAX = 32768;         // candidate keys one series_flow CTA may spill to global scratch
+constexpr int SPILL_MAX = 49152;         // candidate keys one series_flow CTA may spill to global scratch
 // counters + the two series lists, rounded so that the spill space behind them is 256-byte aligned
 constexpr size_t series_lists_bytes(int64_t n_series) {
     return ((size_t)(N_COUNTERS + 2 * n_series) * sizeof(int) + 255) / 256 * 256;
@@ -1351,10 +1351,19 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
     a.out_cnt = 4;
     a.wide = 0;
     cudaError_t e;
+    if (getenv("KO_DEBUG_FORCE_LONG")) {   // development: everything through the slow exact path
+        a.work_cur = 7;
+        series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
+        *launches += 1;
+        return cudaGetLastError();
+    }
     if (ev_p0) cudaEventRecord(ev_p0, st);
     if ((e = ko_flow_launch(&a, fgrid, st)) != cudaSuccess) return e;
     if (ev_p1) cudaEventRecord(ev_p1, st);
     *launches += 1;
+    const char* dbg = getenv("KO_DEBUG_STAGES");   // development: stop after the first n kernels of the long path
+    const int stages = dbg ? atoi(dbg) : 3;
+    if (stages < 2) return cudaSuccess;
     if (a.nq > 0) {
         a.work_list = a.defer_list;
         a.work_cnt = 4;
@@ -1371,6 +1380,7 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
         a.work_cnt = 4;
     }
     a.work_cur = 7;
+    if (stages < 3) return cudaSuccess;
     series_long<<<grid, NTHREADS, LONG_SMEM_BYTES, st>>>(a);
     *launches += 1;
     return cudaGetLastError();

@@ -79,7 +79,7 @@ if "parity" in what:
     print("PARITY", "OK" if ok else "FAILED", flush=True)
 
 if "speed" in what:
-    for name, cfg, n in (("7-day c2", "c2", None), ("30-day c3 slice", "c3", 2400)):
+    for name, cfg, n in (("7-day c2", "c2", None), ("30-day c3 slice", "c3", 5920)):
         vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", n_series_override=n)
         n = len(kinds)
         q = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
