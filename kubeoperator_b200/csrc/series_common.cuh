@@ -35,6 +35,8 @@ struct SeriesArgs {
     int* out_list;          // series_flow: where the series it cannot finish go ...
     int out_cnt;            // ... counted in counters[out_cnt]
     int wide;               // series_flow: second attempt, brackets 5 sigma wide, one undivided candidate pool
+    int pack;               // n_series < 2^27: the first attempt's list carries one entry per unanswered quantile,
+                            // (quantile << 27) | series; otherwise one entry per series
     // series_flow: candidates that do not fit a CTA's shared-memory pool spill to spill[blockIdx.x * spill_cap ...]
     unsigned long long* spill;
     int spill_cap;

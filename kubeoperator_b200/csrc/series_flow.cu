@@ -78,6 +78,7 @@ struct alignas(16) FlowSlot {
     uint32_t total_bytes;    // TMA bytes of the whole series (a multiple of 16)
     int tail_fix;            // the last element is stored by hand (it ends the whole array on an odd element)
     int depth1;              // long series: the planner stays one series ahead only (L2 footprint of its gather)
+    int qsel;                // second attempt: the one quantile this work item is about, or -1 for all of them
     const double* src;       // 16-byte aligned address of stage 0
     long long start;         // element index of the series in values
     // plan (planner)
@@ -178,8 +179,8 @@ constexpr size_t FO_SLOTS = FO_BITMAP + (size_t)F_BG * F_GS * 64;
 constexpr size_t FO_PART = FO_SLOTS + align_up(F_ND * sizeof(FlowSlot), 16);
 constexpr size_t FO_PS = FO_PART + (size_t)F_ND * F_NS * sizeof(FlowPartial);
 constexpr size_t FO_FS = FO_PS + align_up(sizeof(PlanScratch), 16);
-constexpr size_t FO_PSTATE = FO_FS + align_up(sizeof(FinState), 16);   // csm[F_ND][F_NC], cgl[F_ND][F_NC], ovf[F_ND], hcnt[F_ND][F_NH], rel[2]
-constexpr int F_PSTATE_WORDS = F_ND * (2 * F_NC + 1 + F_NH) + 2 + 2;   // ..., rel[2], issued, (pad)
+constexpr size_t FO_PSTATE = FO_FS + align_up(sizeof(FinState), 16);   // csm[F_ND], cgl[F_ND], ovf[F_ND], hcnt[F_ND][F_NH], rel[2], issued
+constexpr int F_PSTATE_WORDS = F_ND * (3 + F_NH) + 2 + 2;
 constexpr size_t FO_BARS = FO_PSTATE + align_up(F_PSTATE_WORDS * 4, 16);
 constexpr size_t FLOW_SMEM_BYTES = FO_BARS + (size_t)FB_COUNT * 8;
 static_assert(FLOW_SMEM_BYTES <= 232448, "series_flow must fit the 227 KB of one SM");
@@ -204,9 +205,9 @@ struct FlowSmem {
     }
     __device__ __forceinline__ PlanScratch* ps() const { return reinterpret_cast<PlanScratch*>(base + FO_PS); }
     __device__ __forceinline__ FinState* fs() const { return reinterpret_cast<FinState*>(base + FO_FS); }
-    __device__ __forceinline__ unsigned* csm() const { return reinterpret_cast<unsigned*>(base + FO_PSTATE); }   // [F_ND][F_NC]
-    __device__ __forceinline__ unsigned* cgl() const { return csm() + F_ND * F_NC; }                            // [F_ND][F_NC]
-    __device__ __forceinline__ unsigned* ovf() const { return cgl() + F_ND * F_NC; }                            // [F_ND]
+    __device__ __forceinline__ unsigned* csm() const { return reinterpret_cast<unsigned*>(base + FO_PSTATE); }   // [F_ND] pool cursor
+    __device__ __forceinline__ unsigned* cgl() const { return csm() + F_ND; }                                   // [F_ND] spill cursor
+    __device__ __forceinline__ unsigned* ovf() const { return cgl() + F_ND; }                                   // [F_ND]
     __device__ __forceinline__ unsigned* hcnt() const { return ovf() + F_ND; }                                  // [F_ND][F_NH]
     __device__ __forceinline__ unsigned* rel() const { return hcnt() + F_ND * F_NH; }   // releases of pool window 0 / 1
     // Ring groups the producer has issued so far.  TMA copies land in any order and a parity wait only tells a phase
@@ -217,32 +218,33 @@ struct FlowSmem {
 };
 
 // Where one series' candidates live: a window of the shared-memory pool and a window of the CTA's global spill,
-// each cut into F_NC equal parts, one per collector warp (no atomics between them).  Counters and spill windows
-// belong to the series' slot (k % F_ND: a slot is reused only after the finish warps are done with it).  The
-// shared-memory pool is halved when series are short enough (two series in flight), otherwise it is one window;
-// either way the next series may only enter a window once the finish warps have released it (a release counter in
-// shared memory) -- until then its candidates go to the spill.
+// both filled through a cursor shared by the collector warps (a monotone series has all candidates of an interval
+// in a few consecutive ring groups, i.e. in the hands of one or two collectors).  Cursors, tie-level counters and
+// the spill window belong to the series' slot (k % F_ND: a slot is reused only after the finish warps are done
+// with it).  The shared-memory pool is halved when series are short enough (two series in flight), otherwise it is
+// one window; either way the next series may only enter a window once the finish warps have released it (a release
+// counter in shared memory) -- until then its candidates go to the spill.
 struct PoolWin {
-    uint32_t s_base, s_sub;     // entries: collector c owns pool[s_base + c * s_sub ...)
-    uint32_t g_base, g_sub;     //          and spill[g_base + c * g_sub ...)
-    int d;                      // slot: which set of counters / spill window
+    uint32_t s_base, s_cap;     // entries pool[s_base ... s_base + s_cap)
+    uint32_t g_base, g_cap;     //         spill[g_base ... g_base + g_cap)
+    int d;                      // slot: which cursors / spill window
     int win;                    // which shared-memory window (0 / 1)
     uint32_t use;               // releases of that window that must have happened before this series may enter it
 };
 __device__ __forceinline__ PoolWin pool_window(bool single, uint32_t k, int spill_cap) {
     PoolWin w;
     w.d = (int)(k % F_ND);
-    w.g_sub = (uint32_t)spill_cap / F_ND / F_NC;
-    w.g_base = (uint32_t)w.d * ((uint32_t)spill_cap / F_ND);
+    w.g_cap = (uint32_t)spill_cap / F_ND;
+    w.g_base = (uint32_t)w.d * w.g_cap;
     if (single) {
         w.win = 0;
         w.use = k;
         w.s_base = 0;
-        w.s_sub = F_POOL / F_NC;
+        w.s_cap = F_POOL;
     } else {
         w.win = (int)(k & 1u);
         w.use = k >> 1;
-        w.s_sub = F_POOL / 2 / F_NC;
+        w.s_cap = F_POOL / 2;
         w.s_base = (uint32_t)w.win * (F_POOL / 2);
     }
     return w;
@@ -388,6 +390,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
     const int L = sl->L;
     const double* v = a.values + sl->start;
     const int nq = a.nq;
+    const int qsel = sl->qsel;
     FT_BEGIN(blockIdx.x == 0 && ptid == 0);
     const double pinf = __longlong_as_double(0x7FF0000000000000LL);
     if (ptid == 0) {
@@ -524,7 +527,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         if (lane < F_NT) {
             const int j = lane >> 1;
             unsigned tr = 0;
-            if (j < nq) {
+            if (j < nq && (qsel < 0 || j == qsel)) {
                 const double z = a.wide ? 5.0 : 3.0;
                 const double p = a.q[j];
                 const double n = (double)ns;
@@ -628,7 +631,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         unsigned ca = 0, cb = 0, pts = 0;
 #pragma unroll
         for (int j = 0; j < NI_MAX; ++j) {
-            if (j < nq) {
+            if (j < nq && (qsel < 0 || j == qsel)) {
                 const int ta = 2 * j, tb = 2 * j + 1;
                 uint32_t A = 0u, B = HK_PINF;
                 unsigned ra = 0u, rb = ns;
@@ -688,17 +691,16 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         }
         pts = pts > heavy_pts ? pts - heavy_pts : 0u;
         const PoolWin pw = pool_window(single, kser, a.spill_cap);
-        // the candidates are spread over F_NC collector windows (stage groups go round); leave room for skew
         const double expect = (double)pts * (double)L / (double)S * 1.25 + 256.0;
         sl->ni = ni;
         sl->nheavy = nh;
         sl->mn_seed = ko_key2d(kmin64);
         sl->mx_seed = ko_key2d(kmax64);
-        if (expect > (double)((pw.s_sub + pw.g_sub) * F_NC)) {
+        if (expect > (double)(pw.s_cap + pw.g_cap)) {
 #ifdef KO_FLOW_DEBUG
             printf("plan deferred (capacity): sid %d L %d pts %u heavy_pts %u S %d ns %u expect %f cap %u ni %d | A %x W %x | A %x W %x | "
                    "A %x W %x | tcum %u %u %u %u %u %u tbin %d %d %d %d %d %d\n", sl->sid, L, pts,
-                   heavy_pts, S, ns, expect, (pw.s_sub + pw.g_sub) * F_NC, ni, sl->A[0], sl->W[0], sl->A[1], sl->W[1], sl->A[2],
+                   heavy_pts, S, ns, expect, pw.s_cap + pw.g_cap, ni, sl->A[0], sl->W[0], sl->A[1], sl->W[1], sl->A[2],
                    sl->W[2], ps->tcum[0], ps->tcum[1], ps->tcum[2], ps->tcum[3], ps->tcum[4], ps->tcum[5], ps->tbin[0],
                    ps->tbin[1], ps->tbin[2], ps->tbin[3], ps->tbin[4], ps->tbin[5]);
 #endif
@@ -824,7 +826,7 @@ __device__ __forceinline__ void patch_stage_edges(uint32_t stage_addr, int lane,
     __syncwarp();
 }
 
-// Stage g = g0 + j of a series belongs to stream warp g % F_NS and to ring group (g / F_GS) % F_NGROUPS.  A series
+// Stage j of a series (ring stage g = g0 + j) belongs to stream warp j % F_NS and to ring group (g / F_GS) % F_NGROUPS.  A series
 // starts on a group boundary; the stage numbers that pad its last group are visited too (wait, release, no work),
 // so that every group gets its F_GS releases.  cg0: bitmap-ring group number of the series' first group (groups of
 // series without capture intervals do not use the bitmap ring and are not counted).
@@ -845,8 +847,9 @@ __device__ __forceinline__ void stream_series(const FlowSmem& sm, const FlowSlot
     const uint32_t full0 = smem_u32(sm.bar(FB_FULL)), empty0 = smem_u32(sm.bar(FB_EMPTY));
     const uint32_t bmfull0 = smem_u32(sm.bar(FB_BMFULL)), bmempty0 = smem_u32(sm.bar(FB_BMEMPTY));
     FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
-    int j = (int)(((uint32_t)ws + F_NS - (g0 % F_NS)) % F_NS);
-    for (; j < npad; j += F_NS) {
+    // (stage j of a series always goes to stream warp j % F_NS, whatever the CTA did before: the partial sums of a
+    // series, and with them the last bits of its sum, do not depend on how the work was distributed)
+    for (int j = ws; j < npad; j += F_NS) {
         const uint32_t g = g0 + (uint32_t)j;
         const uint32_t grp = g / F_GS;
         const uint32_t s = grp % F_NGROUPS, par = (grp / F_NGROUPS) & 1u;
@@ -956,9 +959,9 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
     fin_sync();
     const unsigned nvalid = fs->nvalid;
     unsigned npool_raw = 0;
-#pragma unroll
-    for (int c = 0; c < F_NC; ++c)
-        npool_raw += ni > 0 ? sm.csm()[pw.d * F_NC + c] + sm.cgl()[pw.d * F_NC + c] : 0u;
+    const unsigned nsm_all = ni > 0 ? min(sm.csm()[pw.d], pw.s_cap) : 0u;
+    const unsigned ng_all = ni > 0 ? min(sm.cgl()[pw.d], pw.g_cap) : 0u;
+    npool_raw = nsm_all + ng_all;
     const bool overflow = ni > 0 && sm.ovf()[pw.d] != 0u;
     const unsigned npool = overflow ? 0u : npool_raw;
     const int nheavy = sl->nheavy;
@@ -967,7 +970,10 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
         const int j = ftid;
         int st = Q_DONE;
         unsigned long long ans = ~0ull;   // "NaN"
-        if (j < nq && nvalid > 0 && !fs->fail) {
+        const int qsel = sl->qsel;
+        if (j < nq && qsel >= 0 && j != qsel) {
+            // not this work item's quantile: answered by the first attempt or by another item
+        } else if (j < nq && nvalid > 0 && !fs->fail) {
             if (sl->konst) {
                 if (ko_okey(fs->mn + 0.0) == ko_okey(fs->mx + 0.0)) ans = ko_okey(fs->mn + 0.0);
                 else {
@@ -1004,7 +1010,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
     fin_sync();
     // ---- C. rounds: histogram refinement, then direct selection among <= F_LIST candidates
     int guard = 0;
-    while (fs->pending > 0 && !fs->fail && guard++ < 24) {
+    while (fs->pending > 0 && guard++ < 24) {   // (a quantile that fails does not stop the others)
         for (int i = ftid; i < NI_MAX * 256; i += F_NF * 32) sm.fbins()[i] = 0;
         fin_sync();
         int stj[NI_MAX], shj[NI_MAX];
@@ -1031,15 +1037,14 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                 }
             }
         };
-#pragma unroll 1
-        for (int c = 0; c < F_NC; ++c) {
-            const unsigned nsm = npool > 0u ? sm.csm()[pw.d * F_NC + c] : 0u;
-            const unsigned ng = npool > 0u ? sm.cgl()[pw.d * F_NC + c] : 0u;
-            const unsigned long long* wbase = sm.pool() + pw.s_base + (uint32_t)c * pw.s_sub;
+        {
+            const unsigned nsm = npool > 0u ? nsm_all : 0u;
+            const unsigned ng = npool > 0u ? ng_all : 0u;
+            const unsigned long long* wbase = sm.pool() + pw.s_base;
 #pragma unroll 1
             for (unsigned i = ftid; i < nsm; i += F_NF * 32) visit(wbase[i], 1u);
             if (ng > 0u) {   // spilled part: global loads, four in flight
-                const unsigned long long* gbase = spill + pw.g_base + (uint32_t)c * pw.g_sub;
+                const unsigned long long* gbase = spill + pw.g_base;
 #pragma unroll 1
                 for (unsigned i = ftid; i < ng; i += 4u * (F_NF * 32)) {
                     unsigned long long kk[4];
@@ -1153,19 +1158,41 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
         if (a.out_max) a.out_max[sid] = nvalid > 0 ? fs->mx + 0.0 : nan;
         if (a.out_last) a.out_last[sid] = fs->last;
         if (a.out_count) a.out_count[sid] = (int64_t)nvalid;
-        if (fail) {
+        const int qsel = sl->qsel;
+        if (fail) atomicAdd(&a.counters[9 + (fs->why & 7)], 1);
+        if (fail && (a.wide || !a.pack)) {   // whole series to the next list
             const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
             a.out_list[pos] = sid;
-            atomicAdd(&a.counters[9 + (fs->why & 7)], 1);
-        } else if (a.out_quant) {
-            for (int j = 0; j < nq; ++j)
-                a.out_quant[(int64_t)sid * nq + a.qcol[j]] = fs->ans[j] == ~0ull ? nan : ko_key2d(fs->ans[j]);
+        } else {
+            // first attempt: every failed quantile becomes a work item (quantile, series) of the second attempt and
+            // the others are answered here.  A pool that overflowed: all quantiles, one item each.  A failure the
+            // second attempt cannot mend (almost no valid points, a spread below the key resolution, a constant
+            // pre-sample of a series that is not constant): code 6, straight on to the slow path.
+            const bool direct = fail && (fs->why == 0 || fs->why == 4 || fs->why == 5);
+            const bool all = direct || (fail && fs->why == 3);
+            if (direct) {
+                const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
+                a.out_list[pos] = sid | (6 << 27);
+            } else if (fail) {
+                for (int j = 0; j < nq; ++j) {
+                    if (all || fs->st[j] != Q_DONE) {
+                        const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
+                        a.out_list[pos] = sid | (j << 27);
+                    }
+                }
+            }
+            if (a.out_quant && !all) {
+                for (int j = 0; j < nq; ++j) {
+                    if ((qsel >= 0 && j != qsel) || (fail && fs->st[j] != Q_DONE)) continue;   // (not ours / deferred)
+                    a.out_quant[(int64_t)sid * nq + a.qcol[j]] = fs->ans[j] == ~0ull ? nan : ko_key2d(fs->ans[j]);
+                }
+            }
         }
     }
     if (ftid < F_NH) sm.hcnt()[pw.d * F_NH + ftid] = 0u;
-    if (ftid >= 32 && ftid < 32 + F_NC) {
-        sm.csm()[pw.d * F_NC + (ftid - 32)] = 0u;
-        sm.cgl()[pw.d * F_NC + (ftid - 32)] = 0u;
+    if (ftid == 32) {
+        sm.csm()[pw.d] = 0u;
+        sm.cgl()[pw.d] = 0u;
     }
     if (ftid == 64) sm.ovf()[pw.d] = 0u;
     fin_sync();
@@ -1283,11 +1310,23 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             FT_MARK(5);   // planner: waiting for the finish warps (slot / depth)
             FlowSlot* sl = sm.slot(d);
             if (ptid == 0) {
-                const int w = atomicAdd(&a.counters[a.work_cur], 1);
+                int w, item = 0, code = 7;
+                for (;;) {
+                    w = atomicAdd(&a.counters[a.work_cur], 1);
+                    if (w >= n_work) break;
+                    item = a.work_list[w];
+                    // second attempt: a work item is (code, series) when series numbers fit 27 bits: code 0..3 = that
+                    // quantile alone, 7 = all quantiles, 6 = nothing to gain here, straight on to the slow exact path
+                    code = (a.wide && a.pack) ? (int)((unsigned)item >> 27) : 7;
+                    if (code != 6) break;
+                    const int pos = atomicAdd(&a.counters[a.out_cnt], 1);
+                    a.out_list[pos] = item & 0x7FFFFFF;
+                }
                 if (w >= n_work) {
                     sl->sid = -1;
                 } else {
-                    const int sid = a.work_list[w];
+                    const int sid = (a.wide && a.pack) ? (item & 0x7FFFFFF) : item;
+                    sl->qsel = code < NI_MAX ? code : -1;
                     const long long off0 = a.offsets[sid];
                     const int L = (int)(a.offsets[sid + 1] - off0);
                     const double* v = a.values + off0;
@@ -1353,8 +1392,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             // the shared-memory window was last used by series k - 1 (one pool) or k - 2 (two halves); until the
             // finish warps have released it this series' candidates go to the spill window
             bool pool_ok = pw.use == 0u;
-            unsigned cs = 0, cgs = 0;   // entries of this collector in its shared-memory / spill window
-            bool over = false;
+            bool over = false, spilled = false;
             int gi = (int)(((uint32_t)cw + F_NC - (grp0 % F_NC)) % F_NC);
             for (; gi < ngroups; gi += F_NC) {
                 const uint32_t grp = grp0 + (uint32_t)gi;
@@ -1408,25 +1446,37 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                     }
                     const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
                     FT_MARK(43);   // collector 0: counting
-                    if (!pool_ok) {
-                        pool_ok = *reinterpret_cast<volatile unsigned*>(&sm.rel()[pw.win]) >= pw.use;
+                    if (!pool_ok) {   // shared-memory window not released yet: spill, or wait when the spill is full
+                        volatile unsigned* rel = reinterpret_cast<volatile unsigned*>(&sm.rel()[pw.win]);
+                        pool_ok = *rel >= pw.use;
+                        if (!pool_ok && *reinterpret_cast<volatile unsigned*>(&sm.cgl()[pw.d]) + total > pw.g_cap) {
+                            while (*rel < pw.use) __nanosleep(200);
+                            pool_ok = true;
+                        }
                         __threadfence_block();
                     }
-                    const unsigned avail = pool_ok ? pw.s_sub - cs : 0u;     // shared-memory entries left
-                    const unsigned take = total < avail ? total : avail;
+                    // reserve: shared-memory entries first (when the window is ours), the rest in the spill
+                    unsigned sbase = pw.s_cap, gbase_i = 0;
+                    if (lane == 0) {
+                        if (pool_ok) sbase = atom_shared_add(&sm.csm()[pw.d], total);
+                        const unsigned in_s = sbase < pw.s_cap ? min(total, pw.s_cap - sbase) : 0u;
+                        if (in_s < total) gbase_i = atom_shared_add(&sm.cgl()[pw.d], total - in_s);
+                    }
+                    sbase = __shfl_sync(0xffffffffu, sbase, 0);
+                    gbase_i = __shfl_sync(0xffffffffu, gbase_i, 0);
+                    const unsigned take = sbase < pw.s_cap ? min(total, pw.s_cap - sbase) : 0u;
+                    spilled = spilled || take < total;
                     unsigned e = incl - n;                                       // this lane's first entry of the batch
-                    unsigned long long* wb = sm.pool() + pw.s_base + (uint32_t)cw * pw.s_sub + cs;
-                    unsigned long long* gb = spill + pw.g_base + (uint32_t)cw * pw.g_sub + cgs;
+                    unsigned long long* wb = sm.pool() + pw.s_base + sbase;
+                    unsigned long long* gb = spill + pw.g_base + gbase_i;
 #pragma unroll 1
                     while (lb.any()) {
                         const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lb.pop(wi) * 8u) + 0.0);
                         if (e < take) wb[e] = key;
-                        else if (cgs + (e - take) < pw.g_sub) gb[e - take] = key;
+                        else if (gbase_i + (e - take) < pw.g_cap) gb[e - take] = key;
                         else over = true;
                         ++e;
                     }
-                    cs += take;
-                    cgs += total - take;
                 }
                 __syncwarp();
                 if (lane == 0) {
@@ -1437,12 +1487,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             }
             if (ni > 0) cg += (uint32_t)ngroups;
             over = __any_sync(0xffffffffu, over);
-            if (cgs > 0u) __threadfence();   // spilled keys: in L2 before the finish warps read them
-            if (lane == 0) {
-                sm.csm()[pw.d * F_NC + cw] = cs;
-                sm.cgl()[pw.d * F_NC + cw] = cgs < pw.g_sub ? cgs : pw.g_sub;
-                if (over) sm.ovf()[pw.d] = 1u;
-            }
+            if (spilled) __threadfence();   // spilled keys: in L2 before the finish warps read them
+            if (lane == 0 && over) sm.ovf()[pw.d] = 1u;
             __syncwarp();
             if (lane == 0) mbar_arrive(sm.bar(FB_CDONE + d));
         }

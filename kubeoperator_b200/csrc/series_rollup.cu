@@ -1304,10 +1304,12 @@ __global__ void series_tally(const int* counters, int* tally) {
 }
 
 constexpr int N_COUNTERS = 16;
-constexpr int SPILL_MAX = 49152;         // candidate keys one series_flow CTA may spill to global scratch
-// counters + the two series lists, rounded so that the spill space behind them is 256-byte aligned
+constexpr int SPILL_MAX = 65536;         // candidate keys one series_flow CTA may spill to global scratch
+// counters + the two work lists, rounded so that the spill space behind them is 256-byte aligned.  A list has room
+// for KO_MAX_QUANTILES entries per series: the first attempt of series_flow defers single quantiles.
+constexpr int LIST_PER_SERIES = KO_MAX_QUANTILES;
 constexpr size_t series_lists_bytes(int64_t n_series) {
-    return ((size_t)(N_COUNTERS + 2 * n_series) * sizeof(int) + 255) / 256 * 256;
+    return ((size_t)(N_COUNTERS + 2 * LIST_PER_SERIES * n_series) * sizeof(int) + 255) / 256 * 256;
 }
 
 // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: remember which devices have been set up.
@@ -1350,6 +1352,9 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
     a.out_list = a.defer_list;
     a.out_cnt = 4;
     a.wide = 0;
+    // the first attempt defers single quantiles: up to KO_MAX_QUANTILES entries per series, and the list has room
+    // for n_series entries, so only when that cannot overflow
+    a.pack = (n_series < (1LL << 27)) ? 1 : 0;
     cudaError_t e;
     if (getenv("KO_DEBUG_FORCE_LONG")) {   // development: everything through the slow exact path
         a.work_cur = 7;
@@ -1403,7 +1408,7 @@ static int fill_args(SeriesArgs& a, const double* d_values, const int64_t* d_off
     a.out_quant = d_quant;
     a.counters = d_scratch;
     a.long_list = d_scratch + N_COUNTERS;
-    a.defer_list = d_scratch + N_COUNTERS + n_series;
+    a.defer_list = d_scratch + N_COUNTERS + LIST_PER_SERIES * n_series;
     a.nq = nq;
     // quantiles ascending (stable insertion sort), remembering the caller's column
     for (int j = 0; j < NI_MAX; ++j) {

@@ -29,6 +29,13 @@ def series_layout(cfg):
     return np.array(kinds, np.int8)
 
 
+def mix_kinds(config, n):
+    """``n`` series with the same proportions of kinds as the config (interleaved, not in blocks)."""
+    full = series_layout(CONFIGS[config] if isinstance(config, str) else config)
+    idx = (np.arange(n, dtype=np.int64) * len(full)) // max(n, 1)
+    return full[idx]
+
+
 def n_series(cfg):
     return 4 * cfg["nodes"] + 5 * cfg["nodes"] * cfg["gpus"] + 2 * cfg["pods"]
 
@@ -152,14 +159,15 @@ def make_nodes(seed, n_nodes, n_clusters=1, zero_frac=0.02, hot_frac=0.0):
     return dict(cpu=cpu, mem=mem, cpu_usage=cu, mem_usage=mu, cluster_of_node=cluster)
 
 
-def make_series_torch(config, seed, device, L=None, n_series_override=None):
+def make_series_torch(config, seed, device, L=None, n_series_override=None, kinds=None):
     """Full-size column generated ON THE GPU (torch) from the same distributions as make_series.
-    Returns (values tensor f64 [n*L], offsets tensor i64 [n+1], kinds ndarray)."""
+    Returns (values tensor f64 [n*L], offsets tensor i64 [n+1], kinds ndarray).  ``kinds`` replaces the
+    config's series layout (e.g. a shorter batch with the same mix of kinds)."""
     import torch
     cfg = dict(CONFIGS[config])
     if L is not None:
         cfg["L"] = L
-    kinds = series_layout(cfg)
+    kinds = series_layout(cfg) if kinds is None else np.asarray(kinds, np.int8)
     if n_series_override is not None:
         kinds = np.resize(kinds, n_series_override)
     n, L = len(kinds), cfg["L"]

@@ -80,7 +80,7 @@ if "parity" in what:
 
 if "speed" in what:
     for name, cfg, n in (("7-day c2", "c2", None), ("30-day c3 slice", "c3", 5920)):
-        vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", n_series_override=n)
+        vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", kinds=None if n is None else synth.mix_kinds(cfg, n))
         n = len(kinds)
         q = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
         s = torch.zeros(n, dtype=torch.float64, device="cuda")

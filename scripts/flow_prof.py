@@ -11,7 +11,8 @@ nq = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 iters = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 QS = [0.5, 0.95, 0.99][:nq]
 r = Rollup(0)
-vals, offs, kinds = synth.make_series_torch("c2" if L <= 40320 else "c3", 1, "cuda", L=L, n_series_override=n)
+cfg = "c2" if L <= 40320 else "c3"
+vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", L=L, kinds=synth.mix_kinds(cfg, n))
 q = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
 s = torch.zeros(n, dtype=torch.float64, device="cuda")
 for it in range(iters):

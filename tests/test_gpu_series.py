@@ -157,8 +157,8 @@ def test_few_distinct_values(rollup):
 
 
 def test_more_long_series_than_one_plan_window(rollup):
-    """20 000 long series: the plans are built in windows of 16 384 (the call reads back the number of long
-    series once), and the static entry point's window is 2 048."""
+    """20 000 long series (many per CTA of the persistent one-pass kernel, short ones: three stages each), and the
+    static entry point over 5 000 of them."""
     import torch
     from kubeoperator_b200 import korollup
     rng = np.random.default_rng(12)
@@ -170,7 +170,7 @@ def test_more_long_series_than_one_plan_window(rollup):
     got = rollup.series_rollup(values, offsets, QS)
     exp = c_oracle.series_rollup(values, offsets, QS, nthreads=8)
     assert_series_parity(got, exp, values, offsets, QS)
-    # the no-allocation entry point over 5 000 of them (three windows of 2 048)
+    # the no-allocation entry point over 5 000 of them
     m = 5000
     dv, do = torch.from_numpy(values[:m * L]).cuda(), torch.from_numpy(offsets[:m + 1]).cuda()
     qt = torch.zeros((m, 3), dtype=torch.float64, device="cuda")
@@ -183,13 +183,13 @@ def test_more_long_series_than_one_plan_window(rollup):
 
 
 def test_brackets_that_miss_overflow_or_are_skewed(rollup):
-    """Series built to defeat the pre-sample: the wanted ranks lie where the 1024 strided sample points say
-    nothing (second attempt with wide brackets, then the slow path), candidates pile up in one sub-bracket
-    (cut again), and three separate brackets at once."""
+    """Series built to defeat the pre-sample (1024 aligned runs of four samples, one every 40 samples here): the
+    wanted ranks lie where the sample points say nothing (second attempt with wide intervals, then the slow path),
+    candidates pile up in a sliver of the value range, and three separate intervals at once."""
     rng = np.random.default_rng(13)
-    L = 40960                                           # sample stride 40: positions 20, 60, 100, ...
+    L = 40960                                           # sample runs start at 20, 60, 100, ... (rounded to 4)
     idx = np.arange(L)
-    on_sample = (idx % 40) == 20
+    on_sample = ((idx // 4) % 10) == 5                  # the run of four that holds position 40 i + 20
     series = [
         np.where(on_sample, rng.random(L), 5.0 + rng.random(L)),          # the sample sees only the low 2.5 %
         np.where(on_sample, 5.0 + rng.random(L), rng.random(L)),          # ... only the high 2.5 %
@@ -209,13 +209,62 @@ def test_brackets_that_miss_overflow_or_are_skewed(rollup):
         assert_series_parity(got, exp, values, offsets, qs)
 
 
-def test_very_long_series_refinement_passes(rollup):
-    # 30 days at 15 s (config 3/4 length): the brackets do not fit shared memory -> histogram refinement
-    d = synth.make_series(dict(nodes=1, gpus=1, pods=1, L=172800), seed=6)
-    got = rollup.series_rollup(d["values"], d["offsets"], QS)
-    exp = c_oracle.series_rollup(d["values"], d["offsets"], QS, nthreads=8)
-    assert_series_parity(got, exp, d["values"], d["offsets"], QS)
-    assert rollup.counters()["series_fallback"] > 0
+def test_thirty_day_series_every_kind_one_pass(rollup):
+    """30 days at 15 s (config 3 / 4 length): every series kind, parity with the oracle, and the one-pass kernel
+    answers them itself -- none of them may need the exact multi-pass slow path."""
+    d = synth.make_series(dict(nodes=2, gpus=2, pods=3, L=172800), seed=6)
+    assert set(d["kinds"].tolist()) == {synth.KIND_GAUGE, synth.KIND_CONST, synth.KIND_COUNTER, synth.KIND_DISCRETE}
+    for qs in (QS, [0.5], [0.01, 0.25, 0.75, 0.999]):
+        got = rollup.series_rollup(d["values"], d["offsets"], qs)
+        exp = c_oracle.series_rollup(d["values"], d["offsets"], qs, nthreads=8)
+        assert_series_parity(got, exp, d["values"], d["offsets"], qs)
+    import torch
+    n = len(d["offsets"]) - 1
+    dv, do = torch.from_numpy(d["values"]).cuda(), torch.from_numpy(d["offsets"]).cuda()
+    qt = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
+    rollup.series_rollup_dev(dv.data_ptr(), do.data_ptr(), n, QS, 0, 0, 0, 0, 0, 0, qt.data_ptr(),
+                             torch.cuda.current_stream().cuda_stream)
+    st = rollup.series_status()
+    assert st["long_series"] == n and st["slow_path"] == 0 and st["error_flag"] == 0
+    assert st["second_attempt"] <= 2          # a 3-sigma interval misses its rank now and then
+
+
+def test_series_the_one_pass_kernel_must_defer(rollup):
+    """Series the pre-sample says nothing about (almost only stale samples; a spread below the resolution of the
+    32-bit high key) go to the exact slow path: same results, and the device says so."""
+    import torch
+    rng = np.random.default_rng(21)
+    L = 30000
+    a = rng.random(L)
+    a[rng.random(L) < 0.995] = np.nan                     # ~150 valid samples: the pre-sample sees a handful
+    b = 8589934592.0 + rng.integers(0, 1000, L).astype(np.float64)    # byte counts: equal high words, different values
+    c = rng.beta(2, 5, L)
+    values = np.concatenate([a, b, c])
+    offsets = np.array([0, L, 2 * L, 3 * L], np.int64)
+    got = rollup.series_rollup(values, offsets, QS)
+    exp = c_oracle.series_rollup(values, offsets, QS, nthreads=4)
+    assert_series_parity(got, exp, values, offsets, QS)
+    dv, do = torch.from_numpy(values).cuda(), torch.from_numpy(offsets).cuda()
+    qt = torch.zeros((3, 3), dtype=torch.float64, device="cuda")
+    rollup.series_rollup_dev(dv.data_ptr(), do.data_ptr(), 3, QS, 0, 0, 0, 0, 0, 0, qt.data_ptr(),
+                             torch.cuda.current_stream().cuda_stream)
+    st = rollup.series_status()
+    assert st["slow_path"] == 2 and st["error_flag"] == 0
+    assert np.array_equal(_bits(qt.cpu().numpy()), _bits(exp["quantiles"]))
+
+
+def test_device_error_flag_is_reported(rollup):
+    """ko_series_rollup_dev cannot look at device offsets on the host: a decreasing pair is skipped on the GPU and
+    ko_series_status reports it."""
+    import torch
+    values = torch.rand(5000, dtype=torch.float64, device="cuda")
+    offs = torch.tensor([0, 3000, 2000, 5000], dtype=torch.int64, device="cuda")
+    cnt = torch.full((3,), -1, dtype=torch.int64, device="cuda")
+    rollup.series_rollup_dev(values.data_ptr(), offs.data_ptr(), 3, [], 0, 0, 0, 0, 0, cnt.data_ptr(), 0,
+                             torch.cuda.current_stream().cuda_stream)
+    st = rollup.series_status()
+    assert st["error_flag"] != 0
+    assert cnt.cpu().tolist() == [3000, -1, 3000]          # the bad series is left untouched
 
 
 def test_short_windows_config5(rollup):
@@ -282,7 +331,8 @@ def test_counters_add_up_over_staged_chunks(rollup):
     vals, offs, _ = synth.make_series_torch("c2", 19, "cuda", n_series_override=n)
     body = vals.cpu().numpy()
     rng = np.random.default_rng(19)
-    long30 = rng.beta(2.0, 5.0, 172800)                  # ... behind one 30-day series the fast path must defer
+    long30 = rng.beta(2.0, 5.0, 172800)
+    long30[rng.random(172800) < 0.997] = np.nan          # ... behind one 30-day series the fast path must defer
     tail = rng.beta(2.0, 5.0, 12 * L)                    # and enough after them to open a second chunk
     values = np.concatenate([long30, body, tail])
     offsets = np.concatenate([[0], 172800 + offs.cpu().numpy(),
