@@ -1,16 +1,19 @@
 #!/usr/bin/env python
 """bench.py — samples/s rolled up by the monitoring-rollup hot path (BASELINE.json metric) on N B200.
 
-One "step" = one pass of the hot path over one batch of synthetic input: the window statistics + p50/p95/p99
-of every series of BASELINE.json configs[1] (100-node cluster incl. per-GPU DCGM series, 7 days at 15 s:
-10 400 series x 40 320 samples = 419 M samples, 3.35 GB) — per rank (weak scaling: series are sharded by ID,
-every rank owns one such shard) — followed, for N > 1, by the fleet-wide quantile merge (all-gather of key
-histograms over NCCL).
+One "step" = one pass of the hot path over one batch of synthetic input: window statistics + p50/p95/p99 of every
+series (ko_series_rollup_dev through the C ABI).
+  N = 1 : BASELINE.json configs[2] — 1 000 nodes x 30 pods, 30 days at 15 s: 64 000 series x 172 800 samples =
+          11.06 G samples, 88.5 GB resident in HBM (the largest single-GPU configuration).
+  N > 1 : BASELINE.json configs[3] — 10 000-node multi-cluster fleet, 30 days: 80 000 series x 172 800 samples
+          (110.6 GB) sharded by series ID on cluster boundaries over the N ranks (strong scaling: the fleet is fixed),
+          followed per step by the fleet-wide merges over NCCL (quantile by all-gathered key histograms, top-k, sums).
   value : device-resident (inputs in HBM), CUDA events on the launching stream, max over ranks.
-  e2e   : the same step through the host-pointer C-ABI call (ko_series_rollup: pinned host -> chunked H2D ->
-          kernels -> D2H results) plus the node / pod rollup of the config through the C ABI.
-  --impl reference : the oracle port (plain C, OpenMP, all host threads) on a bounded sample — the reference
-          itself is Python and has no range-window code, so the port is the CPU arm.
+  e2e   : the same rollup through the host-pointer C-ABI call (ko_series_rollup: pinned host -> chunked H2D ->
+          kernels -> D2H) over the largest slice of the workload that is pinned on the host (stated in the line),
+          plus the node / pod rollup of the config through the C ABI.
+  --impl reference : the CPU arm — the oracle port (plain C, OpenMP, all host threads) over a bounded slice of the
+          same workload; the reference itself is Python and has no range-window code.
 """
 import argparse
 import json
@@ -29,7 +32,18 @@ if ROOT not in sys.path:
 QS = [0.5, 0.95, 0.99]
 METRIC = "samples_per_sec_rolled_up"
 UNIT = "samples/s"
-BYTES_PER_SAMPLE = 8.0          # algorithmic bytes per f64 sample (SURVEY.md §8d, DESIGN.md)
+BYTES_PER_SAMPLE = 8.0          # algorithmic bytes per f64 sample (SURVEY.md 8d, DESIGN.md)
+CPU_SLICE_SERIES = 256          # series of the workload the CPU arm rolls up per step (both arms print it)
+SUM_RTOL = 1e-12
+
+
+def workload(world):
+    """(config name, description) of the bench workload at this number of GPUs."""
+    if world == 1:
+        return "c3", ("configs[2]: 1,000 nodes x 30 pods, 30 days at 15 s: dashboard aggregates + p50/p95/p99 "
+                      "(64,000 series x 172,800 samples, 88.5 GB in HBM)")
+    return "c4", ("configs[3]: 10,000-node multi-cluster fleet, 30 days at 15 s (80,000 series x 172,800 samples, "
+                  "110.6 GB) series-sharded on cluster boundaries over %d GPUs, NCCL fleet merges per step" % world)
 
 
 def measured_peak_gbs():
@@ -87,44 +101,55 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_port_baseline(values, offsets, target_seconds=12.0):
-    """The C oracle (all host threads) on a bounded sample of the workload; grows the sample until the run
-    takes about target_seconds."""
+def cpu_slice(config, seed=1, n=CPU_SLICE_SERIES):
+    """The bounded slice of the workload the CPU arm works on: n series with the workload's mix of kinds."""
+    from kubeoperator_b200 import synth
+    cfg = dict(synth.CONFIGS[config])
+    kinds = synth.mix_kinds(config, n)
+    rng = np.random.default_rng(seed)
+    L = cfg["L"]
+    values = np.empty(n * L, np.float64)
+    for i, k in enumerate(kinds):
+        values[i * L:(i + 1) * L] = synth._one_series(rng, int(k), L)
+    return values, np.arange(n + 1, dtype=np.int64) * L
+
+
+def time_cpu_port(values, offsets, target_seconds, min_reps=1):
     from oracle import c_oracle
     cores = os.cpu_count() or 1
-    n_total = len(offsets) - 1
-    n = min(n_total, 64)
+    c_oracle.series_rollup(values, offsets, QS, nthreads=cores)     # warm (page faults, thread pool)
     t0 = time.perf_counter()
-    c_oracle.series_rollup(values[:offsets[n]], offsets[:n + 1], QS, nthreads=cores)
-    dt = max(time.perf_counter() - t0, 1e-4)
-    n = int(min(n_total, max(64, n * target_seconds / dt)))
-    c_oracle.series_rollup(values[:offsets[n]], offsets[:n + 1], QS, nthreads=cores)   # warm (page faults, threads)
-    t0 = time.perf_counter()
-    c_oracle.series_rollup(values[:offsets[n]], offsets[:n + 1], QS, nthreads=cores)
+    c_oracle.series_rollup(values, offsets, QS, nthreads=cores)
     dt1 = max(time.perf_counter() - t0, 1e-4)
-    reps = int(max(1, min(200, round(target_seconds / dt1))))   # the whole workload is short on many cores: repeat it
+    reps = int(max(min_reps, min(500, round(target_seconds / dt1))))
     t0 = time.perf_counter()
     for _ in range(reps):
-        c_oracle.series_rollup(values[:offsets[n]], offsets[:n + 1], QS, nthreads=cores)
+        c_oracle.series_rollup(values, offsets, QS, nthreads=cores)
     dt = time.perf_counter() - t0
-    samples = int(offsets[n] - offsets[0])
-    return {"value": samples * reps / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": "%d series x %d samples of the same workload, %d passes (%.1f s of CPU work, C oracle "
-                      "oracle/korollup_oracle.c with OpenMP on %d threads; the reference has no range-window "
-                      "code, SURVEY.md 0.3)" % (n, samples // max(n, 1), reps, dt, cores)}
+    samples = int(offsets[-1] - offsets[0])
+    return samples * reps / dt, cores, reps, dt
+
+
+def cpu_port_baseline(config, target_seconds=12.0):
+    values, offsets = cpu_slice(config)
+    v, cores, reps, dt = time_cpu_port(values, offsets, target_seconds)
+    n = len(offsets) - 1
+    return {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d series x %d samples of the same workload (same mix of series kinds), %d passes (%.1f s of "
+                      "CPU work, C oracle oracle/korollup_oracle.c with OpenMP on %d threads; the reference has no "
+                      "range-window code, SURVEY.md 0.3)" % (n, int(offsets[1]), reps, dt, cores)}
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the oracle port on the host cores (rank 0 only)."""
+    """--impl reference: the oracle port on the host cores (rank 0 only), CPU_SLICE_SERIES series per step."""
     if rank != 0:
         return
-    from kubeoperator_b200 import synth
     from oracle import c_oracle
     c_oracle.build()
     cores = os.cpu_count() or 1
-    n = 256 if args.sample_series <= 0 else args.sample_series
-    d = synth.make_series("c2", seed=1, max_series=n)
-    values, offsets = d["values"], d["offsets"]
+    config, desc = workload(world)
+    values, offsets = cpu_slice(config)
+    n = len(offsets) - 1
     samples = int(offsets[-1])
     for _ in range(args.warmup):
         c_oracle.series_rollup(values, offsets, QS, nthreads=cores)
@@ -133,16 +158,166 @@ def run_reference(args, rank, world):
         c_oracle.series_rollup(values, offsets, QS, nthreads=cores)
     dt = time.perf_counter() - t0
     v = samples * args.steps / dt
-    sample = ("%d series x 40320 samples of configs[1] per step, C oracle port (oracle/korollup_oracle.c, OpenMP, "
-              "%d threads); the Python reference has no range-window implementation" % (n, cores))
+    sample = ("%d series x %d samples of the workload per step (same mix of series kinds), C oracle port "
+              "(oracle/korollup_oracle.c, OpenMP, %d threads); the Python reference has no range-window "
+              "implementation" % (n, int(offsets[1]), cores))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "configs[1]: 100-node cluster incl. per-GPU DCGM series, 7 d at 15 s; bounded sample",
-                   "series_per_step": n, "samples_per_series": 40320, "quantiles": QS},
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak" if world == 1 else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "cpu_slice_series": n, "samples_per_series": int(offsets[1]), "quantiles": QS},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float64).view(np.uint64)
+
+
+def check_against_oracle(values_np, offsets_np, got, qs):
+    """Outputs of a timed step against the C oracle on the same series: counts / min / max / last / quantiles
+    bit for bit, sums and means within 1e-12 of sum|x|.  Returns the number of mismatching series."""
+    from oracle import c_oracle
+    exp = c_oracle.series_rollup(values_np, offsets_np, qs, nthreads=min(16, os.cpu_count() or 1))
+    n = len(offsets_np) - 1
+    bad = np.zeros(n, bool)
+    bad |= got["count"] != exp["count"]
+    for k in ("min", "max", "last"):
+        both = np.isnan(got[k]) & np.isnan(exp[k])
+        bad |= (bits(got[k]) != bits(exp[k])) & ~both
+    both = np.isnan(got["quantiles"]) & np.isnan(exp["quantiles"])
+    bad |= ((bits(got["quantiles"]) != bits(exp["quantiles"])) & ~both).any(axis=1)
+    absum = np.array([np.nansum(np.abs(values_np[offsets_np[i]:offsets_np[i + 1]])) for i in range(n)])
+    with np.errstate(invalid="ignore"):
+        bad |= ~(np.abs(got["sum"] - exp["sum"]) <= SUM_RTOL * absum)
+        bad |= ~(np.abs(got["mean"] - exp["mean"]) <= SUM_RTOL * absum / np.maximum(exp["count"], 1))
+    return int(bad.sum())
+
+
+def reference_defined_rows(rollup, n_nodes, n_pods, repeats=5):
+    """the rows whose arithmetic the reference itself defines, GPU end to end (host buffers through
+    the C ABI) beside the line-for-line Python restatement (B0) and a NumPy version (B2).
+    a2 = ClusterMonitor.set_cluster_data loop (cluster_monitor.py:163-182); a4 + a5 = list_pods inner loop + the two
+    quick sorts (cluster_monitor.py:93-117, 450-463)."""
+    from kubeoperator_b200 import synth
+    from oracle import rollup_oracle as ro
+    sys.setrecursionlimit(max(sys.getrecursionlimit(), 200000))
+    out = {}
+    nd = synth.make_nodes(5, n_nodes, 1)
+    cl = np.zeros(n_nodes, np.int32)
+
+    def med(fn):
+        fn()
+        ts = []
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            fn()
+            ts.append(time.perf_counter() - t0)
+        return float(np.median(ts)) * 1e3
+
+    nodes = [dict(name="n%d" % i, status="Ready", cpu=float(nd["cpu"][i]), mem=float(nd["mem"][i]),
+                  cpu_usage=float(nd["cpu_usage"][i]), mem_usage=float(nd["mem_usage"][i])) for i in range(n_nodes)]
+    out["a2"] = {
+        "n_nodes": n_nodes,
+        "gpu_e2e_ms": med(lambda: rollup.cluster_rollup(nd["cpu"], nd["mem"], nd["cpu_usage"], nd["mem_usage"], cl, 1, 80.0)),
+        "python_ms": med(lambda: ro.set_cluster_data_numbers(nodes)),
+        "numpy_ms": med(lambda: (nd["cpu"].sum(), nd["mem"].sum(),
+                                 nd["cpu_usage"].sum() / max(1, n_nodes - int(((nd["cpu_usage"] == 0) & (nd["mem_usage"] == 0)).sum())),
+                                 (nd["cpu_usage"] > 80) | (nd["mem_usage"] > 80)))}
+    pods = synth.make_pods(6, n_pods)
+
+    def py_pods():
+        restart = [int(pods["container_restart"][pods["pod_offsets"][i]:pods["pod_offsets"][i + 1]].sum())
+                   for i in range(n_pods)]
+        members = [dict(name=i, restart_count=r) for i, r in enumerate(restart) if r > 0]
+        return ro.quick_sort_pods(members)
+
+    def np_pods():
+        restart = np.add.reduceat(pods["container_restart"], pods["pod_offsets"][:-1])
+        idx = np.flatnonzero(restart > 0)
+        return idx[np.argsort(-restart[idx], kind="stable")]
+
+    out["a4a5"] = {
+        "n_pods": n_pods, "n_containers": int(pods["pod_offsets"][-1]),
+        "gpu_e2e_ms": med(lambda: rollup.pod_rollup(pods["container_restart"], pods["container_ready"],
+                                                     pods["pod_offsets"], pods["pod_phase_ok"])),
+        "python_ms": med(py_pods), "numpy_ms": med(np_pods)}
+    return out
+
+
+def crossover_table(rollup, sizes=(1000, 16000, 256000, 1000000), lengths=(20, 240)):
+    """configs[4]: alert-rule threshold + window statistics sweep over short windows; GPU (device-resident and with
+    host buffers through the C ABI) beside the C port on all host threads and a NumPy version."""
+    import torch
+    from oracle import c_oracle
+    cores = os.cpu_count() or 1
+    rows = []
+    rng = np.random.default_rng(11)
+    for L in lengths:
+        for n in sizes:
+            values = rng.beta(2, 5, n * L)
+            values[rng.random(n * L) < 1e-3] = np.nan
+            offsets = np.arange(n + 1, dtype=np.int64) * L
+            dv, do = torch.from_numpy(values).cuda(), torch.from_numpy(offsets).cuda()
+            outs = [torch.zeros(n, dtype=torch.float64, device="cuda") for _ in range(5)]
+            cnt = torch.zeros(n, dtype=torch.int64, device="cuda")
+            qt = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
+            st = torch.cuda.current_stream().cuda_stream
+
+            def dev():
+                rollup.series_rollup_dev(dv.data_ptr(), do.data_ptr(), n, QS, outs[0].data_ptr(), outs[1].data_ptr(),
+                                         outs[2].data_ptr(), outs[3].data_ptr(), outs[4].data_ptr(), cnt.data_ptr(),
+                                         qt.data_ptr(), st)
+            for _ in range(3):
+                dev()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                dev()
+            e1.record()
+            torch.cuda.synchronize()
+            gpu_dev_ms = e0.elapsed_time(e1) / 10
+
+            def host():
+                r = rollup.series_rollup(values, offsets, QS)
+                return (r["max"] > 0.8) | (r["mean"] > 0.6)           # the alert-rule threshold flags
+            host()
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                host()
+                ts.append(time.perf_counter() - t0)
+            gpu_host_ms = float(np.median(ts)) * 1e3
+            c_oracle.series_rollup(values, offsets, QS, nthreads=cores)
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                c_oracle.series_rollup(values, offsets, QS, nthreads=cores)
+                ts.append(time.perf_counter() - t0)
+            cpu_ms = float(np.median(ts)) * 1e3
+            m = values.reshape(n, L)
+
+            def np_version():
+                with np.errstate(invalid="ignore"):
+                    s = np.nansum(m, axis=1)
+                    c = (~np.isnan(m)).sum(axis=1)
+                    srt = np.sort(m, axis=1)                           # NaN sort last
+                    idx = np.clip(np.ceil(np.array(QS)[None, :] * c[:, None]).astype(np.int64) - 1, 0, L - 1)
+                    return s, c, np.nanmin(m, axis=1), np.nanmax(m, axis=1), np.take_along_axis(srt, idx, axis=1)
+            t0 = time.perf_counter()
+            np_version()
+            numpy_ms = (time.perf_counter() - t0) * 1e3
+            rows.append({"series": n, "window": L, "gpu_device_ms": gpu_dev_ms, "gpu_host_ms": gpu_host_ms,
+                         "cpu_port_ms": cpu_ms, "numpy_ms": numpy_ms})
+            del dv, do, outs, cnt, qt
+    cross = {}
+    for L in lengths:
+        win = [r["series"] for r in rows if r["window"] == L and r["gpu_host_ms"] < r["cpu_port_ms"]]
+        cross["window_%d" % L] = min(win) if win else None
+    return {"rows": rows, "cpu_threads": cores,
+            "gpu_wins_with_host_buffers_from_series": cross,
+            "what": "window statistics + p50/p95/p99 + threshold flags over n series of L samples (configs[4])"}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -158,40 +333,54 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     rollup = Rollup(local_rank)
-    cfg = synth.CONFIGS["c2"]
-    n_series = args.series if args.series > 0 else synth.n_series(cfg)
+    config, desc = workload(world)
+    cfg = synth.CONFIGS[config]
     L = cfg["L"]
-    d_values, d_offsets, kinds = synth.make_series_torch("c2", 1 + rank, dev,
-                                                         n_series_override=n_series if args.series > 0 else None)
+    per_node = cfg.get("per_node", 4)
+    total_series = synth.n_series(cfg)
+    if world == 1:
+        lo, hi = 0, total_series
+    else:   # contiguous series-ID ranges on cluster boundaries, balanced by sample count (equal lengths: by count)
+        nodes_per_cluster = cfg["nodes"] // cfg["clusters"]
+        weights = np.full(cfg["clusters"], nodes_per_cluster * per_node * L, np.int64)
+        c_lo, c_hi = fleet.shard_by_weight(weights, world)[rank]
+        lo, hi = c_lo * nodes_per_cluster * per_node, c_hi * nodes_per_cluster * per_node
+    kinds_all = synth.series_layout(cfg)
+    if args.series > 0:                                     # debug: a shorter batch with the same mix of kinds
+        kinds = synth.mix_kinds(config, args.series)
+        d_values, d_offsets, kinds = synth.make_series_torch(config, 1 + rank, dev, kinds=kinds)
+    else:
+        d_values, d_offsets, kinds = synth.make_series_torch(config, 1 + rank, dev, kinds=kinds_all[lo:hi],
+                                                             zero_nodes=False)
+        per = per_node if world > 1 else 4                  # 2 % of the nodes all-zero (cluster_monitor.py:174)
+        n_nodes_here = (hi - lo) // per if world > 1 else cfg["nodes"]
+        zr = np.random.default_rng(100 + rank).random(n_nodes_here) < 0.02
+        view = d_values.view(-1, L)
+        for node in np.flatnonzero(zr):
+            view[per * node] = 0.0
+            view[per * node + 3] = 0.0
     n_series = len(kinds)
     samples = n_series * L
     outs = {k: torch.zeros(n_series, dtype=torch.float64, device=dev) for k in ("sum", "mean", "min", "max", "last")}
     d_count = torch.zeros(n_series, dtype=torch.int64, device=dev)
     d_quant = torch.zeros((n_series, len(QS)), dtype=torch.float64, device=dev)
-    d_hist = torch.zeros(fleet.HIST_BINS, dtype=torch.int64, device=dev)
-    n_nodes = min(cfg["nodes"], n_series // 4)
-    node_idx = torch.arange(0, 4 * n_nodes, 4, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    fleet_q = [None]
-    fleet_ws = {}
+    fleet_out, fleet_ws = {}, {}
     fleet_rollup = Rollup(local_rank) if world > 1 else None   # own context: keeps the kernel timers of `rollup`
 
     def step_dev():
         rollup.series_rollup_dev(d_values.data_ptr(), d_offsets.data_ptr(), n_series, QS, outs["sum"].data_ptr(),
                                  outs["mean"].data_ptr(), outs["min"].data_ptr(), outs["max"].data_ptr(),
                                  outs["last"].data_ptr(), d_count.data_ptr(), d_quant.data_ptr(), stream)
-        if world > 1:   # fleet-wide p95 of the per-node mean CPU usage
-            node_vals = outs["mean"].index_select(0, node_idx)
-            if n_nodes <= fleet.SMALL_FLEET_CAP:     # few values: one all-gather, select on the GPU, no read-back
-                fleet_q[0] = fleet.fleet_quantile_device(node_vals, 0.95, n_nodes, fleet_rollup, dist, fleet_ws)
-            else:                                    # histogram all-gather, refined 16 bits per round
-                nv = int((node_vals == node_vals).sum().item())
-
-                def hist_fn(shift, mask, prefix):
-                    rollup.key_histogram_dev(node_vals.data_ptr(), node_vals.numel(), shift, mask, prefix,
-                                             d_hist.data_ptr(), stream)
-                    return d_hist
-                fleet_q[0] = fleet.fleet_quantile(hist_fn, nv, 0.95, dist, dev)
+        if world > 1:
+            # fleet-wide merges over NCCL, all on the device, nothing read back inside the step: p95 / p99
+            # over all per-series p95 values by all-reduced key histograms (16 bits per round, digit selection by a
+            # one-CTA kernel), top-10 of the per-series maxima, sums of the additive scalars
+            fleet_out["p95_p99_of_series_p95"] = fleet.fleet_quantiles_device(d_quant[:, 1], [0.95, 0.99], fleet_rollup,
+                                                                              dist, fleet_ws)
+            fleet_out["top10_series_max"] = fleet.fleet_topk_device(outs["max"], lo, 10, dist)
+            fleet_out["sum_and_count"] = fleet.fleet_scalars_device(
+                torch.stack([outs["sum"].nansum(), d_count.sum().double()]), dist)
 
     def sync_all():
         if world > 1:
@@ -219,53 +408,83 @@ def run_ours(args, rank, world, local_rank):
     ms_total = float(ms.item())
     c1 = rollup.counters()
     launches = c1["kernel_launches"] - c0["kernel_launches"]
-    value = world * samples * args.steps / (ms_total * 1e-3)
+    tot = torch.tensor([float(samples)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    value = float(tot.item()) * args.steps / (ms_total * 1e-3)
+    status = rollup.series_status()
 
-    # ---------------- dominant kernel (series_pipe, plus series_long over the deferred series), CUDA events on its stream inside the library
+    # ---------------- parity of the timed step's outputs: a sample of series of every kind against the C oracle
+    pick = np.unique(np.concatenate([np.flatnonzero(kinds == k)[:24] for k in range(4)] +
+                                    [np.linspace(0, n_series - 1, 16).astype(np.int64)]))
+    host_vals = np.concatenate([d_values[i * L:(i + 1) * L].cpu().numpy() for i in pick])
+    host_offs = np.arange(len(pick) + 1, dtype=np.int64) * L
+    pt = torch.from_numpy(pick).to(dev)
+    got = {k: outs[k][pt].cpu().numpy() for k in outs}
+    got["count"] = d_count[pt].cpu().numpy()
+    got["quantiles"] = d_quant[pt].cpu().numpy()
+    n_bad = check_against_oracle(host_vals, host_offs, got, QS)
+    parity = torch.tensor([float(len(pick)), float(n_bad)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(parity)
+    if parity[1].item() > 0:
+        raise SystemExit("bench.py: %d of %d checked series differ from the oracle" % (int(parity[1].item()),
+                                                                                         int(parity[0].item())))
+
+    # ---------------- dominant kernel (series_flow, first launch), CUDA events on its stream inside the library
     kms, pms = [], []
     for _ in range(5):
-        step_dev()
+        rollup.series_rollup_dev(d_values.data_ptr(), d_offsets.data_ptr(), n_series, QS, outs["sum"].data_ptr(),
+                                 outs["mean"].data_ptr(), outs["min"].data_ptr(), outs["max"].data_ptr(),
+                                 outs["last"].data_ptr(), d_count.data_ptr(), d_quant.data_ptr(), stream)
         kms.append(rollup.last_series_kernel_ms())
         pms.append(rollup.last_series_pipe_ms())
-    k_ms = float(np.mean(kms))      # series_plan + series_pipe + second attempt + series_long
-    p_ms = float(np.mean(pms))      # series_pipe alone: the dominant kernel
+    k_ms = float(np.mean(kms))      # series_flow + second attempt + series_long
+    p_ms = float(np.mean(pms))      # series_flow (first launch) alone: the dominant kernel
     peak, peak_src = measured_peak_gbs()
     achieved = BYTES_PER_SAMPLE * samples / (p_ms * 1e-3) / 1e9
     achieved_all = BYTES_PER_SAMPLE * samples / (k_ms * 1e-3) / 1e9
-    traffic = None
+    step_ms = ms_total / args.steps
+    traffic = traffic_src = None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
+            tj = json.load(f)
+            traffic_ratio = tj.get("dram_bytes_per_algorithmic_byte")
+            traffic = traffic_ratio * BYTES_PER_SAMPLE * samples if traffic_ratio else None
+            traffic_src = tj.get("source")
     except Exception:
         pass
 
-    # ---------------- end to end through the host-pointer C ABI
-    host = torch.empty(samples, dtype=torch.float64, pin_memory=True)
-    host.copy_(d_values)
+    # ---------------- end to end through the host-pointer C ABI: the largest slice we pin on the host
+    e2e_series = min(n_series, args.e2e_series)
+    host = torch.empty(e2e_series * L, dtype=torch.float64, pin_memory=True)
+    host.copy_(d_values[:e2e_series * L])
     torch.cuda.synchronize()
     h_values = host.numpy()
-    h_offsets = d_offsets.cpu().numpy()
-    pods = synth.make_pods(7 + rank, cfg["pods"])
+    h_offsets = np.arange(e2e_series + 1, dtype=np.int64) * L
+    e2e_samples = e2e_series * L
+    n_nodes = min(cfg["nodes"], 1000)
+    pods = synth.make_pods(7 + rank, max(cfg["pods"], 30000))
+    nodes = synth.make_nodes(8 + rank, n_nodes, 1)
     cluster_of_node = np.zeros(n_nodes, np.int32)
 
     def step_e2e():
         r = rollup.series_rollup(h_values, h_offsets, QS)
-        last = np.nan_to_num(r["last"][:4 * n_nodes])
-        c = rollup.cluster_rollup(last[1::4], last[2::4], last[0::4], last[3::4], cluster_of_node, 1, 80.0)
+        c = rollup.cluster_rollup(nodes["cpu"], nodes["mem"], nodes["cpu_usage"], nodes["mem_usage"], cluster_of_node,
+                                  1, 80.0)
         p = rollup.pod_rollup(pods["container_restart"], pods["container_ready"], pods["pod_offsets"],
                               pods["pod_phase_ok"])
         return r, c, p
 
-    for _ in range(2):
-        step_e2e()
-    e2e_steps = max(3, min(args.steps, 10))
+    step_e2e()
+    e2e_steps = max(3, min(args.steps, 5))
     sync_all()
     c0 = rollup.counters()
     times = []
     t_begin = time.perf_counter()
     for _ in range(e2e_steps):
         t0 = time.perf_counter()
-        step_e2e()
+        r_e2e = step_e2e()[0]
         times.append(time.perf_counter() - t0)
     sync_all()
     t_total = time.perf_counter() - t_begin
@@ -274,42 +493,62 @@ def run_ours(args, rank, world, local_rank):
     tt = torch.tensor([t_total], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    e2e_value = world * samples * e2e_steps / float(tt.item())
+    e2e_value = world * e2e_samples * e2e_steps / float(tt.item())
+    # the host-pointer path must give what the device-pointer path gave for the same series
+    same = bool(np.array_equal(bits(r_e2e["quantiles"]), bits(d_quant[:e2e_series].cpu().numpy())) and
+                np.array_equal(r_e2e["count"], d_count[:e2e_series].cpu().numpy()))
+    if not same:
+        raise SystemExit("bench.py: host-pointer and device-pointer rollups disagree")
 
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "configs[1]: 100-node cluster incl. per-GPU DCGM series, 7 d at 15 s "
-                                   "(per rank; series sharded by ID)",
-                       "series_per_rank": n_series, "samples_per_series": L, "samples_per_rank": samples,
+            "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True,
+            "scaling": "weak" if world == 1 else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "cpu_slice_series": CPU_SLICE_SERIES,
+                       "series_this_rank": n_series, "samples_per_series": L, "samples_this_rank": samples,
                        "quantiles": QS, "stats": ["sum", "mean", "min", "max", "last", "count"],
-                       "l2": "inputs (%.2f GB per rank) are larger than the 126 MB L2; no flush needed" % (samples * 8 / 1e9),
-                       "multi_gpu": "fleet p95 of per-node mean CPU usage: one NCCL all-gather of the per-node means, selected on the GPU (histogram rounds above 65536 nodes per rank)"
+                       "l2": "inputs (%.1f GB per rank) are larger than the 126 MB L2; no flush needed" % (samples * 8 / 1e9),
+                       "multi_gpu": ("series sharded by ID on cluster boundaries (fleet.shard_by_weight), no collective "
+                                     "on the data path; per step over NCCL: fleet p95 / p99 of the per-series p95 by "
+                                     "all-gathered 65536-bin key histograms, top-10 series maxima, fleet sums")
                                     if world > 1 else "none (N=1: no NCCL)",
-                       "data_gen": "torch on device, distributions of kubeoperator_b200/synth.py"},
+                       "data_gen": "torch on device, float64, distributions of kubeoperator_b200/synth.py "
+                                   "(gauges, constants, counters with resets, stale NaN, all-zero nodes)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "kernel": "series_pipe",
-                         "kernel_ms": p_ms, "algorithmic_bytes_per_launch": BYTES_PER_SAMPLE * samples,
-                         "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "kernel": "series_flow", "kernel_ms": p_ms,
+                         "algorithmic_bytes_per_launch": BYTES_PER_SAMPLE * samples, "peak_source": peak_src,
                          "all_long_series_kernels": {
-                             "what": "series_plan + series_pipe + second attempt + series_long (the whole step "
-                                     "but classify_series / series_small)",
-                             "ms": k_ms, "achieved": achieved_all, "frac": achieved_all / peak}},
+                             "what": "series_flow + its second attempt + series_long", "ms": k_ms,
+                             "achieved": achieved_all, "frac": achieved_all / peak},
+                         "step": {"ms": step_ms, "achieved": BYTES_PER_SAMPLE * samples / (step_ms * 1e-3) / 1e9,
+                                  "frac": BYTES_PER_SAMPLE * samples / (step_ms * 1e-3) / 1e9 / peak}},
             "e2e": {"value": e2e_value, "unit": UNIT,
                     "h2d_bytes_per_step": (c1e["h2d_bytes"] - c0["h2d_bytes"]) // e2e_steps,
                     "d2h_bytes_per_step": (c1e["d2h_bytes"] - c0["d2h_bytes"]) // e2e_steps,
                     "p50_ms": float(np.median(times)) * 1e3, "steps": e2e_steps,
-                    "includes": "ko_series_rollup (pinned host -> H2D -> kernels -> D2H) + ko_cluster_rollup + "
-                                "ko_pod_rollup through the C ABI"},
+                    "includes": "ko_series_rollup (pinned host -> H2D -> kernels -> D2H) over the first %d series of "
+                                "the workload (%.1f GB: the slice pinned on the host; the rate does not depend on the "
+                                "slice) + ko_cluster_rollup (%d nodes) + ko_pod_rollup (%d pods) through the C ABI"
+                                % (e2e_series, e2e_samples * 8 / 1e9, n_nodes, len(pods["pod_phase_ok"]))},
             "gpu_launches": int(launches), "clocks": clocks,
-            "series_needing_extra_pass": int(c1e["series_fallback"]),
+            "series_needing_extra_pass": int(status["second_attempt"]),
+            "series_on_slow_path": int(status["slow_path"]),
+            "parity_checked_series": int(parity[0].item()),
+            "parity_pin": "build-defined (window statistics / nearest-rank quantiles: the oracle is the specification; "
+                          "reference-defined rows are pinned by tests/golden)",
         }
         if world > 1:
-            line["fleet_p95_node_cpu_mean"] = float(fleet_q[0].item()) if hasattr(fleet_q[0], "item") else fleet_q[0]
+            line["fleet"] = {k: ([x.tolist() for x in v] if isinstance(v, tuple) else v.tolist())
+                             for k, v in fleet_out.items()}
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_port_baseline(h_values, h_offsets)
+            line["cpu_baseline"] = cpu_port_baseline(config)
+            if not args.quick:
+                line["reference_defined"] = {
+                    "config_size": reference_defined_rows(rollup, 1000, 30000),
+                    "fleet_size": reference_defined_rows(rollup, 10000, 300000, repeats=1)}
+                line["crossover"] = crossover_table(rollup)
         else:
             line["cpu_baseline"] = None
         print(json.dumps(line))
@@ -324,12 +563,13 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--series", type=int, default=0, help="override the number of series per rank (debug)")
-    ap.add_argument("--sample-series", type=int, default=0, help="series per step of --impl reference")
+    ap.add_argument("--series", type=int, default=0, help="debug: a shorter batch with the same mix of series kinds")
+    ap.add_argument("--e2e-series", type=int, default=8192, help="series of the workload pinned on the host for e2e")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="skip the reference-defined rows and the crossover table")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

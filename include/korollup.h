@@ -157,10 +157,11 @@ int ko_available_rate(ko_ctx* ctx, const int32_t* job_up, const int32_t* job_len
 
 /* ---- a11: fleet roll-up the browser performs ------------------------------------------------------------
  * Replaces DashboardComponent.getClusterData, ui/src/app/dashboard/dashboard.component.ts:117-153.
- * counts is [n_clusters][5] = pods, namespaces, deployments, containers, nodes; max_pods[c] <= 0 means
- * "undefined" (-> 110, :138-141).  out[12] = pod_count, namespace_count, deployment_count,
- * container_count, node_count, cpu_total, mem_total, cpu_usage(%), mem_usage(%), max_pod_count,
- * container_usage(%), count. */
+ * counts is [n_clusters][6] = pods, namespaces, deployments, containers, nodes (all of the cluster's blob), and
+ * ui_nodes = cluster.nodes.length of the UI's own cluster list, or -1 when that list does not hold the cluster (it then
+ * adds no pod capacity, :136-143).  max_pods[c] < 0 means MAX_PODS === undefined (-> 110, :138-141); 0 is a configured
+ * zero.  out[12] = pod_count, namespace_count, deployment_count, container_count, node_count, cpu_total, mem_total,
+ * cpu_usage(%), mem_usage(%), max_pod_count, container_usage(%), count. */
 int ko_fleet_rollup(ko_ctx* ctx, const int64_t* counts, const double* cpu_total,
                     const double* mem_total, const double* cpu_usage, const double* mem_usage,
                     const int32_t* max_pods, int64_t n_clusters, double* out);
@@ -174,6 +175,17 @@ int ko_key_histogram(ko_ctx* ctx, const double* values, int64_t n, int shift, ui
                      uint64_t prefix, int64_t* out_hist);
 int ko_key_histogram_dev(ko_ctx* ctx, const double* d_values, int64_t n, int shift,
                          uint64_t prefix_mask, uint64_t prefix, int64_t* d_out_hist, void* stream);
+
+/* The same round with the refinement state in DEVICE memory, so that the four rounds of a fleet quantile follow each
+ * other on the stream without a trip to the host: ko_key_histogram_state_dev (local histogram under the state's
+ * prefix), an all-reduce of the 65536 bins across the ranks (NCCL, by the caller), ko_key_select_dev (one CTA finds the
+ * digit holding the wanted rank and updates the state).  d_state points to 32 bytes: {uint64 prefix, uint64 mask,
+ * int64 rank (1-based; < 1: no valid value), double result}; start with prefix = mask = 0 and
+ * rank = clamp(ceil(q * n_valid_total), 1, n_valid_total); after the round with shift 0 `result` holds the exact
+ * nearest-rank quantile (NaN when the fleet has no valid value).  BUILD-DEFINED, no counterpart in the reference. */
+int ko_key_histogram_state_dev(ko_ctx* ctx, const double* d_values, int64_t n, int shift, const void* d_state,
+                               int64_t* d_out_hist, void* stream);
+int ko_key_select_dev(ko_ctx* ctx, const int64_t* d_hist, int shift, void* d_state, void* stream);
 
 /* ---- a6: Loki error-line count ------------------------------------------------------
  * Replaces the scan of PrometheusClient.get_msg_from_loki, prometheus_client.py:140-146: per container

@@ -115,10 +115,12 @@ def count_loki_errors(names, lines_by_name, cluster_name, rollup=None):
 class ClusterRollup:
     """Arithmetic of ``ClusterMonitor`` for one cluster; collectors are passed in by the caller."""
 
-    def __init__(self, cluster_name, cluster_id="", token="", rollup=None, threshold=80, alert_sink=None):
+    def __init__(self, cluster_name, cluster_id="", token="", rollup=None, threshold=80, alert_sink=None,
+                 item_id=None, item_name=None, status=None):
         self.cluster_name = cluster_name
         self.cluster_id = cluster_id
         self.token = token
+        self.item_id, self.item_name, self.status = item_id, item_name, status   # cluster.item_id / item_name / status
         self.rollup = rollup or get_rollup()
         self.threshold = threshold
         self.alert_sink = alert_sink
@@ -186,11 +188,18 @@ class ClusterRollup:
         return (float(out["cpu_usage"][0]), float(out["cpu_total"][0]), float(out["mem_usage"][0]),
                 float(out["mem_total"][0]))
 
+    def get_usage_content(self, node):
+        """``ClusterMonitor.get_usage_content`` (cluster_monitor.py:433-442), same keys in the same order; ``node``
+        is the node's dict (the reference serialises ``node.__dict__`` of cluster_data.py:47-55)."""
+        return {"item_name": self.item_name, "resource": "集群", "resource_name": self.cluster_name,
+                "resource_type": "CLUSTER_USAGE", "detail": json.dumps(node), "status": self.status}
+
     def get_usage_message(self, node):
-        """The message the reference meant to send (cluster_monitor.py:423-442, never called there)."""
-        return {"title": "集群资源告警", "level": "WARNING", "type": "CLUSTER",
-                "content": {"resource": "集群", "resource_name": self.cluster_name,
-                            "resource_type": "CLUSTER_USAGE", "detail": json.dumps(node)}}
+        """``ClusterMonitor.get_usage_message`` (cluster_monitor.py:423-431) with the content of
+        ``get_usage_content``: the reference passes the node to ``get_event_content`` there (:427), which labels a
+        usage alert CLUSTER_EVENT; get_usage_content exists for exactly this message and is what is used here."""
+        return {"item_id": self.item_id, "title": "集群资源告警", "content": self.get_usage_content(node),
+                "level": "WARNING", "type": "CLUSTER"}
 
     def set_cluster_data(self, nodes, pods, namespaces, deployments):
         """Returns the dict the reference serialises into Redis at cluster_monitor.py:186-192.  ``pods`` is the
@@ -225,27 +234,18 @@ def dashboard_merge(cluster_blobs, rollup=None):
 
 
 def fleet_rollup(cluster_blobs, max_pods_by_name=None, nodes_by_name=None, rollup=None):
-    """dashboard.component.ts:117-153 over parsed blobs.  ``max_pods_by_name`` = cluster.configs['MAX_PODS'],
-    ``nodes_by_name`` = len(cluster.nodes) of the cluster list the UI holds (:136-143); clusters missing from
-    the maps contribute no pod capacity, as in the UI loop."""
+    """dashboard.component.ts:117-153 over parsed blobs.  ``max_pods_by_name`` = cluster.configs['MAX_PODS'] of
+    the clusters that configure it (a missing name = undefined -> 110; 0 is a configured zero), ``nodes_by_name`` =
+    len(cluster.nodes) of the cluster list the UI holds (:136-143); a cluster missing from that list adds no pod
+    capacity, as in the UI loop.  Without ``nodes_by_name`` every blob's own node count is used."""
     rollup = rollup or get_rollup()
     max_pods_by_name = max_pods_by_name or {}
     counts, cols, mp = [], [[], [], [], []], []
-    extra_capacity = []
     for d in cluster_blobs:
-        known = nodes_by_name is None or d["name"] in nodes_by_name
-        n_nodes_ui = len(d["nodes"]) if nodes_by_name is None else nodes_by_name.get(d["name"], 0)
+        ui_nodes = len(d["nodes"]) if nodes_by_name is None else nodes_by_name.get(d["name"], -1)
         counts.append([len(d["pods"]), len(d["namespaces"]), len(d["deployments"]),
-                       sum(len(p["containers"]) for p in d["pods"]), len(d["nodes"])])
+                       sum(len(p["containers"]) for p in d["pods"]), len(d["nodes"]), int(ui_nodes)])
         for c, k in zip(cols, ("cpu_total", "mem_total", "cpu_usage", "mem_usage")):
             c.append(float(d[k]))
-        m = max_pods_by_name.get(d["name"])
-        mp.append(int(m) if m else 0)
-        extra_capacity.append((n_nodes_ui - len(d["nodes"])) * (int(m) if m else 110) if known else
-                              -len(d["nodes"]) * (int(m) if m else 110))
-    out = rollup.fleet_rollup(counts, cols[0], cols[1], cols[2], cols[3], mp)
-    adj = sum(extra_capacity)
-    if adj:   # the UI multiplies by the node count of ITS cluster list, which may differ from the blob's
-        out["max_pod_count"] += adj
-        out["container_usage"] = (out["pod_count"] / out["max_pod_count"] * 100) if out["max_pod_count"] > 0 else 0
-    return out
+        mp.append(max_pods_by_name.get(d["name"]))
+    return rollup.fleet_rollup(counts, cols[0], cols[1], cols[2], cols[3], mp)

@@ -110,18 +110,21 @@ __global__ void fleet_rollup_kernel(const int64_t* __restrict__ counts, const do
     long long pods = 0, ns = 0, dep = 0, cont = 0, nodes = 0, maxpod = 0, zero = 0;
     double ct = 0, mt = 0, cu = 0, mu = 0;
     for (int64_t c = lane; c < n; c += 32) {
-        pods += counts[c * 5 + 0];
-        ns += counts[c * 5 + 1];
-        dep += counts[c * 5 + 2];
-        cont += counts[c * 5 + 3];
-        nodes += counts[c * 5 + 4];
+        pods += counts[c * 6 + 0];
+        ns += counts[c * 6 + 1];
+        dep += counts[c * 6 + 2];
+        cont += counts[c * 6 + 3];
+        nodes += counts[c * 6 + 4];
         ct += cpu_total[c];
         mt += mem_total[c];
         cu += cpu_usage[c];
         mu += mem_usage[c];
         zero += (cpu_total[c] == 0.0 && mem_total[c] == 0.0) ? 1 : 0;
-        const long long mp = max_pods[c] > 0 ? max_pods[c] : 110;
-        maxpod += mp * counts[c * 5 + 4];
+        // :136-143: only a cluster the UI's own list knows adds capacity (ui_nodes >= 0 = cluster.nodes.length);
+        // MAX_PODS === undefined (passed as a negative value) means 110, a configured 0 stays 0
+        const long long ui_nodes = counts[c * 6 + 5];
+        const long long mp = max_pods[c] >= 0 ? max_pods[c] : 110;
+        if (ui_nodes >= 0) maxpod += mp * ui_nodes;
     }
     pods = wsum_ll(pods); ns = wsum_ll(ns); dep = wsum_ll(dep); cont = wsum_ll(cont);
     nodes = wsum_ll(nodes); maxpod = wsum_ll(maxpod); zero = wsum_ll(zero);
@@ -165,6 +168,70 @@ __global__ void key_hist_kernel(const double* __restrict__ v, int64_t n, int shi
             const unsigned long long k = ko_okey(x + 0.0);
             if ((k & pmask) == prefix) atomicAdd(&hist[(k >> shift) & 0xFFFFull], 1ull);
         }
+    }
+}
+
+// The same with the refinement state (prefix, mask, wanted rank, result) in device memory, so that the rounds of a
+// fleet quantile follow each other on the stream without a trip to the host: histogram -> all-reduce -> select.
+struct KoSelState {
+    unsigned long long prefix, mask;
+    long long rank;      // 1-based rank still wanted inside the prefix; < 1: no valid value in the fleet
+    double result;       // set by the round with shift == 0 (NaN when there is no value)
+};
+__global__ void key_hist_state_kernel(const double* __restrict__ v, int64_t n, int shift, const KoSelState* st,
+                                      unsigned long long* hist) {
+    const unsigned long long pmask = st->mask, prefix = st->prefix;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double x = v[i];
+        if (x == x) {
+            const unsigned long long k = ko_okey(x + 0.0);
+            if ((k & pmask) == prefix) atomicAdd(&hist[(k >> shift) & 0xFFFFull], 1ull);
+        }
+    }
+}
+// One CTA of 1024 threads: the digit whose cumulative count first reaches the wanted rank (64 bins per thread).
+__global__ void __launch_bounds__(1024) key_select_kernel(const unsigned long long* __restrict__ hist, int shift,
+                                                          KoSelState* st) {
+    __shared__ unsigned long long wsum[32];
+    __shared__ int found;
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const long long rank = st->rank;
+    unsigned long long s = 0;
+    for (int i = 0; i < 64; ++i) s += hist[t * 64 + i];
+    unsigned long long incl = s;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += u;
+    }
+    if (lane == 31) wsum[w] = incl;
+    if (t == 0) found = 0;
+    __syncthreads();
+    unsigned long long before_w = 0;
+    for (int i = 0; i < w; ++i) before_w += wsum[i];
+    incl += before_w;
+    const unsigned long long excl = incl - s;
+    if (rank >= 1 && excl < (unsigned long long)rank && (unsigned long long)rank <= incl) {
+        unsigned long long run = excl;
+        int d = 63;
+        for (int i = 0; i < 64; ++i) {
+            const unsigned long long h = hist[t * 64 + i];
+            if (run + h >= (unsigned long long)rank) {
+                d = i;
+                break;
+            }
+            run += h;
+        }
+        const unsigned long long digit = (unsigned long long)(t * 64 + d);
+        st->prefix |= digit << shift;
+        st->mask |= 0xFFFFull << shift;
+        st->rank = rank - (long long)run;
+        if (shift == 0) st->result = ko_key2d(st->prefix) + 0.0;
+        found = 1;
+    }
+    __syncthreads();
+    if (t == 0 && !found) {   // no valid value anywhere (or an inconsistent rank): NaN, and stay that way
+        st->rank = 0;
+        st->result = __longlong_as_double(0x7FF8000000000000LL);
     }
 }
 
@@ -409,14 +476,10 @@ int ko_available_rate(ko_ctx* ctx, const int32_t* job_up, const int32_t* job_len
     return KO_OK;
 }
 
-int ko_key_histogram_dev(ko_ctx* ctx, const double* d_values, int64_t n, int shift, uint64_t prefix_mask,
-                         uint64_t prefix, int64_t* d_out_hist, void* stream) {
-    KO_REQUIRE(ctx && ctx->alive, "ko_key_histogram_dev: ctx not initialised");
-    KO_REQUIRE(n >= 0 && d_out_hist && (n == 0 || d_values), "ko_key_histogram_dev: bad argument");
-    KO_REQUIRE(shift >= 0 && shift <= 48, "ko_key_histogram_dev: shift must be 0..48");
-    std::lock_guard<std::mutex> lk(ctx->mu);
-    KO_CUDA(cudaSetDevice(ctx->device));
-    cudaStream_t st = (cudaStream_t)stream;
+// (unlocked part of ko_key_histogram_dev: the host-pointer call below holds the mutex across staging, launch and
+// read-back, as the header promises)
+static int key_histogram_launch(ko_ctx* ctx, const double* d_values, int64_t n, int shift, uint64_t prefix_mask,
+                                uint64_t prefix, int64_t* d_out_hist, cudaStream_t st) {
     KO_CUDA(cudaMemsetAsync(d_out_hist, 0, (size_t)KO_HIST_BINS * 8, st));
     if (n) {
         int64_t blocks = (n + 255) / 256;
@@ -429,26 +492,64 @@ int ko_key_histogram_dev(ko_ctx* ctx, const double* d_values, int64_t n, int shi
     return KO_OK;
 }
 
+int ko_key_histogram_dev(ko_ctx* ctx, const double* d_values, int64_t n, int shift, uint64_t prefix_mask,
+                         uint64_t prefix, int64_t* d_out_hist, void* stream) {
+    KO_REQUIRE(ctx && ctx->alive, "ko_key_histogram_dev: ctx not initialised");
+    KO_REQUIRE(n >= 0 && d_out_hist && (n == 0 || d_values), "ko_key_histogram_dev: bad argument");
+    KO_REQUIRE(shift >= 0 && shift <= 48, "ko_key_histogram_dev: shift must be 0..48");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_CUDA(cudaSetDevice(ctx->device));
+    return key_histogram_launch(ctx, d_values, n, shift, prefix_mask, prefix, d_out_hist, (cudaStream_t)stream);
+}
+
+int ko_key_histogram_state_dev(ko_ctx* ctx, const double* d_values, int64_t n, int shift, const void* d_state,
+                               int64_t* d_out_hist, void* stream) {
+    KO_REQUIRE(ctx && ctx->alive, "ko_key_histogram_state_dev: ctx not initialised");
+    KO_REQUIRE(n >= 0 && d_out_hist && d_state && (n == 0 || d_values), "ko_key_histogram_state_dev: bad argument");
+    KO_REQUIRE(shift >= 0 && shift <= 48, "ko_key_histogram_state_dev: shift must be 0..48");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    KO_CUDA(cudaMemsetAsync(d_out_hist, 0, (size_t)KO_HIST_BINS * 8, st));
+    if (n) {
+        int64_t blocks = (n + 255) / 256;
+        if (blocks > (int64_t)ctx->num_sms * 8) blocks = (int64_t)ctx->num_sms * 8;
+        key_hist_state_kernel<<<(unsigned)blocks, 256, 0, st>>>(d_values, n, shift, (const KoSelState*)d_state,
+                                                               (unsigned long long*)d_out_hist);
+        KO_CUDA(cudaGetLastError());
+        ctx->counters.kernel_launches += 1;
+    }
+    return KO_OK;
+}
+
+int ko_key_select_dev(ko_ctx* ctx, const int64_t* d_hist, int shift, void* d_state, void* stream) {
+    KO_REQUIRE(ctx && ctx->alive, "ko_key_select_dev: ctx not initialised");
+    KO_REQUIRE(d_hist && d_state, "ko_key_select_dev: bad argument");
+    KO_REQUIRE(shift >= 0 && shift <= 48, "ko_key_select_dev: shift must be 0..48");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_CUDA(cudaSetDevice(ctx->device));
+    key_select_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>((const unsigned long long*)d_hist, shift,
+                                                            (KoSelState*)d_state);
+    KO_CUDA(cudaGetLastError());
+    ctx->counters.kernel_launches += 1;
+    return KO_OK;
+}
+
 int ko_key_histogram(ko_ctx* ctx, const double* values, int64_t n, int shift, uint64_t prefix_mask,
                      uint64_t prefix, int64_t* out_hist) {
     KO_REQUIRE(ctx && ctx->alive, "ko_key_histogram: ctx not initialised");
     KO_REQUIRE(n >= 0 && out_hist && (n == 0 || values), "ko_key_histogram: bad argument");
-    double* d_v;
-    int64_t* d_h;
-    {
-        std::lock_guard<std::mutex> lk(ctx->mu);
-        KO_CUDA(cudaSetDevice(ctx->device));
-        int rc;
-        if ((rc = ko_buf_reserve(&ctx->in_small, (size_t)n * 8 + 256))) return rc;
-        if ((rc = ko_buf_reserve(&ctx->out_small, (size_t)KO_HIST_BINS * 8))) return rc;
-        d_v = (double*)ctx->in_small.p;
-        d_h = (int64_t*)ctx->out_small.p;
-        if (n) KO_CUDA(cudaMemcpyAsync(d_v, values, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
-        ctx->counters.h2d_bytes += n * 8;
-    }
-    int rc = ko_key_histogram_dev(ctx, d_v, n, shift, prefix_mask, prefix, d_h, ctx->stream);
-    if (rc) return rc;
-    std::lock_guard<std::mutex> lk(ctx->mu);
+    KO_REQUIRE(shift >= 0 && shift <= 48, "ko_key_histogram: shift must be 0..48");
+    std::lock_guard<std::mutex> lk(ctx->mu);   // one lock for staging, launch and read-back
+    KO_CUDA(cudaSetDevice(ctx->device));
+    int rc;
+    if ((rc = ko_buf_reserve(&ctx->in_small, (size_t)n * 8 + 256))) return rc;
+    if ((rc = ko_buf_reserve(&ctx->out_small, (size_t)KO_HIST_BINS * 8))) return rc;
+    double* d_v = (double*)ctx->in_small.p;
+    int64_t* d_h = (int64_t*)ctx->out_small.p;
+    if (n) KO_CUDA(cudaMemcpyAsync(d_v, values, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->counters.h2d_bytes += n * 8;
+    if ((rc = key_histogram_launch(ctx, d_v, n, shift, prefix_mask, prefix, d_h, ctx->stream))) return rc;
     KO_CUDA(cudaMemcpyAsync(out_hist, d_h, (size_t)KO_HIST_BINS * 8, cudaMemcpyDeviceToHost, ctx->stream));
     KO_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->counters.d2h_bytes += (int64_t)KO_HIST_BINS * 8;

@@ -52,7 +52,7 @@ constexpr int F_NSTAGES = F_NGROUPS * F_GS;
 constexpr int F_BG = 8;                        // groups of the bitmap ring (64 words each)
 constexpr int F_PF = 3;                        // groups asked into L2 ahead of the ring
 constexpr int F_ND = 4;                        // series slots (descriptor + plan + partials)
-constexpr int F_SMAX = 4096;                   // largest pre-sample
+constexpr int F_SMAX = 8192;                   // largest pre-sample (30-day series)
 constexpr int F_POOL = 7168;                   // candidate keys held in shared memory
 constexpr int F_NH = 8;                        // heavy tie levels per plan
 constexpr int F_LIST = 64;                     // candidates selected by direct rank counting
@@ -167,7 +167,7 @@ constexpr size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 constexpr size_t FO_RING = 0;
 constexpr size_t FO_POOL = FO_RING + (size_t)F_NSTAGES * F_STAGE_BYTES;
 constexpr size_t FO_HK = FO_POOL + (size_t)F_POOL * 8;
-constexpr size_t FO_HIST1 = FO_HK + (size_t)F_SMAX * 8;
+constexpr size_t FO_HIST1 = FO_HK + (size_t)F_SMAX * 4;
 constexpr size_t FO_CUM = FO_HIST1 + 256 * 4;
 constexpr size_t FO_HIST2 = FO_CUM + 272 * 4;
 constexpr size_t FO_LUT = FO_HIST2 + (size_t)F_NT * 256 * 4;
@@ -190,7 +190,7 @@ struct FlowSmem {
     unsigned char* base;
     __device__ __forceinline__ unsigned char* ring() const { return base + FO_RING; }
     __device__ __forceinline__ unsigned long long* pool() const { return reinterpret_cast<unsigned long long*>(base + FO_POOL); }
-    __device__ __forceinline__ unsigned long long* skeys() const { return reinterpret_cast<unsigned long long*>(base + FO_HK); }
+    __device__ __forceinline__ uint32_t* hkeys() const { return reinterpret_cast<uint32_t*>(base + FO_HK); }
     __device__ __forceinline__ unsigned* hist1() const { return reinterpret_cast<unsigned*>(base + FO_HIST1); }
     __device__ __forceinline__ unsigned* cum() const { return reinterpret_cast<unsigned*>(base + FO_CUM); }
     __device__ __forceinline__ unsigned* hist2() const { return reinterpret_cast<unsigned*>(base + FO_HIST2); }
@@ -307,11 +307,9 @@ __device__ __forceinline__ double ld_cg_f64(const double* p) {
     asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(p));
     return v;
 }
-// 16 bytes global -> shared without passing through registers (LDGSTS): the planner's gather
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+__device__ __forceinline__ void ld_v4f64(const double* p, double& x, double& y, double& z, double& w) {   // 32 bytes
+    asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(x), "=d"(y), "=d"(z), "=d"(w) : "l"(p));
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ void lds_v2u32(uint32_t addr, uint32_t& a, uint32_t& b) {
     asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
 }
@@ -413,40 +411,41 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
     const int qper = (nquad + NT - 1) / NT;   // runs of four per thread: 1 (a 256-point sample uses half the threads) .. 8
     const int per = S / NT;          // sample keys per thread in the histogram rounds
     const int lead4 = (int)((reinterpret_cast<uintptr_t>(v) >> 3) & 3u);
-    unsigned long long* sk = sm.skeys();
+    uint32_t* sk = sm.hkeys();
     plan_sync();
-    // ---- gather: all 32-byte loads of a thread in flight together, raw bits to shared memory; then a compact loop
-    // turns the thread's own entries into order-preserving 64-bit keys (code size matters more than ILP here: the
-    // serial roles run through their code once per series and live on instruction-cache misses otherwise)
+    // ---- gather: four 32-byte loads of a thread in flight together; the high keys go to shared memory (that is all
+    // the histogram rounds need), the exact extremes are kept as 64-bit keys on the way
     {
         unsigned long long kmn = ~0ull, kmx = 0ull;
         unsigned nv = 0;
-        {
-            const uint32_t sk32 = smem_u32(sk);
 #pragma unroll 1
-            for (int u = 0; u < qper; ++u) {
-                const int j = ptid + u * NT;
-                if (j < nquad) {
-                    const double* src = v + quad_pos(j, L, nquad, lead4);
-                    cp_async16(sk32 + (uint32_t)j * 32u, src);
-                    cp_async16(sk32 + (uint32_t)j * 32u + 16u, src + 2);
-                }
+        for (int b = 0; b < qper; b += 4) {
+            double x[16];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = ptid + (b + u) * NT;
+                x[4 * u] = x[4 * u + 1] = x[4 * u + 2] = x[4 * u + 3] = 0.0;
+                if (b + u < qper && j < nquad)
+                    ld_v4f64(v + quad_pos(j, L, nquad, lead4), x[4 * u], x[4 * u + 1], x[4 * u + 2], x[4 * u + 3]);
             }
-            cp_async_wait_all();
-        }
-        __syncwarp();
-#pragma unroll 1
-        for (int u = 0; u < qper * 4; ++u) {
-            const int idx = 4 * (ptid + (u >> 2) * NT) + (u & 3);
-            if (idx < S) {
-                const double xx = __longlong_as_double((long long)sk[idx]);
-                const bool ok = (xx == xx);
-                const unsigned long long k = ok ? ko_okey(xx + 0.0) : KO_KEY_NAN;
-                sk[idx] = k;
-                if (ok) {
-                    kmn = k < kmn ? k : kmn;
-                    kmx = k > kmx ? k : kmx;
-                    nv++;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int j = ptid + (b + u) * NT;
+                if (b + u < qper && j < nquad) {
+                    uint32_t hk4[4];
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) {
+                        const double xx = x[4 * u + h];
+                        const bool ok = (xx == xx);
+                        const unsigned long long k = ko_okey(xx + 0.0);
+                        hk4[h] = ok ? (uint32_t)(k >> 32) : HK_NONE;
+                        if (ok) {
+                            kmn = k < kmn ? k : kmn;
+                            kmx = k > kmx ? k : kmx;
+                            nv++;
+                        }
+                    }
+                    *reinterpret_cast<uint4*>(sk + 4 * j) = make_uint4(hk4[0], hk4[1], hk4[2], hk4[3]);
                 }
             }
         }
@@ -496,7 +495,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
     const uint32_t submask = (1u << (sh1 - sh2)) - 1u;
 #pragma unroll 1
     for (int i = 0; i < per; ++i) {
-        const uint32_t k = (uint32_t)(sk[ptid + i * NT] >> 32);
+        const uint32_t k = sk[ptid + i * NT];
         if (k != HK_NONE) red_shared_add(&sm.hist1()[(k - hkmin) >> sh1], 1u);
     }
     plan_sync();
@@ -565,7 +564,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
     // ---- round 2: 256 sub-bins inside the bins that hold an interval end
 #pragma unroll 1
     for (int i = 0; i < per; ++i) {
-        const uint32_t k = (uint32_t)(sk[ptid + i * NT] >> 32);
+        const uint32_t k = sk[ptid + i * NT];
         if (k == HK_NONE) continue;
         const uint32_t d = k - hkmin;
         unsigned m = sm.lut()[d >> sh1];
@@ -605,17 +604,24 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
 #pragma unroll
     for (int t = 0; t < F_NT; ++t) heavy_any |= (ps->tbin[t] >= 0 && ps->tcnt[t] >= heavy_min) ? (1u << t) : 0u;
     if (heavy_any) {
+#pragma unroll 1
         for (int i = 0; i < per; ++i) {
-            const unsigned long long key = sk[ptid + i * NT];
-            const uint32_t k = (uint32_t)(key >> 32);
+            const int idx = ptid + i * NT;
+            const uint32_t k = sk[idx];
             if (k == HK_NONE) continue;
             const uint32_t d = k - hkmin;
             unsigned m = sm.lut()[d >> sh1] & heavy_any;
             const uint32_t sub = (d >> sh2) & submask;
+            unsigned long long key = 0ull;
+            bool have = false;
             while (m) {
                 const int t = __ffs(m) - 1;
                 m &= m - 1;
                 if (ps->tsub[t] == sub) {
+                    if (!have) {   // (the low words are not kept: fetch the sample again)
+                        key = ko_okey(v[quad_pos(idx >> 2, L, nquad, lead4) + (idx & 3)] + 0.0);
+                        have = true;
+                    }
                     red_shared_min_u64(&ps->hmin[t], key);
                     red_shared_max_u64(&ps->hmax[t], key);
                 }
@@ -1021,10 +1027,26 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
             shj[j] = fs->sh[j];
             loj[j] = fs->lo[j];
         }
+        // 32-bit pre-filter per quantile: the key's high word against [lo >> 32, (end of the range) >> 32]; almost
+        // every candidate belongs to one quantile's range only, so the 64-bit arithmetic runs once per key
+        uint32_t lo32[NI_MAX], span32[NI_MAX];
+#pragma unroll
+        for (int j = 0; j < NI_MAX; ++j) {
+            const int she = stj[j] <= Q_COLLECT ? (shj[j] & 63) : 0;
+            const unsigned long long width = stj[j] == Q_HIST ? (255ull << she) | ((1ull << she) - 1ull)
+                                                              : (1ull << she) - 1ull;
+            unsigned long long end = loj[j] + width;
+            if (end < loj[j]) end = ~0ull;
+            lo32[j] = (uint32_t)(loj[j] >> 32);
+            span32[j] = stj[j] <= Q_COLLECT ? (uint32_t)(end >> 32) - lo32[j] : 0u;
+            if (stj[j] > Q_COLLECT) lo32[j] = 0xFFFFFFFFu;   // no high word passes: (hk - lo32) wraps above span
+        }
         auto visit = [&](unsigned long long key, unsigned mult) {
+            const uint32_t hk = (uint32_t)(key >> 32);
 #pragma unroll
             for (int j = 0; j < NI_MAX; ++j) {
-                if (stj[j] > Q_COLLECT || key < loj[j]) continue;
+                if (hk - lo32[j] > span32[j]) continue;   // (also when hk < lo32: the difference wraps)
+                if (key < loj[j]) continue;
                 const unsigned long long dd = (key - loj[j]) >> shj[j];
                 if (stj[j] == Q_HIST) {
                     if (dd < 256ull) red_shared_add(&sm.fbins()[j * 256 + (unsigned)dd], mult);

@@ -173,3 +173,78 @@ def fleet_scalars(values, dist=None, device="cpu"):
     if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t)
     return t.cpu().numpy()
+
+
+# ---- device-side merges: nothing is read back between the steps of a merge (the bench loop stays asynchronous) ----
+def fleet_quantiles_device(values, qs, rollup, dist=None, workspace=None):
+    """Exact nearest-rank quantiles ``qs`` of the pooled per-shard ``values`` (CUDA float64 tensor, NaN = no
+    value), all ranks get the same result: a CUDA float64 tensor of len(qs), valid once the current stream has
+    run.  Four rounds of: local 65 536-bin key histogram under the current prefix (``ko_key_histogram_state_dev``),
+    ONE all-reduce of the bins of all quantiles over NCCL, digit selection on the GPU (``ko_key_select_dev``).
+    The refinement state lives in device memory, so no round waits for the host."""
+    import torch
+    dev = values.device
+    v = values.reshape(-1).contiguous()
+    nq = len(qs)
+    world = dist.get_world_size() if (dist is not None and dist.is_initialized()) else 1
+    ws = workspace if workspace is not None else {}
+    if ws.get("fq_nq") != nq:
+        ws["fq_nq"] = nq
+        ws["fq_state"] = torch.zeros((nq, 4), dtype=torch.int64, device=dev)
+        ws["fq_hist"] = torch.zeros((nq, HIST_BINS), dtype=torch.int64, device=dev)
+        ws["fq_q"] = torch.tensor(list(qs), dtype=torch.float64, device=dev)
+    state, hist, qt = ws["fq_state"], ws["fq_hist"], ws["fq_q"]
+    n = (v == v).sum().reshape(1)
+    if world > 1:
+        dist.all_reduce(n)
+    nf = n.double()
+    rank = torch.clamp(torch.ceil(qt * nf), min=1.0).minimum(nf).long()      # 0 when the fleet has no valid value
+    state.zero_()
+    state[:, 2] = rank
+    stream = torch.cuda.current_stream().cuda_stream
+    for shift in (48, 32, 16, 0):
+        for j in range(nq):
+            rollup.key_histogram_state_dev(v.data_ptr(), v.numel(), shift, state[j].data_ptr(), hist[j].data_ptr(), stream)
+        if world > 1:
+            dist.all_reduce(hist)
+        for j in range(nq):
+            rollup.key_select_dev(hist[j].data_ptr(), shift, state[j].data_ptr(), stream)
+    return state[:, 3].view(torch.float64)
+
+
+def fleet_topk_device(values, global_offset, k, dist=None):
+    """Fleet top-k of per-series ``values`` (CUDA float64, NaN = no value) by (value descending, global index
+    ascending): every shard's own top-k goes through ONE all-gather and is merged on the GPU.  Returns
+    (values[k], global_index[k]) CUDA tensors, padded with -inf / -1 when the fleet holds fewer than k values."""
+    import torch
+    dev = values.device
+    v = torch.nan_to_num(values.reshape(-1), nan=float("-inf"))
+    kk = min(k, v.numel())
+    top_v = torch.full((k,), float("-inf"), dtype=torch.float64, device=dev)
+    top_i = torch.full((k,), -1, dtype=torch.int64, device=dev)
+    if kk:
+        order = torch.argsort(v, descending=True, stable=True)[:kk]          # ties: lower index first
+        top_v[:kk] = v[order]
+        top_i[:kk] = order + int(global_offset)
+    world = dist.get_world_size() if (dist is not None and dist.is_initialized()) else 1
+    if world > 1:
+        gv = torch.empty(world * k, dtype=torch.float64, device=dev)
+        gi = torch.empty(world * k, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(gv, top_v)
+        dist.all_gather_into_tensor(gi, top_i)
+    else:
+        gv, gi = top_v, top_i
+    gi_key = torch.where(gi < 0, torch.full_like(gi, torch.iinfo(torch.int64).max), gi)
+    o1 = torch.argsort(gi_key, stable=True)                                   # secondary key first (stable sorts)
+    o2 = torch.argsort(gv[o1], descending=True, stable=True)
+    sel = o1[o2][:k]
+    out_v, out_i = gv[sel], gi[sel]
+    out_i = torch.where(torch.isinf(out_v) & (out_v < 0), torch.full_like(out_i, -1), out_i)
+    return out_v, out_i
+
+
+def fleet_scalars_device(t, dist=None):
+    """All-reduce(sum) of a small CUDA vector of additive fleet scalars, in place; returns it."""
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t)
+    return t

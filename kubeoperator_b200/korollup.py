@@ -45,6 +45,8 @@ ABI = {
     "ko_fleet_rollup": [_c_vp] + [_c_vp] * 6 + [_c_i64, _c_vp],
     "ko_key_histogram": [_c_vp, _c_vp, _c_i64, _c_int, ctypes.c_uint64, ctypes.c_uint64, _c_vp],
     "ko_key_histogram_dev": [_c_vp, _c_vp, _c_i64, _c_int, ctypes.c_uint64, ctypes.c_uint64, _c_vp, _c_vp],
+    "ko_key_histogram_state_dev": [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp],
+    "ko_key_select_dev": [_c_vp, _c_vp, _c_int, _c_vp, _c_vp],
     "ko_loki_count": [_c_vp, _c_vp, _c_vp, _c_i64, _c_vp, _c_i64, _c_vp],
     "ko_counter_increase": [_c_vp, _c_vp, _c_vp, _c_i64, _c_dbl, _c_vp, _c_vp],
     "ko_prom_open": [ctypes.c_char_p, _c_i64, ctypes.POINTER(_c_vp)],
@@ -275,11 +277,18 @@ class Rollup:
                   "count")
 
     def fleet_rollup(self, counts, cpu_total, mem_total, cpu_usage, mem_usage, max_pods):
-        """The browser's fleet roll-up — dashboard.component.ts:117-153."""
-        counts = _arr(counts, np.int64).reshape(-1, 5)
+        """The browser's fleet roll-up — dashboard.component.ts:117-153.  ``counts`` rows: pods, namespaces,
+        deployments, containers, nodes [, ui_nodes]: ``ui_nodes`` = cluster.nodes.length of the UI's own cluster list,
+        -1 = the list does not hold the cluster (no pod capacity); without the sixth column the blob's node count is
+        used.  ``max_pods`` entries: None or a negative value = MAX_PODS undefined (-> 110); 0 is a configured zero."""
+        counts = np.asarray(counts, np.int64)
+        counts = counts.reshape(-1, counts.shape[-1] if counts.ndim == 2 else 5)
+        if counts.shape[1] == 5:
+            counts = np.concatenate([counts, counts[:, 4:5]], axis=1)
+        counts = np.ascontiguousarray(counts.reshape(-1, 6))
         k = counts.shape[0]
         cols = [_arr(x, np.float64) for x in (cpu_total, mem_total, cpu_usage, mem_usage)]
-        mp = _arr(max_pods, np.int32)
+        mp = _arr([-1 if m is None else int(m) for m in max_pods], np.int32)
         out = np.zeros(12)
         self._check(self._lib.ko_fleet_rollup(self._ctx, _ptr(counts), _ptr(cols[0]), _ptr(cols[1]),
                                               _ptr(cols[2]), _ptr(cols[3]), _ptr(mp), k, _ptr(out)))
@@ -302,6 +311,13 @@ class Rollup:
                                                    int(prefix), d_hist, stream or None))
 
     # ------------------------------------------------------------------ next rows (§8f)
+    def key_histogram_state_dev(self, d_values, n, shift, d_state, d_hist, stream=0):
+        self._check(self._lib.ko_key_histogram_state_dev(self._ctx, d_values, int(n), int(shift), d_state, d_hist,
+                                                         stream or None))
+
+    def key_select_dev(self, d_hist, shift, d_state, stream=0):
+        self._check(self._lib.ko_key_select_dev(self._ctx, d_hist, int(shift), d_state, stream or None))
+
     def loki_count(self, buf, line_offsets, group_offsets):
         """Lines containing b'level=error' per container — prometheus_client.py:140-146."""
         buf = _arr(buf, np.uint8)

@@ -15,6 +15,8 @@ CONFIGS = {
     "c1": dict(nodes=4, gpus=0, pods=120, L=5760),          # 1 master + 3 workers, 24 h
     "c2": dict(nodes=100, gpus=8, pods=3000, L=40320),      # 100 nodes incl. DCGM series, 7 d
     "c3": dict(nodes=1000, gpus=0, pods=30000, L=172800),   # 1000 nodes x 30 pods, 30 d
+    # 10 000-node multi-cluster fleet, 30 d: 8 node-level series per node (the 4 of the reference + 4 GPU aggregates)
+    "c4": dict(nodes=10000, gpus=0, pods=0, L=172800, per_node=8, clusters=100),
 }
 
 
@@ -23,6 +25,9 @@ def series_layout(cfg):
     per GPU util(discrete %) fb_used(gauge) fb_free(gauge) temp(discrete) power(gauge);
     per pod cpu(counter) mem(gauge)."""
     kinds = []
+    if cfg.get("per_node", 4) == 8:     # + GPU aggregates per node: mean util (gauge), fb used (gauge), max temp (discrete), power (gauge)
+        return np.array([KIND_GAUGE, KIND_CONST, KIND_CONST, KIND_GAUGE, KIND_GAUGE, KIND_GAUGE, KIND_DISCRETE,
+                         KIND_GAUGE] * cfg["nodes"], np.int8)
     kinds += [KIND_GAUGE, KIND_CONST, KIND_CONST, KIND_GAUGE] * cfg["nodes"]
     kinds += [KIND_DISCRETE, KIND_GAUGE, KIND_GAUGE, KIND_DISCRETE, KIND_GAUGE] * (cfg["nodes"] * cfg["gpus"])
     kinds += [KIND_COUNTER, KIND_GAUGE] * cfg["pods"]
@@ -32,12 +37,11 @@ def series_layout(cfg):
 def mix_kinds(config, n):
     """``n`` series with the same proportions of kinds as the config (interleaved, not in blocks)."""
     full = series_layout(CONFIGS[config] if isinstance(config, str) else config)
-    idx = (np.arange(n, dtype=np.int64) * len(full)) // max(n, 1)
-    return full[idx]
+    return np.random.default_rng(12345).choice(full, n)
 
 
 def n_series(cfg):
-    return 4 * cfg["nodes"] + 5 * cfg["nodes"] * cfg["gpus"] + 2 * cfg["pods"]
+    return cfg.get("per_node", 4) * cfg["nodes"] + 5 * cfg["nodes"] * cfg["gpus"] + 2 * cfg["pods"]
 
 
 def _one_series(rng, kind, L):
@@ -159,41 +163,67 @@ def make_nodes(seed, n_nodes, n_clusters=1, zero_frac=0.02, hot_frac=0.0):
     return dict(cpu=cpu, mem=mem, cpu_usage=cu, mem_usage=mu, cluster_of_node=cluster)
 
 
-def make_series_torch(config, seed, device, L=None, n_series_override=None, kinds=None):
-    """Full-size column generated ON THE GPU (torch) from the same distributions as make_series.
-    Returns (values tensor f64 [n*L], offsets tensor i64 [n+1], kinds ndarray).  ``kinds`` replaces the
-    config's series layout (e.g. a shorter batch with the same mix of kinds)."""
+def make_series_torch(config, seed, device, L=None, n_series_override=None, kinds=None, rows=256, zero_nodes=True):
+    """Full-size column generated ON THE GPU (torch, float64 throughout) from the same distributions as
+    make_series: Beta draws as ratios of Gamma variates, counters as cumulative Gamma(2, 0.05) increments with
+    resets (p = 1e-5 per sample), staleness NaN (p = 1e-3), 2 % of the nodes all-zero.
+    Returns (values tensor f64 [n*L], offsets tensor i64 [n+1], kinds ndarray).  ``kinds`` replaces the config's
+    series layout (e.g. a shorter batch with the same mix of kinds; no all-zero nodes then)."""
     import torch
-    cfg = dict(CONFIGS[config])
+    cfg = dict(CONFIGS[config]) if isinstance(config, str) else dict(config)
     if L is not None:
         cfg["L"] = L
+    layout = kinds is None
     kinds = series_layout(cfg) if kinds is None else np.asarray(kinds, np.int8)
     if n_series_override is not None:
         kinds = np.resize(kinds, n_series_override)
     n, L = len(kinds), cfg["L"]
     g = torch.Generator(device=device)
     g.manual_seed(seed)
-    values = torch.empty(n * L, dtype=torch.float64, device=device)
+    f64 = torch.float64
+    values = torch.empty(n * L, dtype=f64, device=device)
+    view = values.view(n, L)
     kt = torch.from_numpy(kinds.astype(np.int64)).to(device)
-    rows = 512                                             # generate in row blocks to bound temporaries
-    for r0 in range(0, n, rows):
+
+    def beta(a, b, m):
+        x = torch._standard_gamma(torch.full((m, L), a, dtype=f64, device=device), generator=g)
+        y = torch._standard_gamma(torch.full((m, L), b, dtype=f64, device=device), generator=g)
+        return x.div_(x + y)
+
+    for r0 in range(0, n, rows):                           # row blocks bound the temporaries
         r1 = min(n, r0 + rows)
-        m = r1 - r0
-        k = kt[r0:r1].unsqueeze(1)
-        # Beta(2,5) as an order statistic: 2nd smallest of 6 uniforms; Beta(2,2): 2nd smallest of 3
-        u = torch.rand((m, L, 6), generator=g, device=device, dtype=torch.float32)
-        b25 = torch.kthvalue(u, 2, dim=2).values.double()
-        b22 = torch.kthvalue(u[:, :, :3], 2, dim=2).values.double()
-        w = torch.rand((m, L), generator=g, device=device, dtype=torch.float64)
-        gauge = torch.where(w < 0.01, 0.8 + 0.2 * b25, b25)
-        const = torch.tensor([4.0, 8.0, 16.0, 64.0], device=device, dtype=torch.float64)[
-            torch.randint(0, 4, (m, 1), generator=g, device=device)].expand(m, L)
-        counter = torch.cumsum(0.05 * (-torch.log1p(-u[:, :, 3].double()) - torch.log1p(-u[:, :, 4].double())), dim=1)
-        disc = torch.floor(40.0 + 40.0 * b22)
-        blk = torch.where(k == KIND_GAUGE, gauge, torch.where(k == KIND_CONST, const,
-                          torch.where(k == KIND_COUNTER, counter, disc)))
-        blk = torch.where(w > 0.999, torch.full_like(blk, float("nan")), blk)
-        values[r0 * L:r1 * L] = blk.reshape(-1)
-        del u, b25, b22, w, gauge, counter, disc, blk
+        k = kt[r0:r1]
+        blk = view[r0:r1]
+        for kind in (KIND_GAUGE, KIND_CONST, KIND_COUNTER, KIND_DISCRETE):
+            idx = (k == kind).nonzero().flatten()
+            m = int(idx.numel())
+            if m == 0:
+                continue
+            if kind == KIND_GAUGE:
+                v = beta(2.0, 5.0, m)
+                hot = torch.rand((m, L), generator=g, device=device) < 0.01
+                v = torch.where(hot, 0.8 + 0.2 * v, v)     # 1 % of usage samples above the 0.8 band
+            elif kind == KIND_CONST:
+                c = torch.tensor([4.0, 8.0, 16.0, 64.0], device=device, dtype=f64)
+                v = c[torch.randint(0, 4, (m, 1), generator=g, device=device)].expand(m, L)
+            elif kind == KIND_COUNTER:
+                inc = torch._standard_gamma(torch.full((m, L), 2.0, dtype=f64, device=device), generator=g).mul_(0.05)
+                reset = torch.rand((m, L), generator=g, device=device) < 1e-5
+                c = torch.cumsum(inc, dim=1)
+                base = torch.cummax(torch.where(reset, c - inc, torch.zeros_like(c)), dim=1).values
+                v = c - base                               # restarts from its own increment at a reset
+                del inc, c, base
+            else:
+                v = torch.floor(40.0 + 40.0 * beta(2.0, 2.0, m))   # integer-valued (temperature / util style)
+            stale = torch.rand((m, L), generator=g, device=device) < 1e-3
+            blk[idx] = torch.where(stale, torch.full_like(v, float("nan")), v)
+            del v, stale
+    if layout and zero_nodes:                              # exercises cluster_monitor.py:174
+        nodes = min(cfg["nodes"], n // cfg.get("per_node", 4))
+        per = cfg.get("per_node", 4)
+        z = (torch.rand(nodes, generator=g, device=device) < 0.02).nonzero().flatten().tolist()
+        for node in z:
+            view[per * node] = 0.0
+            view[per * node + 3] = 0.0
     offsets = torch.arange(n + 1, dtype=torch.int64, device=device) * L
     return values, offsets, kinds

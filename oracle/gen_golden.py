@@ -193,7 +193,58 @@ def gen_fleet():
                   cpu_total=20.0, mem_total=62.5, cpu_usage=37.5, mem_usage=40.625, max_pod_count=540,
                   container_usage=150 / 540 * 100, count=2)
     bands = [[0, 255], [None, 255], [0.5, 0], [60, 0], [60.0001, 1], [80, 1], [80.5, 2], [100, 2], [-5, 0]]
-    return dict(clusters=clusters, expect=expect, bands=bands)
+    # More vectors, each worked out by hand from dashboard.component.ts:117-153 (node is not available to run it).
+    # ui_nodes = cluster.nodes.length of the UI's own cluster list; None = the list does not hold the cluster.
+    def cl(pods, ns, dep, cont, nodes, ct, mt, cu, mu, max_pods=None, **kw):
+        return dict(pods=pods, namespaces=ns, deployments=dep, containers=cont, nodes=nodes, cpu_total=ct, mem_total=mt,
+                    cpu_usage=cu, mem_usage=mu, max_pods=max_pods, **kw)
+
+    def ex(pod, ns, dep, cont, node, ct, mt, cu, mu, maxpod, cusage, count):
+        return dict(pod_count=pod, namespace_count=ns, deployment_count=dep, container_count=cont, node_count=node,
+                    cpu_total=ct, mem_total=mt, cpu_usage=cu, mem_usage=mu, max_pod_count=maxpod,
+                    container_usage=cusage, count=count)
+    more = [
+        # no cluster at all: every sum 0, count 0 -> usages stay 0 (:147), maxPodCount 0 -> containerUsage 0 (:151)
+        dict(name="empty fleet", clusters=[], expect=ex(0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0)),
+        # every cluster all-zero: count = 2 - 2 = 0, so the usage SUMS are left undivided (0.25 + 0.5, 0.125 + 0.25)
+        dict(name="count == 0", clusters=[cl(3, 1, 1, 3, 1, 0, 0, 0.25, 0.125), cl(5, 1, 2, 6, 2, 0, 0, 0.5, 0.25)],
+             expect=ex(8, 2, 3, 9, 3, 0, 0, 0.75, 0.375, 110 * 1 + 110 * 2, 8 / 330 * 100, 0)),
+        # cpu_total 0 but mem_total not: the cluster still counts (:131 needs both)
+        dict(name="only one total zero", clusters=[cl(10, 2, 2, 12, 2, 0, 32.0, 0.5, 0.25), cl(10, 2, 2, 12, 2, 16.0, 0, 0.25, 0.5)],
+             expect=ex(20, 4, 4, 24, 4, 16.0, 32.0, 0.75 / 2 * 100, 0.75 / 2 * 100, 440, 20 / 440 * 100, 2)),
+        # MAX_PODS configured as 0: capacity 0 (0 !== undefined), so maxPodCount 0 and containerUsage stays 0
+        dict(name="MAX_PODS 0", clusters=[cl(7, 1, 1, 7, 3, 8.0, 16.0, 0.5, 0.5, max_pods=0)],
+             expect=ex(7, 1, 1, 7, 3, 8.0, 16.0, 50.0, 50.0, 0, 0, 1)),
+        # MAX_PODS present / absent side by side
+        dict(name="MAX_PODS mixed", clusters=[cl(100, 3, 9, 150, 5, 40.0, 160.0, 0.75, 0.5, max_pods=200),
+                                               cl(20, 1, 2, 20, 1, 4.0, 8.0, 0.25, 0.25)],
+             expect=ex(120, 4, 11, 170, 6, 44.0, 168.0, 50.0, 37.5, 200 * 5 + 110, 120 / 1110 * 100, 2)),
+        # a cluster whose blob exists but which the UI's cluster list does not hold: it adds no capacity (:136)
+        dict(name="cluster missing from the UI list", clusters=[cl(50, 2, 4, 60, 4, 16.0, 64.0, 0.5, 0.25, max_pods=100, ui_nodes=None),
+                                                                 cl(10, 1, 1, 10, 2, 8.0, 16.0, 0.25, 0.75)],
+             expect=ex(60, 3, 5, 70, 6, 24.0, 80.0, 37.5, 50.0, 220, 60 / 220 * 100, 2)),
+        # the UI list knows a different number of nodes than the blob holds (a node was added since the last rollup)
+        dict(name="ui list has more nodes", clusters=[cl(30, 1, 3, 30, 2, 8.0, 16.0, 0.5, 0.5, max_pods=50, ui_nodes=3)],
+             expect=ex(30, 1, 3, 30, 2, 8.0, 16.0, 50.0, 50.0, 150, 20.0, 1)),
+        # only missing clusters: maxPodCount 0 -> containerUsage 0 although there are pods
+        dict(name="no capacity known", clusters=[cl(9, 1, 1, 9, 3, 12.0, 24.0, 1.0, 1.0, ui_nodes=None)],
+             expect=ex(9, 1, 1, 9, 3, 12.0, 24.0, 100.0, 100.0, 0, 0, 1)),
+        # pods above capacity: the UI does not clamp
+        dict(name="over capacity", clusters=[cl(300, 1, 1, 300, 1, 4.0, 8.0, 0.9, 0.9, max_pods=100)],
+             expect=ex(300, 1, 1, 300, 1, 4.0, 8.0, 90.0, 90.0, 100, 300.0, 1)),
+    ]
+    return dict(clusters=clusters, expect=expect, bands=bands, more=more)
+
+
+def gen_alerts():
+    """The usage alert payload of cluster_monitor.py:423-442 for nodes of every shape set_cluster_data flags."""
+    cluster = dict(name="prod-a", item_id="3f2c9a10-1111-2222-3333-444455556666", item_name="项目一", status="RUNNING")
+    nodes = [dict(name="worker1.prod-a", status="Ready", cpu=16.0, mem=62.5, cpu_usage=91.25, mem_usage=40.0),
+             dict(name="worker2.prod-a", status="Ready", cpu=8.0, mem=31.25, cpu_usage=12.5, mem_usage=80.5),
+             dict(name="master1.prod-a", status="NotReady", cpu=4.0, mem=15.5, cpu_usage=100.0, mem_usage=100.0),
+             dict(name="节点四", status="Ready", cpu=64.0, mem=503.9, cpu_usage=80.00001, mem_usage=0.0)]
+    msgs, contents = rh.run_usage_messages(cluster, nodes)
+    return dict(cluster=cluster, nodes=nodes, reference_get_usage_message=msgs, reference_get_usage_content=contents)
 
 
 def main():
@@ -205,6 +256,7 @@ def main():
         "reference_loki.json": gen_loki(),
         "builddefined_series.json": gen_series(),
         "handcomputed_fleet.json": gen_fleet(),
+        "reference_usage_alert.json": gen_alerts(),
     }
     for name, obj in files.items():
         with open(os.path.join(OUT, name), "w") as f:

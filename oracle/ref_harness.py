@@ -10,6 +10,8 @@ Used in THIS container only (it needs /root/reference, which does not exist on t
 * ``PrometheusClient.calculate_available_rate`` / ``handle_targets_message``
                                              core/apps/kubeops_api/prometheus_client.py:34-85
 * ``PrometheusClient.get_msg_from_loki``     core/apps/kubeops_api/prometheus_client.py:119-149
+* ``ClusterMonitor.get_usage_message`` / ``get_usage_content``
+                                             core/apps/kubeops_api/cluster_monitor.py:423-442
 
 Nothing here is product code; nothing under kubeoperator_b200/ may import it.  No reference source is
 copied: the modules are imported from where they lie (method: SURVEY.md §8c).
@@ -213,3 +215,17 @@ def run_loki_count(label_values, streams_by_name, cluster_name="c"):
         return cli.get_msg_from_loki(cluster_name)
     finally:
         pc.AppsClient = old
+
+
+def run_usage_messages(cluster, nodes):
+    """REAL ``get_usage_message`` and ``get_usage_content`` (cluster_monitor.py:423-442) for every node dict.
+    ``cluster``: dict with name, item_id, item_name, status.  Returns (messages, contents)."""
+    cm, _ = load_reference()
+    mon = cm.ClusterMonitor.__new__(cm.ClusterMonitor)
+    mon.cluster = types.SimpleNamespace(**cluster)
+    msgs, contents = [], []
+    for n in nodes:
+        node = types.SimpleNamespace(**n)            # cluster_data.py:47-55: the reference dumps node.__dict__
+        msgs.append(mon.get_usage_message(node))
+        contents.append(mon.get_usage_content(node))
+    return msgs, contents

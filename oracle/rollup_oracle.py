@@ -210,7 +210,9 @@ def fleet_rollup(clusters):
     """Line-by-line restatement of dashboard.component.ts:117-153 (TypeScript; JS numbers = f64).
 
     ``clusters``: list of dicts {pods, namespaces, deployments, containers, nodes (ints),
-    cpu_total, mem_total, cpu_usage, mem_usage (floats), max_pods (None -> 110, :138-141)}.
+    cpu_total, mem_total, cpu_usage, mem_usage (floats), max_pods (None = undefined -> 110, :138-141; 0 stays 0)}
+    and optionally ``ui_nodes``: cluster.nodes.length of the UI's own cluster list (:142), None when that list
+    does not hold the cluster (the loop at :136 then finds nothing and no capacity is added); default: ``nodes``.
     """
     pod = ns = dep = cont = node = 0
     cpu_total = mem_total = cpu_usage = mem_usage = 0
@@ -229,10 +231,12 @@ def fleet_rollup(clusters):
         mem_usage = mem_usage + d["mem_usage"]                    # :130
         if d["cpu_total"] == 0 and d["mem_total"] == 0:           # :131
             count -= 1
-        max_pod = d.get("max_pods")
-        if max_pod is None:                                       # :139
-            max_pod = 110                                         # :140
-        max_pod_count = max_pod_count + max_pod * d["nodes"]      # :142-143
+        ui_nodes = d.get("ui_nodes", d["nodes"])
+        if ui_nodes is not None:                                  # :136-137 the UI's cluster list holds it
+            max_pod = d.get("max_pods")                           # :138
+            if max_pod is None:                                   # :139 (=== undefined; 0 is a value)
+                max_pod = 110                                     # :140
+            max_pod_count = max_pod_count + max_pod * ui_nodes    # :142-143
     if count > 0:                                                 # :147
         cpu_usage = cpu_usage / count * 100                       # :148
         mem_usage = mem_usage / count * 100                       # :149

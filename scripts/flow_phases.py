@@ -14,7 +14,10 @@ QS = [0.5, 0.95, 0.99][:nq]
 r = Rollup(0)
 lib = korollup.load_library()
 cfg = "c2" if L <= 40320 else "c3"
-vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", L=L, kinds=synth.mix_kinds(cfg, n))
+import os, numpy as np
+kk = os.environ.get("KO_KINDS")
+kinds = synth.mix_kinds(cfg, n) if not kk else np.resize(np.array([int(x) for x in kk.split(",")], np.int8), n)
+vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", L=L, kinds=kinds)
 q = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
 s = torch.zeros(n, dtype=torch.float64, device="cuda")
 out = (ctypes.c_ulonglong * 64)()

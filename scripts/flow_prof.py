@@ -12,7 +12,10 @@ iters = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 QS = [0.5, 0.95, 0.99][:nq]
 r = Rollup(0)
 cfg = "c2" if L <= 40320 else "c3"
-vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", L=L, kinds=synth.mix_kinds(cfg, n))
+import os, numpy as np
+kk = os.environ.get("KO_KINDS")     # e.g. "2" = counters only, "0,2" = gauges and counters alternating
+kinds = synth.mix_kinds(cfg, n) if not kk else np.resize(np.array([int(x) for x in kk.split(",")], np.int8), n)
+vals, offs, kinds = synth.make_series_torch(cfg, 1, "cuda", L=L, kinds=kinds)
 q = torch.zeros((n, 3), dtype=torch.float64, device="cuda")
 s = torch.zeros(n, dtype=torch.float64, device="cuda")
 for it in range(iters):

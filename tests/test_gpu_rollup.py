@@ -185,34 +185,81 @@ def test_loki_error_count(rollup, golden_dir):
     assert np.array_equal(rollup.loki_count(buf, lo, go), c_oracle.loki_count(buf, lo, go))
 
 
+def _fleet_args(cl):
+    counts = [[c["pods"], c["namespaces"], c["deployments"], c["containers"], c["nodes"],
+               -1 if c.get("ui_nodes", c["nodes"]) is None else c.get("ui_nodes", c["nodes"])] for c in cl]
+    return (counts, [c["cpu_total"] for c in cl], [c["mem_total"] for c in cl], [c["cpu_usage"] for c in cl],
+            [c["mem_usage"] for c in cl], [c["max_pods"] for c in cl])
+
+
 def test_fleet_rollup(rollup, golden_dir):
     from kubeoperator_b200 import cluster_monitor as cm
     g = _load(golden_dir, "handcomputed_fleet.json")
-    cl = g["clusters"]
-    got = rollup.fleet_rollup([[c["pods"], c["namespaces"], c["deployments"], c["containers"], c["nodes"]] for c in cl],
-                              [c["cpu_total"] for c in cl], [c["mem_total"] for c in cl],
-                              [c["cpu_usage"] for c in cl], [c["mem_usage"] for c in cl],
-                              [c["max_pods"] or 0 for c in cl])
+    got = rollup.fleet_rollup(*_fleet_args(g["clusters"]))
     for k, v in g["expect"].items():
         assert _close(got[k], v), k
+    for case in g["more"]:            # hand-computed: count == 0, MAX_PODS 0 / absent, clusters the UI does not list ...
+        if not case["clusters"]:
+            continue
+        got = rollup.fleet_rollup(*_fleet_args(case["clusters"]))
+        for k, v in case["expect"].items():
+            assert _close(got[k], v), (case["name"], k, got[k], v)
     rng = np.random.default_rng(8)
     K = 5000
     cl = [dict(pods=int(rng.integers(0, 500)), namespaces=int(rng.integers(0, 9)), deployments=int(rng.integers(0, 50)),
                containers=int(rng.integers(0, 900)), nodes=int(rng.integers(0, 40)),
                cpu_total=float(rng.choice([0.0, 16.0, 64.0])), mem_total=float(rng.choice([0.0, 128.5])),
                cpu_usage=float(rng.random()), mem_usage=float(rng.random()),
-               max_pods=None if rng.random() < 0.5 else int(rng.integers(10, 300))) for _ in range(K)]
+               max_pods=None if rng.random() < 0.5 else int(rng.integers(0, 300)),
+               ui_nodes=None if rng.random() < 0.1 else int(rng.integers(0, 40))) for _ in range(K)]
     exp = ro.fleet_rollup(cl)
-    got = rollup.fleet_rollup([[c["pods"], c["namespaces"], c["deployments"], c["containers"], c["nodes"]] for c in cl],
-                              [c["cpu_total"] for c in cl], [c["mem_total"] for c in cl],
-                              [c["cpu_usage"] for c in cl], [c["mem_usage"] for c in cl],
-                              [c["max_pods"] or 0 for c in cl])
+    got = rollup.fleet_rollup(*_fleet_args(cl))
     for k, v in exp.items():
         assert _close(got[k], v), k
     blobs = [dict(name="a", pods=[dict(containers=[1, 2])] * 3, namespaces=[1], deployments=[1, 2], nodes=[1, 2],
-                  cpu_total=8.0, mem_total=4.0, cpu_usage=0.5, mem_usage=0.25)]
-    out = cm.fleet_rollup(blobs, {"a": 50}, {"a": 2}, rollup)
-    assert out["max_pod_count"] == 100 and _close(out["container_usage"], 3.0) and out["container_count"] == 6
+                  cpu_total=8.0, mem_total=4.0, cpu_usage=0.5, mem_usage=0.25),
+             dict(name="gone", pods=[dict(containers=[1])] * 2, namespaces=[1], deployments=[1], nodes=[1],
+                  cpu_total=4.0, mem_total=4.0, cpu_usage=0.25, mem_usage=0.25)]
+    out = cm.fleet_rollup(blobs, {"a": 50}, {"a": 3}, rollup)          # "gone" is not in the UI's cluster list
+    assert out["max_pod_count"] == 150 and _close(out["container_usage"], 5 / 150 * 100) and out["container_count"] == 8
+    out = cm.fleet_rollup(blobs, {"a": 0}, {"a": 2, "gone": 1}, rollup)  # MAX_PODS configured as 0 is a value
+    assert out["max_pod_count"] == 110
+
+
+def test_flagged_nodes_reach_the_alert_sink_with_the_reference_payload(rollup, golden_dir):
+    """f4 end to end: set_cluster_data's threshold flags (cluster_monitor.py:174-179) -> one message per flagged node,
+    equal to the reference's CLUSTER_USAGE payload (tests/golden/reference_usage_alert.json)."""
+    import json
+    from kubeoperator_b200 import cluster_monitor as cm
+    g = _load(golden_dir, "reference_usage_alert.json")
+    c = g["cluster"]
+    quiet = [dict(name="quiet", status="Ready", cpu=4.0, mem=8.0, cpu_usage=10.0, mem_usage=20.0),
+             dict(name="idle", status="Ready", cpu=4.0, mem=8.0, cpu_usage=0.0, mem_usage=0.0)]
+    nodes = [quiet[0]] + g["nodes"][:2] + [quiet[1]] + g["nodes"][2:]
+    sent = []
+    cr = cm.ClusterRollup(c["name"], rollup=rollup, alert_sink=sent.append, item_id=c["item_id"],
+                          item_name=c["item_name"], status=c["status"])
+    cr.rollup_nodes(nodes)
+    assert [n["name"] for n in cr.flagged_nodes] == [n["name"] for n in g["nodes"]]
+    assert len(sent) == len(g["nodes"])
+    for msg, ref_msg, ref_content in zip(sent, g["reference_get_usage_message"], g["reference_get_usage_content"]):
+        want = dict(ref_msg)
+        want["content"] = ref_content
+        assert json.dumps(msg, ensure_ascii=False) == json.dumps(want, ensure_ascii=False)
+
+
+def test_health_day_mean_through_the_library(rollup):
+    """a8: handle_cluster_health_msg_day (cluster_health_utils.py:28-33) is the arithmetic mean over all HOUR rows;
+    through the library that is the ``mean`` of ko_series_rollup over the rows as one series per day."""
+    rng = np.random.default_rng(31)
+    days = [rng.integers(0, 101, 24).astype(np.float64) for _ in range(40)] + [np.full(24, 100.0), np.zeros(24),
+                                                                                 np.array([33.0])]
+    offsets = np.concatenate([[0], np.cumsum([len(d) for d in days])]).astype(np.int64)
+    got = rollup.series_rollup(np.concatenate(days), offsets, ())
+    for i, d in enumerate(days):
+        exp = ro.health_day_mean([int(x) for x in d])
+        assert abs(got["mean"][i] - exp) <= 1e-12 * max(1.0, abs(exp)), (i, got["mean"][i], exp)
+        assert int(got["mean"][i]) == int(exp)              # what the IntegerField keeps (models/cluster_health_history.py:17)
 
 
 def test_counter_increase(rollup):

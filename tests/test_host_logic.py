@@ -103,3 +103,24 @@ def test_cluster_data_dict_key_order():
     assert list(d) == ["id", "name", "pods", "nodes", "token", "namespaces", "deployments", "cpu_usage", "cpu_total",
                        "mem_usage", "mem_total", "restart_pods", "warn_containers", "error_loki_containers",
                        "error_pods"]          # cluster_data.py:9-23
+
+
+def test_usage_alert_payload_equals_reference(golden_dir):
+    """f4: the CLUSTER_USAGE message of cluster_monitor.py:423-442.  get_usage_content must be the reference's dict
+    (same keys, order, values); get_usage_message is the reference's message with that content (the reference wires
+    get_event_content there by mistake, which labels the alert CLUSTER_EVENT)."""
+    import json
+    import os
+    from kubeoperator_b200 import cluster_monitor as cm
+    g = json.load(open(os.path.join(golden_dir, "reference_usage_alert.json")))
+    c = g["cluster"]
+    cr = cm.ClusterRollup(c["name"], rollup=object(), item_id=c["item_id"], item_name=c["item_name"], status=c["status"])
+    for node, ref_msg, ref_content in zip(g["nodes"], g["reference_get_usage_message"], g["reference_get_usage_content"]):
+        content = cr.get_usage_content(node)
+        assert content == ref_content and list(content) == list(ref_content)
+        msg = cr.get_usage_message(node)
+        want = dict(ref_msg)
+        assert want["content"]["resource_type"] == "CLUSTER_EVENT"        # the reference's slip, recorded
+        want["content"] = ref_content
+        assert msg == want and list(msg) == list(ref_msg)
+        assert json.dumps(msg, ensure_ascii=False) == json.dumps(want, ensure_ascii=False)

@@ -119,6 +119,17 @@ def _dec(v):
     return float(v)
 
 
+def test_fleet_rollup_more_handcomputed_vectors(golden_dir):
+    """count == 0, every cluster zero, MAX_PODS absent / present / 0, clusters the UI list does not hold, a UI node
+    count that differs from the blob's: each worked out by hand from dashboard.component.ts:117-153."""
+    g = _load(golden_dir, "handcomputed_fleet.json")
+    assert len(g["more"]) >= 8
+    for case in g["more"]:
+        got = ro.fleet_rollup(case["clusters"])
+        for k, v in case["expect"].items():
+            assert math.isclose(got[k], v, rel_tol=1e-15, abs_tol=0), (case["name"], k, got[k], v)
+
+
 def test_series_builddefined_vectors(golden_dir):
     g = _load(golden_dir, "builddefined_series.json")
     qs = g["qs"]
