@@ -407,10 +407,10 @@ int ko_fleet_rollup(ko_ctx* ctx, const int64_t* counts, const double* cpu_total,
     KO_CUDA(cudaSetDevice(ctx->device));
     const size_t K = (size_t)n_clusters;
     int rc;
-    if ((rc = ko_buf_reserve(&ctx->in_small, piece(K * 5, 8) + 4 * piece(K, 8) + piece(K, 4) + 256))) return rc;
+    if ((rc = ko_buf_reserve(&ctx->in_small, piece(K * 6, 8) + 4 * piece(K, 8) + piece(K, 4) + 256))) return rc;
     if ((rc = ko_buf_reserve(&ctx->out_small, 256))) return rc;
     Bump in{(unsigned char*)ctx->in_small.p, 0};
-    int64_t* d_counts = in.take<int64_t>(K * 5);
+    int64_t* d_counts = in.take<int64_t>(K * 6);
     double* d_ct = in.take<double>(K);
     double* d_mt = in.take<double>(K);
     double* d_cu = in.take<double>(K);
@@ -419,7 +419,7 @@ int ko_fleet_rollup(ko_ctx* ctx, const int64_t* counts, const double* cpu_total,
     double* d_out = (double*)ctx->out_small.p;
     cudaStream_t st = ctx->stream;
     if (K) {
-        KO_CUDA(cudaMemcpyAsync(d_counts, counts, K * 40, cudaMemcpyHostToDevice, st));
+        KO_CUDA(cudaMemcpyAsync(d_counts, counts, K * 48, cudaMemcpyHostToDevice, st));
         KO_CUDA(cudaMemcpyAsync(d_ct, cpu_total, K * 8, cudaMemcpyHostToDevice, st));
         KO_CUDA(cudaMemcpyAsync(d_mt, mem_total, K * 8, cudaMemcpyHostToDevice, st));
         KO_CUDA(cudaMemcpyAsync(d_cu, cpu_usage, K * 8, cudaMemcpyHostToDevice, st));
@@ -431,7 +431,7 @@ int ko_fleet_rollup(ko_ctx* ctx, const int64_t* counts, const double* cpu_total,
     ctx->counters.kernel_launches += 1;
     KO_CUDA(cudaMemcpyAsync(out, d_out, 12 * 8, cudaMemcpyDeviceToHost, st));
     KO_CUDA(cudaStreamSynchronize(st));
-    ctx->counters.h2d_bytes += (int64_t)(K * 76);
+    ctx->counters.h2d_bytes += (int64_t)(K * 84);
     ctx->counters.d2h_bytes += 96;
     return KO_OK;
 }

@@ -50,7 +50,7 @@ constexpr int F_GROUP_BYTES = F_GS * F_STAGE_BYTES;
 constexpr int F_NGROUPS = 7;
 constexpr int F_NSTAGES = F_NGROUPS * F_GS;
 constexpr int F_BG = 8;                        // groups of the bitmap ring (64 words each)
-constexpr int F_PF = 3;                        // groups asked into L2 ahead of the ring
+constexpr int F_PF = 8;                        // groups asked into L2 ahead of the ring
 constexpr int F_ND = 4;                        // series slots (descriptor + plan + partials)
 constexpr int F_SMAX = 8192;                   // largest pre-sample (30-day series)
 constexpr int F_POOL = 7168;                   // candidate keys held in shared memory
@@ -1264,7 +1264,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             for (uint32_t k = 0;; ++k) {
                 const int d = (int)(k % F_ND);
                 FP(0, k, 1);
-                mbar_wait_hint(sm.bar(FB_DESC + d), (k / F_ND) & 1u);
+                mbar_wait_sleep<200>(sm.bar(FB_DESC + d), (k / F_ND) & 1u);
                 FP(0, k, 2);
                 FT_MARK(0);   // producer: waiting for a descriptor
                 const FlowSlot* sl = sm.slot(d);
@@ -1322,11 +1322,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             FT_MARK(6);   // planner: planning
             // slot reuse: the finish of series k - F_ND; long series: stay one series ahead of the stream warps only
             if (ptid == 0) FP(1, k, 1);
-            if (k >= (uint32_t)F_ND) mbar_wait_hint(sm.bar(FB_FREE + d), ((k / F_ND) - 1u) & 1u);
+            if (k >= (uint32_t)F_ND) mbar_wait_sleep<400>(sm.bar(FB_FREE + d), ((k / F_ND) - 1u) & 1u);
             if (ptid == 0) FP(1, k, 2);
             if (prev_depth1 && k >= 1u) {   // the stream warps have begun series k - 1
                 const uint32_t kk = k - 1u;
-                mbar_wait_hint(sm.bar(FB_START + (int)(kk % F_ND)), (kk / F_ND) & 1u);
+                mbar_wait_sleep<400>(sm.bar(FB_START + (int)(kk % F_ND)), (kk / F_ND) & 1u);
             }
             if (ptid == 0) FP(1, k, 3);
             FT_MARK(5);   // planner: waiting for the finish warps (slot / depth)
@@ -1399,7 +1399,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const uint32_t par = (k / F_ND) & 1u;
             FT_MARK(41);   // collector 0: working
             if (lane == 0) FP(2 + (cw & 1), k, 1);
-            mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            mbar_wait_sleep<200>(sm.bar(FB_PLAN + d), par);
             if (lane == 0) FP(2 + (cw & 1), k, 2);
             FT_MARK(40);   // collector 0: waiting for the plan
             const FlowSlot* sl = sm.slot(d);
@@ -1431,7 +1431,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                 // full, every earlier group has been handed back (the producer loads in order), so the bitmap slot's
                 // previous use is over and the second wait cannot mistake it for this one.
                 wait_group_full(sm, grp);
-                mbar_wait_hint(sm.bar(FB_BMFULL + bs), buse & 1u);
+                mbar_wait_sleep<100>(sm.bar(FB_BMFULL + bs), buse & 1u);
                 FT_MARK(42);   // collector 0: waiting for bitmaps
                 LaneBits lb;
                 lds_v2u32(bm0 + bs * (uint32_t)(F_GS * 64) + (uint32_t)lane * 8u, lb.w0, lb.w1);
@@ -1491,13 +1491,42 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                     unsigned e = incl - n;                                       // this lane's first entry of the batch
                     unsigned long long* wb = sm.pool() + pw.s_base + sbase;
                     unsigned long long* gb = spill + pw.g_base + gbase_i;
+                    FT_MARK(44);   // collector 0: reserving
+                    const bool to_pool = take == total, to_spill = take == 0 && gbase_i + total <= pw.g_cap;
+                    if (to_pool || to_spill) {
+                        // the whole batch goes to one place (all but one batch of a series): one candidate of each of
+                        // the lane's two words per round, two independent chains; the destination is a generic
+                        // address held in a register pair, so that nothing but the loop body is in the loop
+                        unsigned long long dst;
+                        asm volatile("mov.u64 %0, %1;" : "=l"(dst) : "l"(to_pool ? wb : gb));
+                        const uint32_t a0 = stage_addr + (uint32_t)((wi >> 2) * 128 + ((wi & 2) ? 64 : 0)) * 8u;
+                        uint32_t w0 = lb.w0, w1 = lb.w1;
+                        unsigned long long d0 = dst + (unsigned long long)e * 8ull;
+                        unsigned long long d1 = d0 + (unsigned long long)__popc(w0) * 8ull;
 #pragma unroll 1
-                    while (lb.any()) {
-                        const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lb.pop(wi) * 8u) + 0.0);
-                        if (e < take) wb[e] = key;
-                        else if (gbase_i + (e - take) < pw.g_cap) gb[e - take] = key;
-                        else over = true;
-                        ++e;
+                        while (w0 | w1) {
+                            if (w0) {
+                                const int b = __ffs(w0) - 1;
+                                w0 &= w0 - 1;
+                                st_generic_u64(d0, ko_okey(lds_f64(a0 + (uint32_t)b * 16u) + 0.0));
+                                d0 += 8ull;
+                            }
+                            if (w1) {
+                                const int b = __ffs(w1) - 1;
+                                w1 &= w1 - 1;
+                                st_generic_u64(d1, ko_okey(lds_f64(a0 + 8u + (uint32_t)b * 16u) + 0.0));
+                                d1 += 8ull;
+                            }
+                        }
+                    } else {
+#pragma unroll 1
+                        while (lb.any()) {
+                            const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lb.pop(wi) * 8u) + 0.0);
+                            if (e < take) wb[e] = key;
+                            else if (gbase_i + (e - take) < pw.g_cap) gb[e - take] = key;
+                            else over = true;
+                            ++e;
+                        }
                     }
                 }
                 __syncwarp();
@@ -1523,14 +1552,14 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const uint32_t par = (k / F_ND) & 1u;
             FT_MARK(22);   // finish: working
             if (ftid == 0) FP(4, k, 1);
-            mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            mbar_wait_sleep<400>(sm.bar(FB_PLAN + d), par);
             if (ftid == 0) FP(4, k, 2);
             FT_MARK(20);   // finish: waiting for the plan
             const FlowSlot* sl = sm.slot(d);
             if (sl->sid < 0) break;
-            mbar_wait_hint(sm.bar(FB_SDONE + d), par);
+            mbar_wait_sleep<400>(sm.bar(FB_SDONE + d), par);
             if (ftid == 0) FP(4, k, 3);
-            mbar_wait_hint(sm.bar(FB_CDONE + d), par);
+            mbar_wait_sleep<400>(sm.bar(FB_CDONE + d), par);
             if (ftid == 0) FP(4, k, 4);
             FT_MARK(21);   // finish: waiting for the stream warps and the collectors
             const PoolWin pw = pool_window(single, k, a.spill_cap);
@@ -1552,7 +1581,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const uint32_t par = (k / F_ND) & 1u;
             FT_MARK(31);   // stream warp 0: working (scan + epilogue)
             if (lane == 0 && ws < 3) FP(5 + ws, k, 1);
-            mbar_wait_hint(sm.bar(FB_PLAN + d), par);
+            mbar_wait_sleep<100>(sm.bar(FB_PLAN + d), par);
             if (lane == 0 && ws < 3) FP(5 + ws, k, 2);
             FT_MARK(30);   // stream warp 0: waiting for the plan
             const FlowSlot* sl = sm.slot(d);
