@@ -8,10 +8,9 @@
  *
  * Conventions
  *   - All buffers are caller-allocated, C-contiguous, native endian.  `*_dev` entry points take DEVICE
- *     pointers and a CUDA stream (as void*) and only enqueue work (one exception: ko_series_rollup_dev with
- *     more than 16384 series, and ko_series_rollup_static with more than 2048, wait once on the stream to
- *     read back how many of them are long); the others take HOST pointers, do their own H2D/D2H and
- *     return when the outputs are valid.
+ *     pointers and a CUDA stream (as void*) and only enqueue work (ko_series_status is the call that waits for
+ *     the stream and reads the flags back); the others take HOST pointers, do their own H2D/D2H and return
+ *     when the outputs are valid.
  *   - Return 0 (KO_OK) or a negative KO_E* code; ko_last_error() gives the message (thread-local,
  *     library-owned).  There is NO CPU fallback: without a CUDA device every compute call fails.
  *   - CUDA is initialised lazily inside ko_init(), never at load time, so the library may be dlopen'ed
@@ -131,16 +130,19 @@ int ko_series_status(ko_ctx* ctx, int32_t* out4);
  * they ask for a rollup: a worker whose GPU memory belongs entirely to another component's pool, a request
  * thread that cannot afford the device-wide synchronisation hidden in cudaMalloc / cudaFree, or any section of
  * a program in which the CUDA allocator is off limits.  This entry point has NO COUNTERPART IN THE REFERENCE
- * (and needs no ko_ctx): the work list and counters that ko_series_rollup_dev keeps in memory it cudaMallocs on
- * demand live here in a fixed array inside the library image (series lists, 4*(8+2*KO_STATIC_MAX_SERIES) bytes, plus a window of 2048 plans: 1.7 MiB),
- * which every GPU that loads the library holds until the process exits.  It calls no cudaMalloc, cudaFree or
- * other allocating routine.  Limits and rules:
- *   - n_series > KO_STATIC_MAX_SERIES is refused with KO_EINVAL (split the batch);
- *   - the first call on a device looks up the array's device address and sets the kernels' shared-memory
- *     attributes; make that first call before any stream capture begins;
+ * (and needs no ko_ctx): the work lists, counters and candidate spill space that ko_series_rollup_dev keeps in
+ * memory it cudaMallocs on demand live here in a fixed array inside the library image - 6.6 MiB: counters and two
+ * lists of 4 * KO_STATIC_MAX_SERIES ints (2 MiB) plus 4.6 MiB of spill space - which every GPU that loads the
+ * library holds until the process exits.  It calls no cudaMalloc, cudaFree or other allocating routine, and the
+ * free device memory reported by cudaMemGetInfo is the same before and after a call.  Limits and rules:
+ *   - n_series > KO_STATIC_MAX_SERIES is refused with KO_EINVAL and a message naming the limit (split the batch);
+ *   - the first call on a device looks up the array's device address (cudaGetSymbolAddress, once per device) and
+ *     sets the kernels' shared-memory attributes; later calls only clear the counters and launch kernels;
  *   - all calls on a device share the array, which keeps the previous call's contents (its counters are
  *     cleared on `stream` at the start of each call): calls whose kernels could overlap on the GPU race on it,
- *     so issue them on one stream or otherwise serialise them.
+ *     so issue them on one stream or otherwise serialise them;
+ *   - the spill space is small: series of more than about 100 000 samples are computed by the exact multi-pass
+ *     kernel instead of the one-pass kernel (same results, about a third of the speed).
  * `device` is the CUDA ordinal; it is made current.  Pointers are device pointers as in ko_series_rollup_dev. */
 int ko_series_rollup_static(int device, const double* d_values, const int64_t* d_offsets, int64_t n_series,
                             const double* q, int nq, double* d_out_sum, double* d_out_mean, double* d_out_min,

@@ -1637,15 +1637,17 @@ extern "C" int ko_series_rollup(ko_ctx* ctx, const double* values, const int64_t
 // CUDA allocator is off limits.  ko_series_rollup_dev grows ctx->scratch with cudaMalloc when a bigger batch
 // arrives; this entry point never does: no cudaMalloc, no cudaFree, no ctx (ko_init creates streams/events).
 //
-// Price: every GPU that loads libkorollup.so holds the array until the process exits (lists for
-// KO_STATIC_MAX_SERIES series, 512 KiB, plus 1.1 MiB of spill space: 1.7 MiB), batches above KO_STATIC_MAX_SERIES
-// series are refused, and all calls on one device share the array: it keeps the previous call's contents (the
-// counters are cleared on the caller's stream at the start of every call), so two calls whose kernels may overlap
-// on the GPU — different streams, or threads launching concurrently — race on it.  Serialise them on one stream.
-// The spill space is small: series whose candidates do not fit it (30-day series) take the slow exact path.
+// Price: every GPU that loads libkorollup.so holds the array until the process exits - 6.6 MiB: the counters and
+// the two work lists for KO_STATIC_MAX_SERIES series (4 entries per series and list, 2 MiB) and 4.6 MiB of spill
+// space for quantile candidates.  Batches above KO_STATIC_MAX_SERIES series are refused with KO_EINVAL and a message
+// that names the limit.  All calls on one device share the array: it keeps the previous call's contents (the
+// counters are cleared on the caller's stream at the start of every call), so two calls whose kernels may overlap on
+// the GPU - different streams, or threads launching concurrently - race on it.  Serialise them on one stream.
+// The spill space is small (4 096 candidate keys per CTA, 16 times less than ko_series_rollup_dev allocates): series
+// whose candidates do not fit it - 30-day series - are computed by the exact multi-pass kernel instead of the one-pass kernel, with the same results.
 namespace {
 
-constexpr size_t STATIC_SPILL_BYTES = 1179648;
+constexpr size_t STATIC_SPILL_BYTES = 148 * 4096 * 8;   // 4 096 candidate keys per CTA on a 148-SM GPU
 static __device__ __align__(256) int g_static_scratch[(series_lists_bytes(KO_STATIC_MAX_SERIES) + STATIC_SPILL_BYTES) /
                                                        sizeof(int)];
 

@@ -188,8 +188,8 @@ def fleet_quantiles_device(values, qs, rollup, dist=None, workspace=None):
     nq = len(qs)
     world = dist.get_world_size() if (dist is not None and dist.is_initialized()) else 1
     ws = workspace if workspace is not None else {}
-    if ws.get("fq_nq") != nq:
-        ws["fq_nq"] = nq
+    if ws.get("fq_qs") != tuple(qs):
+        ws["fq_qs"] = tuple(qs)
         ws["fq_state"] = torch.zeros((nq, 4), dtype=torch.int64, device=dev)
         ws["fq_hist"] = torch.zeros((nq, HIST_BINS), dtype=torch.int64, device=dev)
         ws["fq_q"] = torch.tensor(list(qs), dtype=torch.float64, device=dev)

@@ -109,9 +109,9 @@ STATIC_MAX_SERIES = 65536
 def series_rollup_static(device, d_values, d_offsets, n_series, qs, d_sum=0, d_mean=0, d_min=0, d_max=0, d_last=0,
                          d_count=0, d_quant=0, stream=0):
     """``ko_series_rollup_static``: the device-pointer series rollup for callers that must not allocate GPU
-    memory (no ``Rollup`` / ko_ctx needed, nothing is cudaMalloc'ed; scratch is a fixed 1.7 MiB array inside the
-    library).  At most ``STATIC_MAX_SERIES`` series per call; calls on one device must not overlap on the GPU;
-    make the first call on a device before any stream capture.  Arguments as ``Rollup.series_rollup_dev``."""
+    memory (no ``Rollup`` / ko_ctx needed, nothing is cudaMalloc'ed; scratch is a fixed 6.6 MiB array inside the
+    library).  At most ``STATIC_MAX_SERIES`` series per call (more raise ``KoRollupError``); calls on one device
+    must not overlap on the GPU.  Arguments as ``Rollup.series_rollup_dev``."""
     lib = load_library()
     q = _arr(qs, np.float64)
     rc = lib.ko_series_rollup_static(int(device), d_values, d_offsets, int(n_series), _ptr(q) if len(q) else None,
