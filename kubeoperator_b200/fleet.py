@@ -218,7 +218,8 @@ def fleet_topk_device(values, global_offset, k, dist=None):
     (values[k], global_index[k]) CUDA tensors, padded with -inf / -1 when the fleet holds fewer than k values."""
     import torch
     dev = values.device
-    v = torch.nan_to_num(values.reshape(-1), nan=float("-inf"))
+    v = values.reshape(-1)
+    v = torch.where(v != v, torch.full_like(v, float("-inf")), v)            # NaN only: +inf stays +inf
     kk = min(k, v.numel())
     top_v = torch.full((k,), float("-inf"), dtype=torch.float64, device=dev)
     top_i = torch.full((k,), -1, dtype=torch.int64, device=dev)
