@@ -56,6 +56,7 @@ def test_fleet_topk_and_scalars_device_one_gpu():
     rng = np.random.default_rng(5)
     v = rng.integers(0, 9, 400).astype(np.float64)
     v[rng.random(400) < 0.1] = np.nan
+    v[17], v[301] = np.inf, -np.inf                       # infinities are values, only NaN means "no value"
     tv, ti = fleet.fleet_topk_device(torch.from_numpy(v).cuda(), 1000, 10)
     keys = np.where(np.isnan(v), -np.inf, v)
     order = np.argsort(-keys, kind="stable")[:10]         # value descending, index ascending among ties
