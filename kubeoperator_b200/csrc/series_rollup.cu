@@ -229,16 +229,8 @@ __device__ __forceinline__ void warp_sort_keys(unsigned long long (&r)[K], int l
     }
 }
 template <int K>
-__device__ __forceinline__ void small_sorted_quantiles(const SeriesArgs& a, const double* v, int L, unsigned nv,
+__device__ __forceinline__ void small_sorted_quantiles(const SeriesArgs& a, unsigned long long (&r)[K], unsigned nv,
                                                        int64_t sid, int lane) {
-    unsigned long long r[K];
-#pragma unroll
-    for (int e = 0; e < K; ++e) {
-        const int i = lane + 32 * e;   // coalesced; which register holds which sample does not matter before the sort
-        double x = __longlong_as_double(0x7FF8000000000000LL);
-        if (i < L) x = ko_ld_stream(v + i);
-        r[e] = (x == x) ? ko_okey(x + 0.0) : KO_KEY_NAN;
-    }
     warp_sort_keys<K>(r, lane);
 #pragma unroll
     for (int j = 0; j < NI_MAX; ++j) {
@@ -257,22 +249,236 @@ __device__ __forceinline__ void small_sorted_quantiles(const SeriesArgs& a, cons
     }
 }
 
-__global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_small[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t sid = (int64_t)blockIdx.x * 8 + warp;
-    if (sid >= a.n_series) return;
-    const int64_t off0 = a.offsets[sid];
-    const int64_t Ll = a.offsets[sid + 1] - off0;
-    if (Ll > SMALL_MAX || Ll < 0) return;
-    const int L = (int)Ll;
-    const double* v = a.values + off0;
-    unsigned long long* keys = nullptr;
-    unsigned* hist = nullptr;
-    if (a.nq > 0) {
-        keys = reinterpret_cast<unsigned long long*>(smem_small) + (size_t)warp * SMALL_MAX;
-        hist = reinterpret_cast<unsigned*>(smem_small + (size_t)8 * SMALL_MAX * 8) + warp * HBINS;
+// Windows of 33 .. 256 samples: one pass of a 256-bin histogram over the span [min, max] of the series' keys finds the
+// bin of every wanted rank (bins are equal power-of-two ranges of key space, so the map is monotone); the few keys of
+// that bin are compacted with ballots and the one with the wanted rank among them is picked by counting.  A bin with
+// more than 32 keys (tie levels, clusters) sends the series to the register sort above.  scratch: 256 bins + 32 keys.
+constexpr int SMALL_SCRATCH_BYTES = HBINS * 4 + 32 * 8;
+template <int K>
+__device__ __forceinline__ void small_hist_quantiles(const SeriesArgs& a, unsigned long long (&k)[K], unsigned nv,
+                                                     double mn, double mx, int64_t sid, int lane,
+                                                     unsigned char* scratch) {
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    if (nv == 0 || mn == mx) {   // no valid sample / one distinct value (-0 and +0 both give +0, as everywhere)
+        if (lane < a.nq) a.out_quant[sid * a.nq + lane] = nv == 0 ? nan : mn + 0.0;
+        return;
     }
+    unsigned* hist = reinterpret_cast<unsigned*>(scratch);
+    unsigned long long* cand = reinterpret_cast<unsigned long long*>(scratch + HBINS * 4);
+    const unsigned long long kmin = ko_okey(mn + 0.0), diff = ko_okey(mx + 0.0) - kmin;
+    const int sh = max(0, 56 - __clzll((long long)diff));   // (diff >> sh) <= 255
+    reinterpret_cast<uint4*>(hist)[lane * 2] = make_uint4(0u, 0u, 0u, 0u);
+    reinterpret_cast<uint4*>(hist)[lane * 2 + 1] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    unsigned bin[K];
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        bin[e] = k[e] != KO_KEY_NAN ? (unsigned)((k[e] - kmin) >> sh) : 0xFFFFu;
+        if (bin[e] < (unsigned)HBINS) red_shared_add(&hist[bin[e]], 1u);
+    }
+    __syncwarp();
+    const uint4 h0 = reinterpret_cast<const uint4*>(hist)[lane * 2], h1 = reinterpret_cast<const uint4*>(hist)[lane * 2 + 1];
+    const unsigned c[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += c[i];
+    unsigned incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+#pragma unroll 1
+    for (int j = 0; j < a.nq; ++j) {
+        const unsigned p = nearest_rank_dev(nv, a.q[j]) - 1u;   // 0-based rank
+        const unsigned bal = __ballot_sync(0xffffffffu, incl > p);
+        const int src = __ffs(bal) - 1;                          // nv > p: some lane has it
+        unsigned b = 0, before = 0, cnt = 0;
+        if (lane == src) {
+            unsigned run = incl - s;
+            bool found = false;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (!found && run + c[i] > p) {
+                    b = (unsigned)(lane * 8 + i);
+                    before = run;
+                    cnt = c[i];
+                    found = true;
+                }
+                run += c[i];
+            }
+        }
+        b = __shfl_sync(0xffffffffu, b, src);
+        before = __shfl_sync(0xffffffffu, before, src);
+        cnt = __shfl_sync(0xffffffffu, cnt, src);
+        if (cnt > 32u) {   // warp-uniform: sort the whole series instead (writes every quantile)
+            small_sorted_quantiles<K>(a, k, nv, sid, lane);
+            return;
+        }
+        unsigned base = 0;
+#pragma unroll
+        for (int e = 0; e < K; ++e) {
+            const bool hit = bin[e] == b;
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (hit) cand[base + __popc(m & ((1u << lane) - 1u))] = k[e];
+            base += __popc(m);
+        }
+        __syncwarp();
+        const unsigned rho = p - before;   // 0-based rank inside the bin
+        const unsigned long long mine = lane < (int)cnt ? cand[lane] : KO_KEY_NAN;
+        int less = 0;
+#pragma unroll 1
+        for (unsigned i = 0; i < cnt; ++i) less += cand[i] < mine ? 1 : 0;
+        // the wanted key is the one with the most keys below it among those with at most rho below (ties share a count)
+        const int best = (lane < (int)cnt && (unsigned)less <= rho) ? less : -1;
+        const int top = __reduce_max_sync(0xffffffffu, best);
+        const int owner = __ffs(__ballot_sync(0xffffffffu, best == top)) - 1;
+        const unsigned long long key = __shfl_sync(0xffffffffu, mine, owner);
+        if (lane == 0) a.out_quant[sid * a.nq + a.qcol[j]] = ko_key2d(key);
+        __syncwarp();   // cand is reused by the next quantile
+    }
+}
+
+// One series of at most 32 * K samples by one warp: the samples are loaded once, K per lane, and stay in registers
+// for the statistics and for the quantiles.
+template <int K>
+__device__ __forceinline__ void small_one(const SeriesArgs& a, const double* v, int L, int64_t sid, int lane,
+                                          unsigned char* scratch) {
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    double x[K];
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        const int i = lane + 32 * e;
+        x[e] = i < L ? ko_ld_stream(v + i) : nan;
+    }
+    double sum = 0.0, mn = INFINITY, mx = -INFINITY, lastv = nan;
+    unsigned nv = 0;
+    int last_idx = -1;
+#pragma unroll
+    for (int e = 0; e < K; ++e) {
+        if (x[e] == x[e]) {
+            sum += x[e];
+            nv++;
+            last_idx = lane + 32 * e;
+            lastv = x[e];
+        }
+        mn = fmin(mn, x[e]);
+        mx = fmax(mx, x[e]);
+    }
+    sum = warp_sum(sum);
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    nv = warp_sum_u(nv);
+    const int last_all = __reduce_max_sync(0xffffffffu, last_idx);
+    const int owner = __ffs(__ballot_sync(0xffffffffu, last_idx == last_all)) - 1;
+    lastv = __shfl_sync(0xffffffffu, lastv, owner);
+    if (lane == 0) {
+        if (a.out_sum) a.out_sum[sid] = sum;
+        if (a.out_mean) a.out_mean[sid] = nv > 0 ? sum / (double)nv : 0.0;
+        if (a.out_min) a.out_min[sid] = nv > 0 ? mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = nv > 0 ? mx + 0.0 : nan;
+        if (a.out_last) a.out_last[sid] = last_all >= 0 ? lastv : nan;
+        if (a.out_count) a.out_count[sid] = (int64_t)nv;
+    }
+    if (a.nq == 0 || !a.out_quant) return;
+    unsigned long long k[K];
+#pragma unroll
+    for (int e = 0; e < K; ++e) k[e] = (x[e] == x[e]) ? ko_okey(x[e] + 0.0) : KO_KEY_NAN;
+    if (K == 1) small_sorted_quantiles<K>(a, k, nv, sid, lane);
+    else small_hist_quantiles<K>(a, k, nv, mn, mx, sid, lane, scratch);
+}
+
+// Four series of at most 32 samples side by side in one warp, eight lanes each (alert-rule windows: 20 samples =
+// 5 min at 15 s).  Lane sl of a group holds samples sl, sl + 8, sl + 16, sl + 24 (loaded by the caller, NaN beyond the
+// series).  Quantiles by counting: for every key the number of keys of its series below it; the key wanted for
+// 0-based rank p is the one with the largest such count <= p.
+__device__ __forceinline__ void small_quad(const SeriesArgs& a, int64_t sid, bool valid, const double (&x)[4], int Lmax,
+                                           int lane) {
+    const int sl = lane & 7;
+    const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    double sum = 0.0, mn = INFINITY, mx = -INFINITY, lastv = nan;
+    unsigned nv = 0;
+    int last_idx = -1;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        if (x[e] == x[e]) {
+            sum += x[e];
+            nv++;
+            last_idx = sl + 8 * e;
+            lastv = x[e];
+        }
+        mn = fmin(mn, x[e]);
+        mx = fmax(mx, x[e]);
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {   // stays inside the aligned group of eight lanes
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        nv += __shfl_xor_sync(0xffffffffu, nv, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, last_idx, o);
+        const double ov = __shfl_xor_sync(0xffffffffu, lastv, o);
+        if (oi > last_idx) {
+            last_idx = oi;
+            lastv = ov;
+        }
+    }
+    if (valid && sl == 0) {
+        if (a.out_sum) a.out_sum[sid] = sum;
+        if (a.out_mean) a.out_mean[sid] = nv > 0 ? sum / (double)nv : 0.0;
+        if (a.out_min) a.out_min[sid] = nv > 0 ? mn + 0.0 : nan;
+        if (a.out_max) a.out_max[sid] = nv > 0 ? mx + 0.0 : nan;
+        if (a.out_last) a.out_last[sid] = last_idx >= 0 ? lastv : nan;
+        if (a.out_count) a.out_count[sid] = (int64_t)nv;
+    }
+    if (a.nq == 0 || !a.out_quant) return;
+    unsigned long long k[4];
+    int less[4] = {0, 0, 0, 0};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) k[e] = (x[e] == x[e]) ? ko_okey(x[e] + 0.0) : KO_KEY_NAN;
+    const int ne = (Lmax + 7) >> 3;   // rows of eight that hold samples somewhere in the warp
+#pragma unroll
+    for (int ee = 0; ee < 4; ++ee) {
+        if (ee < ne) {
+#pragma unroll
+            for (int src = 0; src < 8; ++src) {
+                const unsigned long long kj = __shfl_sync(0xffffffffu, k[ee], src, 8);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) less[e] += kj < k[e] ? 1 : 0;
+            }
+        }
+    }
+#pragma unroll 1
+    for (int j = 0; j < a.nq; ++j) {
+        const int p = nv > 0 ? (int)nearest_rank_dev(nv, a.q[j]) - 1 : -1;
+        int best = -1;
+        unsigned long long bk = KO_KEY_NAN;
+#pragma unroll
+        for (int e = 0; e < 4; ++e)   // (stale samples and empty slots have nv keys below them: never <= p)
+            if (less[e] <= p && less[e] > best) {
+                best = less[e];
+                bk = k[e];
+            }
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) {
+            const int ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bk, o);
+            if (ob > best) {
+                best = ob;
+                bk = ok;
+            }
+        }
+        if (valid && sl == 0) a.out_quant[sid * a.nq + a.qcol[j]] = nv > 0 ? ko_key2d(bk) : nan;
+    }
+}
+
+// Statistics of one series of at most SMALL_MAX samples by one warp, keys to shared memory (series_medium).
+struct SmallStats {
+    double sum, mn, mx;
+    unsigned nv;
+};
+__device__ __forceinline__ SmallStats small_stats(const SeriesArgs& a, const double* v, int L, int64_t sid, int lane,
+                                                  unsigned long long* keys) {
     double sum = 0.0, mn = INFINITY, mx = -INFINITY;
     unsigned nv = 0;
     int last_idx = -1;
@@ -286,7 +492,7 @@ __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
         }
         mn = fmin(mn, x);
         mx = fmax(mx, x);
-        if (keys && L > 256) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
+        if (keys) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
     }
     sum = warp_sum(sum);
     mn = warp_min(mn);
@@ -303,18 +509,95 @@ __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
         if (a.out_last) a.out_last[sid] = last_idx >= 0 ? v[last_idx] : nan;
         if (a.out_count) a.out_count[sid] = (int64_t)nv;
     }
-    if (a.nq > 0 && a.out_quant && L <= 256) {   // sorted in registers (the samples are re-read: they sit in L1)
-        if (L <= 32) small_sorted_quantiles<1>(a, v, L, nv, sid, lane);
-        else if (L <= 64) small_sorted_quantiles<2>(a, v, L, nv, sid, lane);
-        else if (L <= 128) small_sorted_quantiles<4>(a, v, L, nv, sid, lane);
-        else small_sorted_quantiles<8>(a, v, L, nv, sid, lane);
-    } else if (a.nq > 0 && a.out_quant) {
+    SmallStats st = {sum, mn, mx, nv};
+    return st;
+}
+
+// Series of at most SMALL_SHORT samples: SMALL_PER_WARP consecutive series per warp.  When all of them have at most 32
+// samples they are computed four at a time side by side (small_quad), the loads of all of them issued before the
+// first is used; else one after the other by the whole warp (small_one).  Longer series are skipped here.
+constexpr int SMALL_SHORT = 256;
+constexpr int SMALL_PER_WARP = 16;
+__global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_small[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t sid0 = ((int64_t)blockIdx.x * 8 + warp) * SMALL_PER_WARP;
+    if (sid0 >= a.n_series) return;
+    // lane l < 17 holds offsets[sid0 + l] (clamped to the batch)
+    int64_t off_l = 0;
+    {
+        const int64_t i = sid0 + lane;
+        off_l = a.offsets[i <= a.n_series ? i : a.n_series];
+    }
+    const int64_t len_l = __shfl_down_sync(0xffffffffu, off_l, 1) - off_l;   // lanes 0..15: the series' lengths
+    const bool mine_short = lane >= SMALL_PER_WARP || sid0 + lane >= a.n_series || (len_l >= 0 && len_l <= 32);
+    if (__all_sync(0xffffffffu, mine_short)) {
+        int Lmax = (lane < SMALL_PER_WARP && sid0 + lane < a.n_series) ? (int)len_l : 0;
+        Lmax = __reduce_max_sync(0xffffffffu, Lmax);
+        const int g = lane >> 3, sl = lane & 7;
+        const double nan = __longlong_as_double(0x7FF8000000000000LL);
+        double x[SMALL_PER_WARP / 4][4];
+#pragma unroll
+        for (int qd = 0; qd < SMALL_PER_WARP / 4; ++qd) {
+            const int64_t sid = sid0 + qd * 4 + g;
+            const int64_t off = __shfl_sync(0xffffffffu, off_l, qd * 4 + g);
+            const int Lg = (int)__shfl_sync(0xffffffffu, len_l, qd * 4 + g);   // (every lane takes part)
+            const int L = sid < a.n_series ? Lg : 0;
+            const double* v = a.values + off;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int i = sl + 8 * e;
+                x[qd][e] = i < L ? ko_ld_stream(v + i) : nan;
+            }
+        }
+#pragma unroll
+        for (int qd = 0; qd < SMALL_PER_WARP / 4; ++qd) {
+            const int64_t sid = sid0 + qd * 4 + g;
+            small_quad(a, sid, sid < a.n_series, x[qd], Lmax, lane);
+        }
+        return;
+    }
+    unsigned char* scratch = smem_small + (size_t)warp * SMALL_SCRATCH_BYTES;
+#pragma unroll 1
+    for (int gg = 0; gg < SMALL_PER_WARP; ++gg) {
+        const int64_t s1 = sid0 + gg;
+        const int64_t o1 = __shfl_sync(0xffffffffu, off_l, gg), L1 = __shfl_sync(0xffffffffu, len_l, gg);
+        if (s1 >= a.n_series || L1 < 0 || L1 > SMALL_SHORT) continue;   // warp-uniform
+        const int L = (int)L1;
+        const double* v = a.values + o1;
+        if (L <= 32) small_one<1>(a, v, L, s1, lane, scratch);
+        else if (L <= 64) small_one<2>(a, v, L, s1, lane, scratch);
+        else if (L <= 128) small_one<4>(a, v, L, s1, lane, scratch);
+        else small_one<8>(a, v, L, s1, lane, scratch);
         __syncwarp();
-        const unsigned long long kmin = ko_okey(mn + 0.0), kmax = ko_okey(mx + 0.0);
+    }
+}
+
+// Series of SMALL_SHORT + 1 .. SMALL_MAX samples: one warp per series, keys in shared memory, MSB-first radix select.
+__global__ void __launch_bounds__(256) series_medium(SeriesArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_small[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t sid = (int64_t)blockIdx.x * 8 + warp;
+    if (sid >= a.n_series) return;
+    const int64_t off0 = a.offsets[sid];
+    const int64_t Ll = a.offsets[sid + 1] - off0;
+    if (Ll > SMALL_MAX || Ll <= SMALL_SHORT) return;
+    const int L = (int)Ll;
+    const double* v = a.values + off0;
+    unsigned long long* keys = nullptr;
+    unsigned* hist = nullptr;
+    if (a.nq > 0) {
+        keys = reinterpret_cast<unsigned long long*>(smem_small) + (size_t)warp * SMALL_MAX;
+        hist = reinterpret_cast<unsigned*>(smem_small + (size_t)8 * SMALL_MAX * 8) + warp * HBINS;
+    }
+    const SmallStats st = small_stats(a, v, L, sid, lane, keys);
+    if (a.nq > 0 && a.out_quant) {
+        __syncwarp();
+        const unsigned long long kmin = ko_okey(st.mn + 0.0), kmax = ko_okey(st.mx + 0.0);
         for (int j = 0; j < a.nq; ++j) {
             double r = __longlong_as_double(0x7FF8000000000000LL);
-            if (nv > 0) {
-                unsigned rho = nearest_rank_dev(nv, a.q[j]);
+            if (st.nv > 0) {
+                unsigned rho = nearest_rank_dev(st.nv, a.q[j]);
                 r = ko_key2d(warp_radix_select(keys, L, rho, kmin, kmax, hist, lane));
             }
             if (lane == 0) a.out_quant[sid * a.nq + a.qcol[j]] = r;
@@ -1321,7 +1604,7 @@ int series_set_attributes(int device) {
     std::lock_guard<std::mutex> lk(g_attr_mu);
     if (g_attr_dev[device]) return KO_OK;
     KO_CUDA(cudaFuncSetAttribute(series_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LONG_SMEM_BYTES));
-    KO_CUDA(cudaFuncSetAttribute(series_small, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    KO_CUDA(cudaFuncSetAttribute(series_medium, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  8 * SMALL_MAX * 8 + 8 * HBINS * 4));
     KO_CUDA(ko_flow_set_attributes());
     g_attr_dev[device] = true;
@@ -1391,6 +1674,13 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
     return cudaGetLastError();
 }
 
+// The two kernels of the series that are not long: each skips the series that are not its own.
+static void launch_short_paths(const SeriesArgs& a, int64_t n_series, int nq, cudaStream_t st) {
+    series_small<<<(unsigned)((n_series + 8 * SMALL_PER_WARP - 1) / (8 * SMALL_PER_WARP)), 256, 8 * SMALL_SCRATCH_BYTES, st>>>(a);
+    const size_t medium_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
+    series_medium<<<(unsigned)((n_series + 7) / 8), 256, medium_smem, st>>>(a);
+}
+
 static int fill_args(SeriesArgs& a, const double* d_values, const int64_t* d_offsets, int64_t n_series,
                      const double* q, int nq, double* d_sum, double* d_mean, double* d_min, double* d_max,
                      double* d_last, int64_t* d_count, double* d_quant, int* d_scratch) {
@@ -1443,10 +1733,9 @@ int ko_series_launch(ko_ctx* ctx, const double* d_values, const int64_t* d_offse
     KO_CUDA(cudaMemsetAsync(d_scratch, 0, N_COUNTERS * sizeof(int), stream));
     const int cb = 256;
     classify_series<<<(unsigned)((n_series + cb - 1) / cb), cb, 0, stream>>>(a);
-    const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
-    series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, stream>>>(a);
+    launch_short_paths(a, n_series, nq, stream);
     KO_CUDA(cudaEventRecord(ctx->ev_k0, stream));
-    int launches = 2;
+    int launches = 3;
     void* spill = reinterpret_cast<unsigned char*>(d_scratch) + series_lists_bytes(n_series);
     KO_CUDA(launch_long_path(a, ctx->num_sms, n_series, spill, (size_t)ctx->num_sms * SPILL_MAX * 8, stream,
                              &launches, ctx->ev_p0, ctx->ev_p1));
@@ -1711,8 +2000,7 @@ extern "C" int ko_series_rollup_static(int device, const double* d_values, const
     // the array still holds the last call's cursors / flags / lists: the counters must start at zero
     KO_CUDA(cudaMemsetAsync(sd->scratch, 0, N_COUNTERS * sizeof(int), st));
     classify_series<<<(unsigned)((n_series + 255) / 256), 256, 0, st>>>(a);
-    const size_t small_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
-    series_small<<<(unsigned)((n_series + 7) / 8), 256, small_smem, st>>>(a);
+    launch_short_paths(a, n_series, nq, st);
     int launches = 0;
     // the lists are laid out for the call's n_series; the spill space starts behind the largest possible lists
     void* spill = reinterpret_cast<unsigned char*>(sd->scratch) + series_lists_bytes(KO_STATIC_MAX_SERIES);

@@ -281,6 +281,66 @@ def test_short_windows_config5(rollup):
         assert_series_parity(got, exp, values, offsets, ())
 
 
+def test_short_windows_every_length_ties_and_mixed_quads(rollup):
+    """series_small: four series of <= 32 samples side by side in one warp (eight lanes each), one warp per series
+    with the histogram select for 33..256 samples (register sort when a histogram bin holds more than 32 keys),
+    series_medium above.  Every length 0..300, tie-heavy / constant / NaN-heavy / infinite values, and batches whose
+    groups of four consecutive series mix short, medium and long ones."""
+    rng = np.random.default_rng(21)
+    qsets = ([0.5, 0.95, 0.99], [0.0, 1.0, 0.25, 0.75], [0.5])
+
+    def draw(L, mode):
+        if mode == 0:
+            v = rng.beta(2, 5, L) * 100.0
+        elif mode == 1:
+            v = rng.integers(0, 4, L).astype(np.float64)            # few distinct values: bins far above 32 keys
+        elif mode == 2:
+            v = np.full(L, 7.25)
+        elif mode == 3:
+            v = rng.normal(0.0, 1e-300, L)                           # tiny magnitudes, both signs, +-0 among them
+            v[rng.random(L) < 0.2] = 0.0
+            v[rng.random(L) < 0.1] = -0.0
+        elif mode == 4:
+            v = rng.normal(0.0, 1.0, L)
+            v[rng.random(L) < 0.05] = np.inf
+            v[rng.random(L) < 0.05] = -np.inf
+        else:
+            v = np.concatenate([np.full(L - L // 3, 50.0), 50.0 + rng.random(L // 3) * 1e-9])   # one crowded bin
+            rng.shuffle(v)
+        v[rng.random(L) < (0.6 if mode == 0 and L % 7 == 0 else 0.02)] = np.nan
+        return v
+
+    # 1. every length, every mode, uniform batches (all four series of a warp alike)
+    for mode in range(6):
+        lens = np.repeat(np.arange(0, 301), 2)
+        vals = [draw(int(L), mode) for L in lens]
+        values = np.concatenate(vals) if len(vals) else np.zeros(0)
+        offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        qs = qsets[mode % 3]
+        got = rollup.series_rollup(values, offsets, qs)
+        exp = c_oracle.series_rollup(values, offsets, qs, nthreads=8)
+        assert_series_parity(got, exp, values, offsets, qs)
+    # 2. lengths shuffled: a warp's four series mix <= 32, <= 256, <= 1024 and long ones; all-NaN and empty series
+    lens = np.concatenate([rng.integers(0, 33, 400), rng.integers(33, 257, 200), rng.integers(257, 1025, 60),
+                           rng.integers(1025, 3000, 12), [0, 0, 0, 1, 1, 32, 32, 33, 256, 257, 1024, 1025]])
+    rng.shuffle(lens)
+    vals = [draw(int(L), int(rng.integers(0, 6))) for L in lens]
+    for i in range(0, len(vals), 37):
+        vals[i][:] = np.nan
+    values = np.concatenate(vals)
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    got = rollup.series_rollup(values, offsets, QS)
+    exp = c_oracle.series_rollup(values, offsets, QS, nthreads=8)
+    assert_series_parity(got, exp, values, offsets, QS)
+    # 3. a batch of 20-sample windows whose count is not a multiple of four (last warp partly empty)
+    n, L = 1003, 20
+    values = rng.beta(2, 5, n * L)
+    offsets = np.arange(n + 1, dtype=np.int64) * L
+    got = rollup.series_rollup(values, offsets, QS)
+    exp = c_oracle.series_rollup(values, offsets, QS, nthreads=8)
+    assert_series_parity(got, exp, values, offsets, QS)
+
+
 def test_quantile_order_and_subsets(rollup):
     d = synth.make_series("c1", seed=8, max_series=12)
     for qs in ([0.99, 0.5], [0.5], [0.25, 0.25, 0.75, 0.1]):
