@@ -2,23 +2,21 @@
 // HBM.  BUILD-DEFINED semantics (oracle/rollup_oracle.py series_stats; include/korollup.h): the reference only
 // ships PromQL strings for range windows (core/apps/kubeops_api/prometheus_client.py:90-111).
 //
-// One persistent CTA per SM, 28 warps, warp-specialised; three series are in flight per CTA:
-//   PLANNER   (4 warps)  series k+1: strided pre-sample of up to 4096 points (2048 aligned pairs), two rounds of
+// One persistent CTA per SM, 32 warps, warp-specialised; three series are in flight per CTA:
+//   PLANNER   (8 warps)  series k+1: strided pre-sample of up to 8192 points (aligned runs of four), two rounds of
 //                        256-bin histograms over the 32-bit "high keys" (top half of the order-preserving image of
 //                        an f64) give, per wanted quantile, a key interval [A, A+W] that holds its rank with
 //                        ~3 sigma; heavy tie levels at the interval ends are listed so that they are counted instead
 //                        of stored.
-//   PRODUCER  (1 lane)   series k: cp.async.bulk (TMA, SASS UBLKCP) of 16 KB groups into a 6-group ring, completion
+//   PRODUCER  (1 lane)   series k: cp.async.bulk (TMA, SASS UBLKCP) of 16 KB groups into a 7-group ring, completion
 //                        on mbarrier transaction counts, groups asked into L2 ahead of the ring.
 //   STREAM    (15 warps) series k: each warp owns whole 4 KB stages.  Per sample: sum (f64), and on the high key
 //                        alone (integer pipe) the running-extreme / NaN filter, "count below A" per interval
-//                        (sub.cc / subc) and the in-interval test; the in-interval flags go to a bitmap ring
-//                        (vote.ballot).  Samples are never compared as doubles on the common path, and nothing
-//                        irregular happens here.
-//   COLLECTOR (4 warps)  series k, one ring group behind: reads the bitmaps of a scanned group, copies the flagged
-//                        samples from the ring to the candidate pool (shared memory, spilling to global scratch) and
-//                        only then hands the ring group back to the producer.
-//   FINISH    (4 warps)  series k-1: combines the warps' partial statistics, checks every interval by exact counts
+//                        (sub.cc / subc) and the in-interval test.  The in-interval flags stay in a register (16 per
+//                        lane and stage); after the stage's scan the warp reserves room for its flagged samples in
+//                        the candidate pool (one shared-memory atomic per stage; shared memory first, global spill
+//                        behind it), copies them there as 64-bit keys and hands the stage back to the producer.
+//   FINISH    (8 warps)  series k-1: combines the warps' partial statistics, checks every interval by exact counts
 //                        and selects the wanted order statistics among the candidates by 256-bin histogram refinement
 //                        in 64-bit key space; writes the outputs.
 // Whatever the plan cannot guarantee (a rank outside its interval, an overflowing pool, a pre-sample with almost no
@@ -30,18 +28,16 @@
 
 namespace {
 
-constexpr int F_NS = 11;                       // stream warps (28 warps: registers are granted per 4 warps)
+constexpr int F_NS = 15;                       // stream warps
 constexpr int F_NP = 8;                        // planner warps
-constexpr int F_NC = 4;                        // collector warps
 constexpr int F_NF = 8;                        // finish warps
-constexpr int F_WARPS = 1 + F_NP + F_NC + F_NF + F_NS;
-constexpr int F_THREADS = F_WARPS * 32;        // 896
+constexpr int F_WARPS = 1 + F_NP + F_NF + F_NS;
+constexpr int F_THREADS = F_WARPS * 32;        // 1024
 // The scheduler prefers the warp with the highest id: the serial roles (whose latency everything else waits for)
 // come last, the stream warps (throughput, always something to do) first.
 constexpr int F_W_STREAM = 0;                  // first stream warp
 constexpr int F_W_FIN = F_W_STREAM + F_NS;     // first finish warp
-constexpr int F_W_COLL = F_W_FIN + F_NF;       // first collector warp
-constexpr int F_W_PLAN = F_W_COLL + F_NC;      // first planner warp
+constexpr int F_W_PLAN = F_W_FIN + F_NF;       // first planner warp
 constexpr int F_W_PROD = F_W_PLAN + F_NP;      // the producer warp
 constexpr int F_STAGE = 512;                   // samples per ring stage (4 KB): 4 warp steps of 128 samples
 constexpr int F_STAGE_BYTES = F_STAGE * 8;
@@ -49,7 +45,6 @@ constexpr int F_GS = 4;                        // stages per ring group: one TMA
 constexpr int F_GROUP_BYTES = F_GS * F_STAGE_BYTES;
 constexpr int F_NGROUPS = 7;
 constexpr int F_NSTAGES = F_NGROUPS * F_GS;
-constexpr int F_BG = 8;                        // groups of the bitmap ring (64 words each)
 constexpr int F_PF = 8;                        // groups asked into L2 ahead of the ring
 constexpr int F_ND = 4;                        // series slots (descriptor + plan + partials)
 constexpr int F_SMAX = 8192;                   // largest pre-sample (30-day series)
@@ -64,9 +59,8 @@ constexpr uint32_t HK_NINF = 0x000FFFFFu;      // high key of -inf; anything bel
 constexpr uint32_t HK_NONE = 0xFFFFFFFFu;      // a sample that takes no part (stale or outside the series)
 constexpr uint32_t HK_UNUSED = 0xFFFFFFFEu;    // A of an unused interval (W = 0): no key equals it, HK_NONE is above
 
-enum { FB_FULL = 0, FB_EMPTY = FB_FULL + F_NGROUPS, FB_BMFULL = FB_EMPTY + F_NGROUPS, FB_BMEMPTY = FB_BMFULL + F_BG,
-       FB_DESC = FB_BMEMPTY + F_BG, FB_PLAN = FB_DESC + F_ND, FB_FREE = FB_PLAN + F_ND, FB_SDONE = FB_FREE + F_ND,
-       FB_CDONE = FB_SDONE + F_ND, FB_START = FB_CDONE + F_ND, FB_COUNT = FB_START + F_ND };
+enum { FB_FULL = 0, FB_EMPTY = FB_FULL + F_NGROUPS, FB_DESC = FB_EMPTY + F_NGROUPS, FB_PLAN = FB_DESC + F_ND,
+       FB_FREE = FB_PLAN + F_ND, FB_SDONE = FB_FREE + F_ND, FB_START = FB_SDONE + F_ND, FB_COUNT = FB_START + F_ND };
 
 struct alignas(16) FlowSlot {
     // descriptor (planner thread 0)
@@ -174,8 +168,7 @@ constexpr size_t FO_LUT = FO_HIST2 + (size_t)F_NT * 256 * 4;
 constexpr size_t FO_FBINS = FO_LUT + 256;
 constexpr size_t FO_FLISTK = FO_FBINS + (size_t)NI_MAX * 256 * 4;
 constexpr size_t FO_FLISTM = FO_FLISTK + (size_t)NI_MAX * F_LIST * 8;
-constexpr size_t FO_BITMAP = FO_FLISTM + (size_t)NI_MAX * F_LIST * 4;
-constexpr size_t FO_SLOTS = FO_BITMAP + (size_t)F_BG * F_GS * 64;
+constexpr size_t FO_SLOTS = FO_FLISTM + (size_t)NI_MAX * F_LIST * 4;
 constexpr size_t FO_PART = FO_SLOTS + align_up(F_ND * sizeof(FlowSlot), 16);
 constexpr size_t FO_PS = FO_PART + (size_t)F_ND * F_NS * sizeof(FlowPartial);
 constexpr size_t FO_FS = FO_PS + align_up(sizeof(PlanScratch), 16);
@@ -198,7 +191,6 @@ struct FlowSmem {
     __device__ __forceinline__ unsigned* fbins() const { return reinterpret_cast<unsigned*>(base + FO_FBINS); }
     __device__ __forceinline__ unsigned long long* flistk() const { return reinterpret_cast<unsigned long long*>(base + FO_FLISTK); }
     __device__ __forceinline__ unsigned* flistm() const { return reinterpret_cast<unsigned*>(base + FO_FLISTM); }
-    __device__ __forceinline__ unsigned char* bitmap() const { return base + FO_BITMAP; }
     __device__ __forceinline__ FlowSlot* slot(int d) const { return reinterpret_cast<FlowSlot*>(base + FO_SLOTS) + d; }
     __device__ __forceinline__ FlowPartial* part(int d, int w) const {
         return reinterpret_cast<FlowPartial*>(base + FO_PART) + d * F_NS + w;
@@ -721,7 +713,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
 
 // ------------------------------------------------------------------------------------------------ stream
 struct StreamAcc {
-    double s0, s1, s2, s3, mn, mx;
+    double s0, s1, mn, mx;
     uint32_t rlo, rhi;       // fast path while every high key lies strictly between them
     unsigned nan;
     unsigned c[NI_MAX];      // MINUS the number of samples below A[i] (see stream_step)
@@ -737,8 +729,8 @@ __device__ __forceinline__ void acc_bounds(StreamAcc& acc) {
 // NI intervals.  addr: the lane's 16 bytes of the first step.  Slots of a stage that lie outside the series have been
 // overwritten with NaN before (patch_stage_edges), so every slot is either a sample or NaN here.
 template <int NI>
-__device__ __forceinline__ void stream_step2(uint32_t addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
-                                             const uint32_t (&W)[NI_MAX], uint32_t bm_addr, int lane) {
+__device__ __forceinline__ uint32_t stream_step2(uint32_t addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
+                                                 const uint32_t (&W)[NI_MAX]) {
     double x[8];
     lds_v2f64(addr, x[0], x[1]);
     lds_v2f64(addr + 512u, x[2], x[3]);
@@ -783,16 +775,11 @@ __device__ __forceinline__ void stream_step2(uint32_t addr, StreamAcc& acc, cons
             acc_bounds(acc);
         }
     }
-    acc.s0 += x[0];
-    acc.s1 += x[1];
-    acc.s2 += x[2];
-    acc.s3 += x[3];
-    acc.s0 += x[4];
-    acc.s1 += x[5];
-    acc.s2 += x[6];
-    acc.s3 += x[7];
+    // (pairwise inside the step, two running sums: short dependent chains without more live registers)
+    acc.s0 += (x[0] + x[2]) + (x[4] + x[6]);
+    acc.s1 += (x[1] + x[3]) + (x[5] + x[7]);
+    uint32_t m = 0u;   // bit e: sample e of this lane lies in one of the intervals
     if (NI > 0) {
-        uint32_t b[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             bool q = false;
@@ -804,21 +791,104 @@ __device__ __forceinline__ void stream_step2(uint32_t addr, StreamAcc& acc, cons
                 asm("sub.cc.u32 %0, %2, %3;\n\tsubc.u32 %1, %1, 0;" : "=r"(d), "+r"(acc.c[i]) : "r"(k[e]), "r"(A[i]));
                 q = q || (d <= W[i]);
             }
-            b[e] = __ballot_sync(0xffffffffu, q);
-        }
-        if (lane == 0) {
-            sts_v4u32(bm_addr, b[0], b[1], b[2], b[3]);
-            sts_v4u32(bm_addr + 16u, b[4], b[5], b[6], b[7]);
+            m |= q ? (1u << e) : 0u;
         }
     }
+    return m;
 }
 
+// One stage: returns the lane's 16 in-interval flags.  Bit b = t * 8 + e flags the sample at stage offset
+// (b >> 1) * 64 + lane * 2 + (b & 1): sample e of step t sits at t * 256 + (e >> 1) * 64 + lane * 2 + (e & 1).
 template <int NI>
-__device__ __forceinline__ void stream_stage(uint32_t stage_addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
-                                             const uint32_t (&W)[NI_MAX], uint32_t bm_addr, int lane) {
+__device__ __forceinline__ uint32_t stream_stage(uint32_t stage_addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
+                                                 const uint32_t (&W)[NI_MAX], int lane) {
+    uint32_t m = 0u;
 #pragma unroll 1
     for (int t = 0; t < 2; ++t)
-        stream_step2<NI>(stage_addr + (uint32_t)t * 2048u + (uint32_t)lane * 16u, acc, A, W, bm_addr + t * 32u, lane);
+        m |= stream_step2<NI>(stage_addr + (uint32_t)t * 2048u + (uint32_t)lane * 16u, acc, A, W) << (t * 8);
+    return m;
+}
+// byte offset (from the lane's first sample of the stage) of the sample that flag bit b stands for
+__device__ __forceinline__ uint32_t flag_offset(int b) { return (uint32_t)(b >> 1) * 512u + (uint32_t)(b & 1) * 8u; }
+
+// The flagged samples of one scanned stage go to the series' candidate pool as 64-bit keys: room for all of the
+// warp's candidates is reserved with one atomic on the slot's cursor (shared-memory window first - when the finish
+// warps have released it - then the global spill window), then every lane copies its own.  Samples on a listed tie
+// level are counted instead.  flags: bit 0 = the shared-memory window is ours, bit 1 = something did not fit,
+// bit 2 = something went to the spill.
+__device__ __forceinline__ void store_candidates(const SeriesArgs& a, const FlowSmem& sm, bool single, uint32_t kser,
+                                                 uint32_t stage_addr, uint32_t m, int lane, uint32_t& flags) {
+    // (everything but the flags is looked up again here: the scan loop around this call has no registers to spare)
+    const PoolWin pw = pool_window(single, kser, a.spill_cap);
+    const FlowSlot* sl = sm.slot(pw.d);
+    unsigned long long* spill = a.spill + (size_t)blockIdx.x * (size_t)a.spill_cap;
+    const int nheavy = sl->nheavy;
+    if (nheavy > 0) {
+        uint32_t rest = m;
+#pragma unroll 1
+        while (rest) {
+            const int b = __ffs(rest) - 1;
+            rest &= rest - 1;
+            const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lane * 16u + flag_offset(b)) + 0.0);
+            int hit = -1;
+#pragma unroll 1
+            for (int h = 0; h < nheavy; ++h) hit = sl->heavy[h] == key ? h : hit;
+            if (hit >= 0) {
+                red_shared_add(&sm.hcnt()[pw.d * F_NH + hit], 1u);
+                m &= ~(1u << b);
+            }
+        }
+        if (!__any_sync(0xffffffffu, m != 0u)) return;
+    }
+    const unsigned n = __popc(m);
+    if (!(flags & 1u)) {   // shared-memory window not released yet: spill, or wait when the spill is full
+        volatile unsigned* rel = reinterpret_cast<volatile unsigned*>(&sm.rel()[pw.win]);
+        bool ok = *rel >= pw.use;
+        if (!ok && *reinterpret_cast<volatile unsigned*>(&sm.cgl()[pw.d]) + 512u > pw.g_cap) {
+            while (*rel < pw.use) __nanosleep(200);
+            ok = true;
+        }
+        if (ok) flags |= 1u;
+        __threadfence_block();
+    }
+    if (n == 0u) return;
+    // Every lane reserves room for its own candidates: one atomic instruction for the warp (lanes that hit the same
+    // cursor are serialised by the hardware, which is cheaper than a prefix sum over the warp plus a broadcast).
+    // Shared-memory entries first (when the window is ours), whatever does not fit goes to the spill.
+    unsigned sbase = pw.s_cap, gbase_i = 0;
+    if (flags & 1u) sbase = atom_shared_add(&sm.csm()[pw.d], n);
+    const unsigned take = sbase < pw.s_cap ? min(n, pw.s_cap - sbase) : 0u;
+    if (take < n) {
+        gbase_i = atom_shared_add(&sm.cgl()[pw.d], n - take);
+        flags |= 4u;
+    }
+    unsigned long long* wb = sm.pool() + pw.s_base + sbase;
+    unsigned long long* gb = spill + pw.g_base + gbase_i;
+    const uint32_t lane_addr = stage_addr + (uint32_t)lane * 16u;
+    const bool to_pool = take == n, to_spill = take == 0u && gbase_i + n <= pw.g_cap;
+    if (to_pool || to_spill) {   // all of the lane's candidates go to one place (nearly always)
+        unsigned long long dst;
+        asm volatile("mov.u64 %0, %1;" : "=l"(dst) : "l"(to_pool ? wb : gb));
+#pragma unroll 1
+        while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            st_generic_u64(dst, ko_okey(lds_f64(lane_addr + flag_offset(b)) + 0.0));
+            dst += 8ull;
+        }
+    } else {
+        unsigned e = 0;
+#pragma unroll 1
+        while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            const unsigned long long key = ko_okey(lds_f64(lane_addr + flag_offset(b)) + 0.0);
+            if (e < take) wb[e] = key;
+            else if (gbase_i + (e - take) < pw.g_cap) gb[e - take] = key;
+            else flags |= 2u;
+            ++e;
+        }
+    }
 }
 
 // First / last stage of a series: the slots in front of the series (16-byte alignment) and behind its end hold
@@ -834,82 +904,48 @@ __device__ __forceinline__ void patch_stage_edges(uint32_t stage_addr, int lane,
 
 // Stage j of a series (ring stage g = g0 + j) belongs to stream warp j % F_NS and to ring group (g / F_GS) % F_NGROUPS.  A series
 // starts on a group boundary; the stage numbers that pad its last group are visited too (wait, release, no work),
-// so that every group gets its F_GS releases.  cg0: bitmap-ring group number of the series' first group (groups of
-// series without capture intervals do not use the bitmap ring and are not counted).
+// so that every group gets its F_GS releases.
 template <int NI>
-__device__ __forceinline__ void stream_series(const FlowSmem& sm, const FlowSlot* sl, StreamAcc& acc, int ws, int lane,
-                                              uint32_t cg0) {
+__device__ __forceinline__ void stream_series(const SeriesArgs& a, const FlowSmem& sm, const FlowSlot* sl, StreamAcc& acc,
+                                              int ws, int lane, bool single, uint32_t kser, uint32_t& flags) {
     uint32_t A[NI_MAX], W[NI_MAX];
 #pragma unroll
     for (int i = 0; i < NI_MAX; ++i) {
         A[i] = sl->A[i];
         W[i] = sl->W[i];
     }
-    const int L = sl->L, lead = sl->lead, n = sl->nstages;
+    const int n = sl->nstages;
     const int npad = (n + F_GS - 1) / F_GS * F_GS;
-    const uint32_t g0 = sl->g0;
-    const uint32_t bm0 = smem_u32(sm.bitmap());
     const uint32_t ring0 = smem_u32(sm.ring());
-    const uint32_t full0 = smem_u32(sm.bar(FB_FULL)), empty0 = smem_u32(sm.bar(FB_EMPTY));
-    const uint32_t bmfull0 = smem_u32(sm.bar(FB_BMFULL)), bmempty0 = smem_u32(sm.bar(FB_BMEMPTY));
+    const uint32_t empty0 = smem_u32(sm.bar(FB_EMPTY));
     FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
     // (stage j of a series always goes to stream warp j % F_NS, whatever the CTA did before: the partial sums of a
     // series, and with them the last bits of its sum, do not depend on how the work was distributed)
     for (int j = ws; j < npad; j += F_NS) {
-        const uint32_t g = g0 + (uint32_t)j;
+        const uint32_t g = *reinterpret_cast<const volatile uint32_t*>(&sl->g0) + (uint32_t)j;   // (reloaded: registers)
         const uint32_t grp = g / F_GS;
-        const uint32_t s = grp % F_NGROUPS, par = (grp / F_NGROUPS) & 1u;
+        const uint32_t s = grp % F_NGROUPS;
         const uint32_t stage_addr = ring0 + s * (uint32_t)F_GROUP_BYTES + (g % F_GS) * (uint32_t)F_STAGE_BYTES;
-        const uint32_t cgi = cg0 + (uint32_t)(j / F_GS);
-        const uint32_t bs = cgi % F_BG, buse = cgi / F_BG;
-        const uint32_t bm_addr = bm0 + bs * (uint32_t)(F_GS * 64) + (g % F_GS) * 64u;
         if (lane == 0 && ws < 3) FP(5 + ws, 0, 16 + j);
         wait_group_full(sm, grp);
         FT_MARK(32);   // stream warp 0: waiting for a full stage
-        // (after the ring wait: the bitmap slot's previous group is then known to be older than this one)
-        if (NI > 0 && buse > 0u) mbar_wait_addr(bmempty0 + bs * 8u, (buse - 1u) & 1u);   // the collector has read it
-        FT_MARK(34);   // stream warp 0: waiting for the bitmap slot
         if (j < n) {
             if (j == 0 || j == n - 1) {
-                const int end_valid = L + lead - j * F_STAGE;
+                const int lead = sl->lead;
+                const int end_valid = sl->L + lead - j * F_STAGE;
                 patch_stage_edges(stage_addr, lane, j == 0 ? lead : 0, end_valid < F_STAGE ? end_valid : F_STAGE);
             }
-            stream_stage<NI>(stage_addr, acc, A, W, bm_addr, lane);
-        } else if (NI > 0) {
-            if (lane < 16) sts_u32f(bm_addr + (uint32_t)lane * 4u, 0u);
+            const uint32_t m = stream_stage<NI>(stage_addr, acc, A, W, lane);
+            FT_MARK(33);   // stream warp 0: scan
+            if (NI > 0 && __any_sync(0xffffffffu, m != 0u)) store_candidates(a, sm, single, kser, stage_addr, m, lane, flags);
+            FT_MARK(34);   // stream warp 0: storing candidates
         }
-        FT_MARK(33);   // stream warp 0: scan
         __syncwarp();
-        if (lane == 0) {
-            mbar_arrive_addr(empty0 + s * 8u);
-            if (NI > 0) mbar_arrive_addr(bmfull0 + bs * 8u);
-        }
+        if (lane == 0) mbar_arrive_addr(empty0 + s * 8u);
     }
 }
 
 __device__ __forceinline__ double shfl_xor_f64(double v, int o) { return __shfl_xor_sync(0xffffffffu, v, o); }
-
-// ------------------------------------------------------------------------------------------------ collector
-// The flagged samples of one lane's two bitmap words (64 samples of one stage: words wi and wi + 1).
-// Bit b of word w flags the sample at stage offset (w >> 2) * 128 + ((w & 2) ? 64 : 0) + 2 * b + (w & 1).
-struct LaneBits {
-    uint32_t w0, w1;
-    __device__ __forceinline__ bool any() const { return (w0 | w1) != 0u; }
-    // offset (in samples, from the stage's first slot) of the next flagged sample; removes it
-    __device__ __forceinline__ int pop(int wi) {
-        int w, b;
-        if (w0) {
-            b = __ffs(w0) - 1;
-            w0 &= w0 - 1;
-            w = wi;
-        } else {
-            b = __ffs(w1) - 1;
-            w1 &= w1 - 1;
-            w = wi + 1;
-        }
-        return (w >> 2) * 128 + ((w & 2) ? 64 : 0) + 2 * b + (w & 1);
-    }
-};
 
 // ------------------------------------------------------------------------------------------------ finish
 // All finish threads (ftid in [0, 128)).  Returns nothing; outputs are written here.
@@ -1229,18 +1265,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
     if (tid == 0) {
         for (int s = 0; s < F_NGROUPS; ++s) {
             mbar_init(sm.bar(FB_FULL + s), 1);
-            mbar_init(sm.bar(FB_EMPTY + s), F_GS + 1);   // the four scanning warps and the group's collector
-        }
-        for (int s = 0; s < F_BG; ++s) {
-            mbar_init(sm.bar(FB_BMFULL + s), F_GS);
-            mbar_init(sm.bar(FB_BMEMPTY + s), 1);
+            mbar_init(sm.bar(FB_EMPTY + s), F_GS);   // the four warps that scan the group's stages
         }
         for (int d = 0; d < F_ND; ++d) {
             mbar_init(sm.bar(FB_DESC + d), 1);
             mbar_init(sm.bar(FB_PLAN + d), 1);
             mbar_init(sm.bar(FB_FREE + d), 1);
             mbar_init(sm.bar(FB_SDONE + d), F_NS);
-            mbar_init(sm.bar(FB_CDONE + d), F_NC);
             mbar_init(sm.bar(FB_START + d), 1);
         }
         mbar_fence_init();
@@ -1384,165 +1415,6 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             if (ptid == 0) FP(1, k, 5);
             if (ptid == 0) mbar_arrive(sm.bar(FB_PLAN + d));
         }
-    } else if (warp >= F_W_COLL) {
-        // =============================== COLLECTOR ===============================
-        // Ring group grp belongs to collector grp % F_NC.  With capture intervals: wait until the group's four
-        // stages are scanned (bitmaps full), copy the flagged samples from the ring to the pool window, release the
-        // bitmaps and the ring group.  Without: just hand the ring group back.
-        const int cw = warp - F_W_COLL;
-        uint32_t cg = 0;   // bitmap-ring group counter (groups of series with capture intervals)
-        const uint32_t bm0 = smem_u32(sm.bitmap());
-        const uint32_t ring0 = smem_u32(sm.ring());
-        FT_BEGIN(blockIdx.x == 0 && cw == 0 && lane == 0);
-        for (uint32_t k = 0;; ++k) {
-            const int d = (int)(k % F_ND);
-            const uint32_t par = (k / F_ND) & 1u;
-            FT_MARK(41);   // collector 0: working
-            if (lane == 0) FP(2 + (cw & 1), k, 1);
-            mbar_wait_sleep<200>(sm.bar(FB_PLAN + d), par);
-            if (lane == 0) FP(2 + (cw & 1), k, 2);
-            FT_MARK(40);   // collector 0: waiting for the plan
-            const FlowSlot* sl = sm.slot(d);
-            if (sl->sid < 0) break;
-            const PoolWin pw = pool_window(single, k, a.spill_cap);
-            const int ngroups = (sl->nstages + F_GS - 1) / F_GS;
-            const uint32_t grp0 = sl->g0 / F_GS;
-            const int ni = sl->ni, nheavy = sl->nheavy;
-            unsigned long long hkey[F_NH];   // the listed tie levels, in registers (~0 never equals a key)
-#pragma unroll
-            for (int h = 0; h < F_NH; ++h) hkey[h] = h < nheavy ? sl->heavy[h] : ~0ull;
-            // the shared-memory window was last used by series k - 1 (one pool) or k - 2 (two halves); until the
-            // finish warps have released it this series' candidates go to the spill window
-            bool pool_ok = pw.use == 0u;
-            bool over = false, spilled = false;
-            int gi = (int)(((uint32_t)cw + F_NC - (grp0 % F_NC)) % F_NC);
-            for (; gi < ngroups; gi += F_NC) {
-                const uint32_t grp = grp0 + (uint32_t)gi;
-                const uint32_t s = grp % F_NGROUPS, u = grp / F_NGROUPS;
-                if (lane == 0) FP(2 + (cw & 1), k, 16 + gi);
-                if (ni == 0) {
-                    wait_group_full(sm, grp);   // the group's phase has begun
-                    if (lane == 0) mbar_arrive(sm.bar(FB_EMPTY + s));
-                    continue;
-                }
-                const uint32_t cgi = cg + (uint32_t)gi;
-                const uint32_t bs = cgi % F_BG, buse = cgi / F_BG;
-                // Order matters: a parity wait only tells this phase from the previous one.  Once the ring group is
-                // full, every earlier group has been handed back (the producer loads in order), so the bitmap slot's
-                // previous use is over and the second wait cannot mistake it for this one.
-                wait_group_full(sm, grp);
-                mbar_wait_sleep<100>(sm.bar(FB_BMFULL + bs), buse & 1u);
-                FT_MARK(42);   // collector 0: waiting for bitmaps
-                LaneBits lb;
-                lds_v2u32(bm0 + bs * (uint32_t)(F_GS * 64) + (uint32_t)lane * 8u, lb.w0, lb.w1);
-                // lane: stage lane / 8 of the group, words (lane % 8) * 2 and + 1 of that stage
-                const uint32_t stage_addr = ring0 + s * (uint32_t)F_GROUP_BYTES + (uint32_t)(lane >> 3) * F_STAGE_BYTES;
-                const int wi = (lane & 7) * 2;
-                if (__any_sync(0xffffffffu, lb.any())) {
-                    // (compact loops on purpose: this code must stay in the instruction cache beside the scan loop)
-                    if (nheavy > 0) {   // samples on a listed tie level are counted, not stored
-                        LaneBits rest = lb;
-                        uint32_t k0 = lb.w0, k1 = lb.w1;
-#pragma unroll 1
-                        while (rest.any()) {
-                            const uint32_t p0 = rest.w0, p1 = rest.w1;
-                            const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)rest.pop(wi) * 8u) + 0.0);
-                            int hit = -1;
-#pragma unroll
-                            for (int h = 0; h < F_NH; ++h) hit = hkey[h] == key ? h : hit;
-                            if (hit >= 0) {
-                                red_shared_add(&sm.hcnt()[pw.d * F_NH + hit], 1u);
-                                k0 &= ~(p0 ^ rest.w0);   // clear the bit just popped
-                                k1 &= ~(p1 ^ rest.w1);
-                            }
-                        }
-                        lb.w0 = k0;
-                        lb.w1 = k1;
-                    }
-                    const unsigned n = __popc(lb.w0) + __popc(lb.w1);
-                    unsigned incl = n;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
-                        if (lane >= o) incl += t;
-                    }
-                    const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
-                    FT_MARK(43);   // collector 0: counting
-                    if (!pool_ok) {   // shared-memory window not released yet: spill, or wait when the spill is full
-                        volatile unsigned* rel = reinterpret_cast<volatile unsigned*>(&sm.rel()[pw.win]);
-                        pool_ok = *rel >= pw.use;
-                        if (!pool_ok && *reinterpret_cast<volatile unsigned*>(&sm.cgl()[pw.d]) + total > pw.g_cap) {
-                            while (*rel < pw.use) __nanosleep(200);
-                            pool_ok = true;
-                        }
-                        __threadfence_block();
-                    }
-                    // reserve: shared-memory entries first (when the window is ours), the rest in the spill
-                    unsigned sbase = pw.s_cap, gbase_i = 0;
-                    if (lane == 0) {
-                        if (pool_ok) sbase = atom_shared_add(&sm.csm()[pw.d], total);
-                        const unsigned in_s = sbase < pw.s_cap ? min(total, pw.s_cap - sbase) : 0u;
-                        if (in_s < total) gbase_i = atom_shared_add(&sm.cgl()[pw.d], total - in_s);
-                    }
-                    sbase = __shfl_sync(0xffffffffu, sbase, 0);
-                    gbase_i = __shfl_sync(0xffffffffu, gbase_i, 0);
-                    const unsigned take = sbase < pw.s_cap ? min(total, pw.s_cap - sbase) : 0u;
-                    spilled = spilled || take < total;
-                    unsigned e = incl - n;                                       // this lane's first entry of the batch
-                    unsigned long long* wb = sm.pool() + pw.s_base + sbase;
-                    unsigned long long* gb = spill + pw.g_base + gbase_i;
-                    FT_MARK(44);   // collector 0: reserving
-                    const bool to_pool = take == total, to_spill = take == 0 && gbase_i + total <= pw.g_cap;
-                    if (to_pool || to_spill) {
-                        // the whole batch goes to one place (all but one batch of a series): one candidate of each of
-                        // the lane's two words per round, two independent chains; the destination is a generic
-                        // address held in a register pair, so that nothing but the loop body is in the loop
-                        unsigned long long dst;
-                        asm volatile("mov.u64 %0, %1;" : "=l"(dst) : "l"(to_pool ? wb : gb));
-                        const uint32_t a0 = stage_addr + (uint32_t)((wi >> 2) * 128 + ((wi & 2) ? 64 : 0)) * 8u;
-                        uint32_t w0 = lb.w0, w1 = lb.w1;
-                        unsigned long long d0 = dst + (unsigned long long)e * 8ull;
-                        unsigned long long d1 = d0 + (unsigned long long)__popc(w0) * 8ull;
-#pragma unroll 1
-                        while (w0 | w1) {
-                            if (w0) {
-                                const int b = __ffs(w0) - 1;
-                                w0 &= w0 - 1;
-                                st_generic_u64(d0, ko_okey(lds_f64(a0 + (uint32_t)b * 16u) + 0.0));
-                                d0 += 8ull;
-                            }
-                            if (w1) {
-                                const int b = __ffs(w1) - 1;
-                                w1 &= w1 - 1;
-                                st_generic_u64(d1, ko_okey(lds_f64(a0 + 8u + (uint32_t)b * 16u) + 0.0));
-                                d1 += 8ull;
-                            }
-                        }
-                    } else {
-#pragma unroll 1
-                        while (lb.any()) {
-                            const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lb.pop(wi) * 8u) + 0.0);
-                            if (e < take) wb[e] = key;
-                            else if (gbase_i + (e - take) < pw.g_cap) gb[e - take] = key;
-                            else over = true;
-                            ++e;
-                        }
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive(sm.bar(FB_BMEMPTY + bs));
-                    mbar_arrive(sm.bar(FB_EMPTY + s));
-                }
-                FT_MARK(45);   // collector 0: storing candidates
-            }
-            if (ni > 0) cg += (uint32_t)ngroups;
-            over = __any_sync(0xffffffffu, over);
-            if (spilled) __threadfence();   // spilled keys: in L2 before the finish warps read them
-            if (lane == 0 && over) sm.ovf()[pw.d] = 1u;
-            __syncwarp();
-            if (lane == 0) mbar_arrive(sm.bar(FB_CDONE + d));
-        }
     } else if (warp >= F_W_FIN) {
         // =============================== FINISH ===============================
         const int ftid = tid - F_W_FIN * 32;
@@ -1559,9 +1431,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             if (sl->sid < 0) break;
             mbar_wait_sleep<400>(sm.bar(FB_SDONE + d), par);
             if (ftid == 0) FP(4, k, 3);
-            mbar_wait_sleep<400>(sm.bar(FB_CDONE + d), par);
-            if (ftid == 0) FP(4, k, 4);
-            FT_MARK(21);   // finish: waiting for the stream warps and the collectors
+            FT_MARK(21);   // finish: waiting for the stream warps
             const PoolWin pw = pool_window(single, k, a.spill_cap);
             finish_series(a, sm, sl, d, ftid, pw, spill);
             if (ftid == 0) FP(4, k, 5);
@@ -1574,7 +1444,6 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
     } else {
         // =============================== STREAM ===============================
         const int ws = warp - F_W_STREAM;
-        uint32_t cg = 0;   // bitmap-ring group counter, as in the collectors
         FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
         for (uint32_t k = 0;; ++k) {
             const int d = (int)(k % F_ND);
@@ -1590,8 +1459,6 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             StreamAcc acc;
             acc.s0 = 0.0;
             acc.s1 = 0.0;
-            acc.s2 = 0.0;
-            acc.s3 = 0.0;
             acc.mn = sl->mn_seed;
             acc.mx = sl->mx_seed;
             acc.nan = 0;
@@ -1599,16 +1466,21 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             for (int i = 0; i < NI_MAX; ++i) acc.c[i] = 0;
             acc_bounds(acc);
             const int ni = sl->ni;
+            // the shared-memory window was last used by series k - 1 (one pool) or k - 2 (two halves); until the
+            // finish warps have released it this series' candidates go to the spill window
+            uint32_t flags = pool_window(single, k, a.spill_cap).use == 0u ? 1u : 0u;
             switch (ni) {
-                case 0: stream_series<0>(sm, sl, acc, ws, lane, cg); break;
-                case 1: stream_series<1>(sm, sl, acc, ws, lane, cg); break;
-                case 2: stream_series<2>(sm, sl, acc, ws, lane, cg); break;
-                case 3: stream_series<3>(sm, sl, acc, ws, lane, cg); break;
-                default: stream_series<4>(sm, sl, acc, ws, lane, cg); break;
+                case 0: stream_series<0>(a, sm, sl, acc, ws, lane, single, k, flags); break;
+                case 1: stream_series<1>(a, sm, sl, acc, ws, lane, single, k, flags); break;
+                case 2: stream_series<2>(a, sm, sl, acc, ws, lane, single, k, flags); break;
+                case 3: stream_series<3>(a, sm, sl, acc, ws, lane, single, k, flags); break;
+                default: stream_series<4>(a, sm, sl, acc, ws, lane, single, k, flags); break;
             }
-            if (ni > 0) cg += (uint32_t)((sl->nstages + F_GS - 1) / F_GS);
+            if (__any_sync(0xffffffffu, (flags & 4u) != 0u)) __threadfence();   // spilled keys: in L2 before the finish warps read them
+            const bool over = __any_sync(0xffffffffu, (flags & 2u) != 0u);
+            if (lane == 0 && over) sm.ovf()[d] = 1u;
             // warp totals -> partial of (slot, warp)
-            double s = (acc.s0 + acc.s1) + (acc.s2 + acc.s3), mn = acc.mn, mx = acc.mx;
+            double s = acc.s0 + acc.s1, mn = acc.mn, mx = acc.mx;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
                 s += shfl_xor_f64(s, o);

@@ -34,9 +34,7 @@ names = {0: "producer wait desc", 1: "producer wait empty stage", 2: "producer i
          6: "planner plan (total)", 10: "  plan: gather", 11: "  plan: round 1 + targets", 12: "  plan: round 2",
          13: "  plan: heavy levels", 14: "  plan: thread 0", 20: "finish wait plan", 21: "finish wait stream",
          22: "finish work", 30: "stream0 wait plan", 31: "stream0 series work (all)", 32: "  stream0 wait full stage",
-         33: "  stream0 scan", 34: "  stream0 wait bitmap slot", 40: "collector0 wait plan",
-         41: "collector0 work (all)", 42: "  collector0 wait bitmaps", 43: "  collector0 read",
-         44: "  collector0 reserve", 45: "  collector0 store"}
+         33: "  stream0 scan", 34: "  stream0 store candidates"}
 per = max(1, n // 148)
 print("L=%d n=%d nq=%d series_flow %.3f ms (%.0f GB/s), ~%d series per CTA; kcycles per series in CTA 0:" %
       (L, n, nq, pms, vals.numel() * 8 / pms / 1e6, per))
