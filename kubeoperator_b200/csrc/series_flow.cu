@@ -28,17 +28,20 @@
 
 namespace {
 
-constexpr int F_NS = 15;                       // stream warps
-constexpr int F_NP = 8;                        // planner warps
+// 32 warps: 1 producer, F_NF finish, and stream + planner warps split by the launch's mode: series of more than
+// F_DOUBLE_MAXL samples (one series per candidate pool) are bound by the scan and leave the planner idle most of the
+// time, shorter ones keep eight planner warps busy.
+constexpr int F_NS_LONG = 19, F_NP_LONG = 4;   // stream / planner warps when the batch holds a series > F_DOUBLE_MAXL
+constexpr int F_NS_SHORT = 15, F_NP_SHORT = 8; // ... otherwise
+constexpr int F_NS_MAX = 19;
 constexpr int F_NF = 8;                        // finish warps
-constexpr int F_WARPS = 1 + F_NP + F_NF + F_NS;
+constexpr int F_WARPS = 32;
+static_assert(1 + F_NP_LONG + F_NF + F_NS_LONG == F_WARPS && 1 + F_NP_SHORT + F_NF + F_NS_SHORT == F_WARPS, "role split");
 constexpr int F_THREADS = F_WARPS * 32;        // 1024
 // The scheduler prefers the warp with the highest id: the serial roles (whose latency everything else waits for)
 // come last, the stream warps (throughput, always something to do) first.
-constexpr int F_W_STREAM = 0;                  // first stream warp
-constexpr int F_W_FIN = F_W_STREAM + F_NS;     // first finish warp
-constexpr int F_W_PLAN = F_W_FIN + F_NF;       // first planner warp
-constexpr int F_W_PROD = F_W_PLAN + F_NP;      // the producer warp
+// warps [0, ns) stream, [ns, ns + F_NF) finish, [ns + F_NF, 31) planner, 31 producer
+constexpr int F_W_PROD = F_WARPS - 1;          // the producer warp
 constexpr int F_STAGE = 512;                   // samples per ring stage (4 KB): 4 warp steps of 128 samples
 constexpr int F_STAGE_BYTES = F_STAGE * 8;
 constexpr int F_GS = 4;                        // stages per ring group: one TMA copy and one pair of barriers (16 KB)
@@ -170,7 +173,7 @@ constexpr size_t FO_FLISTK = FO_FBINS + (size_t)NI_MAX * 256 * 4;
 constexpr size_t FO_FLISTM = FO_FLISTK + (size_t)NI_MAX * F_LIST * 8;
 constexpr size_t FO_SLOTS = FO_FLISTM + (size_t)NI_MAX * F_LIST * 4;
 constexpr size_t FO_PART = FO_SLOTS + align_up(F_ND * sizeof(FlowSlot), 16);
-constexpr size_t FO_PS = FO_PART + (size_t)F_ND * F_NS * sizeof(FlowPartial);
+constexpr size_t FO_PS = FO_PART + (size_t)F_ND * F_NS_MAX * sizeof(FlowPartial);
 constexpr size_t FO_FS = FO_PS + align_up(sizeof(PlanScratch), 16);
 constexpr size_t FO_PSTATE = FO_FS + align_up(sizeof(FinState), 16);   // csm[F_ND], cgl[F_ND], ovf[F_ND], hcnt[F_ND][F_NH], rel[2], issued
 constexpr int F_PSTATE_WORDS = F_ND * (3 + F_NH) + 2 + 2;
@@ -193,7 +196,7 @@ struct FlowSmem {
     __device__ __forceinline__ unsigned* flistm() const { return reinterpret_cast<unsigned*>(base + FO_FLISTM); }
     __device__ __forceinline__ FlowSlot* slot(int d) const { return reinterpret_cast<FlowSlot*>(base + FO_SLOTS) + d; }
     __device__ __forceinline__ FlowPartial* part(int d, int w) const {
-        return reinterpret_cast<FlowPartial*>(base + FO_PART) + d * F_NS + w;
+        return reinterpret_cast<FlowPartial*>(base + FO_PART) + d * F_NS_MAX + w;
     }
     __device__ __forceinline__ PlanScratch* ps() const { return reinterpret_cast<PlanScratch*>(base + FO_PS); }
     __device__ __forceinline__ FinState* fs() const { return reinterpret_cast<FinState*>(base + FO_FS); }
@@ -247,7 +250,7 @@ __device__ __forceinline__ void wait_group_full(const FlowSmem& sm, uint32_t grp
     while (*iss <= grp) __nanosleep(64);
     mbar_wait(sm.bar(FB_FULL + (int)(grp % F_NGROUPS)), (grp / F_NGROUPS) & 1u);
 }
-__device__ __forceinline__ void plan_sync() { asm volatile("bar.sync 3, %0;" ::"n"(F_NP * 32) : "memory"); }
+__device__ __forceinline__ void plan_sync(int nthreads) { asm volatile("bar.sync 3, %0;" ::"r"(nthreads) : "memory"); }
 __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(F_NF * 32) : "memory"); }
 
 __device__ __forceinline__ uint32_t hi_key(uint32_t h) {   // top half of ko_okey()
@@ -371,10 +374,9 @@ __device__ __forceinline__ int quad_pos(int j, int L, int nquad, int lead4) {
     return p;
 }
 
-// All planner threads (ptid in [0, F_NP * 32)).  Fills the plan fields of the slot.
+// All planner threads (ptid in [0, NT)).  Fills the plan fields of the slot.
 __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem& sm, FlowSlot* sl, int ptid, bool single,
-                                             uint32_t kser) {
-    constexpr int NT = F_NP * 32;
+                                             uint32_t kser, int NT) {
     PlanScratch* ps = sm.ps();
     const int lane = ptid & 31;
     const int L = sl->L;
@@ -395,7 +397,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         ps->nvalid = 0;
     }
     if (nq == 0) {
-        plan_sync();
+        plan_sync(NT);
         return;
     }
     const int S = sample_size(L);
@@ -404,7 +406,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
     const int per = S / NT;          // sample keys per thread in the histogram rounds
     const int lead4 = (int)((reinterpret_cast<uintptr_t>(v) >> 3) & 3u);
     uint32_t* sk = sm.hkeys();
-    plan_sync();
+    plan_sync(NT);
     // ---- gather: four 32-byte loads of a thread in flight together; the high keys go to shared memory (that is all
     // the histogram rounds need), the exact extremes are kept as 64-bit keys on the way
     {
@@ -458,7 +460,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         for (int i = ptid; i < F_NT * 256; i += NT) sm.hist2()[i] = 0;
         for (int i = ptid; i < 256 / 4; i += NT) reinterpret_cast<uint32_t*>(sm.lut())[i] = 0;
     }
-    plan_sync();
+    plan_sync(NT);
     FT_MARK(10);   // gather
     const unsigned ns = ps->nvalid;
     const unsigned long long kmin64 = ps->kmin, kmax64 = ps->kmax;
@@ -477,7 +479,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
                 sl->mx_seed = ko_key2d(kmax64);
             }
         }
-        plan_sync();
+        plan_sync(NT);
         return;
     }
     // ---- round 1: 256 bins over [hkmin, hkmax]
@@ -490,7 +492,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         const uint32_t k = sk[ptid + i * NT];
         if (k != HK_NONE) red_shared_add(&sm.hist1()[(k - hkmin) >> sh1], 1u);
     }
-    plan_sync();
+    plan_sync(NT);
     if (ptid < 32) {   // exclusive prefix of the 256 bins -> cum[0..256]
         unsigned c[8];
         unsigned sum8 = 0;
@@ -551,7 +553,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         if (lane < F_NT && tb >= 0)
             atomicOr(reinterpret_cast<unsigned*>(sm.lut()) + (tb >> 2), (1u << lane) << ((tb & 3) * 8));
     }
-    plan_sync();
+    plan_sync(NT);
     FT_MARK(11);   // round 1 + targets
     // ---- round 2: 256 sub-bins inside the bins that hold an interval end
 #pragma unroll 1
@@ -567,10 +569,10 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
             red_shared_add(&sm.hist2()[t * 256 + sub], 1u);
         }
     }
-    plan_sync();
-    // planner warp w resolves the ends w, w + F_NP, ...
+    plan_sync(NT);
+    // planner warp w resolves the ends w, w + (number of planner warps), ...
     unsigned heavy_any = 0;
-    for (int t = ptid >> 5; t < F_NT; t += F_NP) {
+    for (int t = ptid >> 5; t < F_NT; t += NT >> 5) {
         const int tb = ps->tbin[t];
         if (tb >= 0) {
             int bin;
@@ -588,7 +590,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
             }
         }
     }
-    plan_sync();
+    plan_sync(NT);
     FT_MARK(12);   // round 2
     // ---- heavy tie levels: a sub-bin at an interval end that holds many sample points may be one repeated value
     // (an integer-valued gauge, a clamp).  It is, when the smallest and the largest sample key inside it are equal.
@@ -619,7 +621,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
                 }
             }
         }
-        plan_sync();
+        plan_sync(NT);
     }
     FT_MARK(13);   // heavy levels
     // ---- thread 0: intervals (quantiles ascend, so do their interval ends), heavy list, capacity check
@@ -708,7 +710,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         }
     }
     FT_MARK(14);   // thread 0
-    plan_sync();
+    plan_sync(NT);
 }
 
 // ------------------------------------------------------------------------------------------------ stream
@@ -902,12 +904,12 @@ __device__ __forceinline__ void patch_stage_edges(uint32_t stage_addr, int lane,
     __syncwarp();
 }
 
-// Stage j of a series (ring stage g = g0 + j) belongs to stream warp j % F_NS and to ring group (g / F_GS) % F_NGROUPS.  A series
+// Stage j of a series (ring stage g = g0 + j) belongs to stream warp j % ns and to ring group (g / F_GS) % F_NGROUPS.  A series
 // starts on a group boundary; the stage numbers that pad its last group are visited too (wait, release, no work),
 // so that every group gets its F_GS releases.
 template <int NI>
 __device__ __forceinline__ void stream_series(const SeriesArgs& a, const FlowSmem& sm, const FlowSlot* sl, StreamAcc& acc,
-                                              int ws, int lane, bool single, uint32_t kser, uint32_t& flags) {
+                                              int ws, int ns, int lane, bool single, uint32_t kser, uint32_t& flags) {
     uint32_t A[NI_MAX], W[NI_MAX];
 #pragma unroll
     for (int i = 0; i < NI_MAX; ++i) {
@@ -919,9 +921,10 @@ __device__ __forceinline__ void stream_series(const SeriesArgs& a, const FlowSme
     const uint32_t ring0 = smem_u32(sm.ring());
     const uint32_t empty0 = smem_u32(sm.bar(FB_EMPTY));
     FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
-    // (stage j of a series always goes to stream warp j % F_NS, whatever the CTA did before: the partial sums of a
-    // series, and with them the last bits of its sum, do not depend on how the work was distributed)
-    for (int j = ws; j < npad; j += F_NS) {
+    // (stage j of a series always goes to stream warp j % ns, whatever the CTA did before: the partial sums of a
+    // series, and with them the last bits of its sum, do not depend on how the work was distributed among the CTAs -
+    // only on ns, i.e. on whether the launch is in the long-series mode)
+    for (int j = ws; j < npad; j += ns) {
         const uint32_t g = *reinterpret_cast<const volatile uint32_t*>(&sl->g0) + (uint32_t)j;   // (reloaded: registers)
         const uint32_t grp = g / F_GS;
         const uint32_t s = grp % F_NGROUPS;
@@ -950,7 +953,7 @@ __device__ __forceinline__ double shfl_xor_f64(double v, int o) { return __shfl_
 // ------------------------------------------------------------------------------------------------ finish
 // All finish threads (ftid in [0, 128)).  Returns nothing; outputs are written here.
 __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSmem& sm, const FlowSlot* sl, int d, int ftid,
-                              const PoolWin& pw, const unsigned long long* spill) {
+                              const PoolWin& pw, const unsigned long long* spill, int ns) {
     FinState* fs = sm.fs();
     const int lane = ftid & 31, fw = ftid >> 5;
     const int nq = a.nq, ni = sl->ni;
@@ -958,13 +961,13 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
     // ---- A. partial statistics (warp 0, fixed order) and the last valid sample (warp 1)
     if (fw == 0) {
-        const FlowPartial* p = sm.part(d, lane < F_NS ? lane : 0);
-        double s = lane < F_NS ? p->sum : 0.0;
+        const FlowPartial* p = sm.part(d, lane < ns ? lane : 0);
+        double s = lane < ns ? p->sum : 0.0;
         double mn = p->mn, mx = p->mx;
-        unsigned nn = lane < F_NS ? p->nan : 0u;
+        unsigned nn = lane < ns ? p->nan : 0u;
         unsigned c[NI_MAX];
 #pragma unroll
-        for (int i = 0; i < NI_MAX; ++i) c[i] = lane < F_NS ? p->c[i] : 0u;
+        for (int i = 0; i < NI_MAX; ++i) c[i] = lane < ns ? p->c[i] : 0u;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             s += shfl_xor_f64(s, o);
@@ -1262,6 +1265,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
     FlowSmem sm;
     sm.base = flow_smem;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const bool single = a.wide != 0 || a.counters[8] > F_DOUBLE_MAXL;
+    const int ns = single ? F_NS_LONG : F_NS_SHORT, np = single ? F_NP_LONG : F_NP_SHORT;
+    const int w_fin = ns, w_plan = ns + F_NF;
     if (tid == 0) {
         for (int s = 0; s < F_NGROUPS; ++s) {
             mbar_init(sm.bar(FB_FULL + s), 1);
@@ -1271,7 +1277,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             mbar_init(sm.bar(FB_DESC + d), 1);
             mbar_init(sm.bar(FB_PLAN + d), 1);
             mbar_init(sm.bar(FB_FREE + d), 1);
-            mbar_init(sm.bar(FB_SDONE + d), F_NS);
+            mbar_init(sm.bar(FB_SDONE + d), (uint32_t)ns);
             mbar_init(sm.bar(FB_START + d), 1);
         }
         mbar_fence_init();
@@ -1283,7 +1289,6 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
 #endif
     __syncthreads();
     const int n_work = a.counters[a.work_cnt];
-    const bool single = a.wide != 0 || a.counters[8] > F_DOUBLE_MAXL;
     unsigned long long* spill = a.spill + (size_t)blockIdx.x * (size_t)a.spill_cap;
 
     if (warp == F_W_PROD) {
@@ -1340,9 +1345,9 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                 }
             }
         }
-    } else if (warp >= F_W_PLAN) {
+    } else if (warp >= w_plan) {
         // =============================== PLANNER ===============================
-        const int ptid = tid - F_W_PLAN * 32;
+        const int ptid = tid - w_plan * 32;
         PlanScratch* ps = sm.ps();
         uint32_t g = 0;
         const long long arr_end = a.offsets[a.n_series];
@@ -1403,7 +1408,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                 ps->work = sl->sid;
                 mbar_arrive(sm.bar(FB_DESC + d));
             }
-            plan_sync();
+            plan_sync(np * 32);
             if (ps->work < 0) {
                 if (ptid == 0) mbar_arrive(sm.bar(FB_PLAN + d));
                 break;
@@ -1411,13 +1416,13 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             g += (uint32_t)((sl->nstages + F_GS - 1) / F_GS * F_GS);   // every series starts a ring group
             prev_depth1 = sl->depth1;
             if (ptid == 0) FP(1, k, 4);
-            planner_plan(a, sm, sl, ptid, single, k);
+            planner_plan(a, sm, sl, ptid, single, k, np * 32);
             if (ptid == 0) FP(1, k, 5);
             if (ptid == 0) mbar_arrive(sm.bar(FB_PLAN + d));
         }
-    } else if (warp >= F_W_FIN) {
+    } else if (warp >= w_fin) {
         // =============================== FINISH ===============================
-        const int ftid = tid - F_W_FIN * 32;
+        const int ftid = tid - w_fin * 32;
         FT_BEGIN(blockIdx.x == 0 && ftid == 0);
         for (uint32_t k = 0;; ++k) {
             const int d = (int)(k % F_ND);
@@ -1433,7 +1438,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             if (ftid == 0) FP(4, k, 3);
             FT_MARK(21);   // finish: waiting for the stream warps
             const PoolWin pw = pool_window(single, k, a.spill_cap);
-            finish_series(a, sm, sl, d, ftid, pw, spill);
+            finish_series(a, sm, sl, d, ftid, pw, spill, ns);
             if (ftid == 0) FP(4, k, 5);
             if (ftid == 0) {   // (finish_series ends with a barrier of the finish warps: all reads of the pool are done)
                 __threadfence_block();
@@ -1443,7 +1448,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
         }
     } else {
         // =============================== STREAM ===============================
-        const int ws = warp - F_W_STREAM;
+        const int ws = warp;
         FT_BEGIN(blockIdx.x == 0 && ws == 0 && lane == 0);
         for (uint32_t k = 0;; ++k) {
             const int d = (int)(k % F_ND);
@@ -1470,11 +1475,11 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             // finish warps have released it this series' candidates go to the spill window
             uint32_t flags = pool_window(single, k, a.spill_cap).use == 0u ? 1u : 0u;
             switch (ni) {
-                case 0: stream_series<0>(a, sm, sl, acc, ws, lane, single, k, flags); break;
-                case 1: stream_series<1>(a, sm, sl, acc, ws, lane, single, k, flags); break;
-                case 2: stream_series<2>(a, sm, sl, acc, ws, lane, single, k, flags); break;
-                case 3: stream_series<3>(a, sm, sl, acc, ws, lane, single, k, flags); break;
-                default: stream_series<4>(a, sm, sl, acc, ws, lane, single, k, flags); break;
+                case 0: stream_series<0>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;
+                case 1: stream_series<1>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;
+                case 2: stream_series<2>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;
+                case 3: stream_series<3>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;
+                default: stream_series<4>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;
             }
             if (__any_sync(0xffffffffu, (flags & 4u) != 0u)) __threadfence();   // spilled keys: in L2 before the finish warps read them
             const bool over = __any_sync(0xffffffffu, (flags & 2u) != 0u);
