@@ -84,6 +84,7 @@ struct alignas(16) FlowSlot {
     int konst;               // the pre-sample holds one single value: no capture, the finish checks min == max
     int nheavy;
     uint32_t A[NI_MAX], W[NI_MAX];   // interval i holds the samples with A <= high key <= A + W
+    double Ad[NI_MAX], Bd[NI_MAX];   // the same interval as doubles: Ad <= x <= Bd (the scan compares doubles)
     int qiv[NI_MAX];         // interval of quantile j
     double mn_seed, mx_seed; // valid samples of the series (or +inf / -inf): start of the running extremes
     unsigned long long heavy[F_NH];  // keys of heavy tie levels (zero canonical)
@@ -679,6 +680,15 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
             sl->A[i] = HK_UNUSED;
             sl->W[i] = 0u;
         }
+        // The scan works on the samples themselves (FP64 pipe), so every interval is also handed over as the smallest
+        // and the largest double whose high key lies in [A, A + W].  Key order is value order with -0 = +0, which is
+        // exactly how doubles compare; high keys at or beyond the infinities' are clamped to the infinities.
+        for (int i = 0; i < NI_MAX; ++i) {
+            const uint32_t ka = sl->A[i], kb = ka + sl->W[i];
+            const double qnan = __longlong_as_double(0x7FF8000000000000LL);
+            sl->Ad[i] = i >= ni ? qnan : (ka <= HK_NINF ? -pinf : ko_key2d((unsigned long long)ka << 32));
+            sl->Bd[i] = i >= ni ? qnan : (kb >= HK_PINF ? pinf : ko_key2d(((unsigned long long)kb << 32) | 0xFFFFFFFFull));
+        }
         int nh = 0;
         unsigned heavy_pts = 0;
         for (int t = 0; t < F_NT; ++t) {
@@ -715,47 +725,98 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
 
 // ------------------------------------------------------------------------------------------------ stream
 struct StreamAcc {
-    double s0, s1, mn, mx;
-    uint32_t rlo, rhi;       // fast path while every high key lies strictly between them
+    double s0, s1, mn, mx;   // mn / mx: the warp's running extremes (equal in all lanes)
     unsigned nan;
-    unsigned c[NI_MAX];      // MINUS the number of samples below A[i] (see stream_step)
+    unsigned c[NI_MAX];      // samples below interval i
 };
 
-__device__ __forceinline__ void acc_bounds(StreamAcc& acc) {
-    const uint32_t kx = (uint32_t)(ko_okey(acc.mx) >> 32), kn = (uint32_t)(ko_okey(acc.mn) >> 32);
-    acc.rhi = kx < HK_PINF ? kx : HK_PINF;
-    acc.rlo = kn > HK_NINF ? kn : HK_NINF;
+// One sample against NI intervals, hand-written so that every comparison result stays a predicate (the compiler
+// turns them into SEL / LOP3 / ISETP sequences on the integer pipe, which is the pipe this kernel must keep free):
+// per interval  pb = x < Ad;  @pb c += 1;  q_i = (x <= Bd) && !pb;   then  @(q_0 | ... ) m |= bit.
+template <int NI>
+__device__ __forceinline__ void sample_intervals(double x, const double (&Ad)[NI_MAX], const double (&Bd)[NI_MAX],
+                                                 unsigned (&c)[NI_MAX], uint32_t& m, uint32_t bit) {
+    if (NI == 1) {
+        asm("{\n\t.reg .pred pb, q0;\n\t"
+            "setp.lt.f64 pb, %2, %3;\n\t@pb add.u32 %0, %0, 1;\n\tsetp.le.and.f64 q0, %2, %4, !pb;\n\t"
+            "@q0 or.b32 %1, %1, %5;\n\t}"
+            : "+r"(c[0]), "+r"(m)
+            : "d"(x), "d"(Ad[0]), "d"(Bd[0]), "r"(bit));
+    } else if (NI == 2) {
+        asm("{\n\t.reg .pred pb, q0, q1;\n\t"
+            "setp.lt.f64 pb, %3, %4;\n\t@pb add.u32 %0, %0, 1;\n\tsetp.le.and.f64 q0, %3, %5, !pb;\n\t"
+            "setp.lt.f64 pb, %3, %6;\n\t@pb add.u32 %1, %1, 1;\n\tsetp.le.and.f64 q1, %3, %7, !pb;\n\t"
+            "or.pred q0, q0, q1;\n\t"
+            "@q0 or.b32 %2, %2, %8;\n\t}"
+            : "+r"(c[0]), "+r"(c[1]), "+r"(m)
+            : "d"(x), "d"(Ad[0]), "d"(Bd[0]), "d"(Ad[1]), "d"(Bd[1]), "r"(bit));
+    } else if (NI == 3) {
+        asm("{\n\t.reg .pred pb, q0, q1, q2;\n\t"
+            "setp.lt.f64 pb, %4, %5;\n\t@pb add.u32 %0, %0, 1;\n\tsetp.le.and.f64 q0, %4, %6, !pb;\n\t"
+            "setp.lt.f64 pb, %4, %7;\n\t@pb add.u32 %1, %1, 1;\n\tsetp.le.and.f64 q1, %4, %8, !pb;\n\t"
+            "setp.lt.f64 pb, %4, %9;\n\t@pb add.u32 %2, %2, 1;\n\tsetp.le.and.f64 q2, %4, %10, !pb;\n\t"
+            "or.pred q0, q0, q1;\n\tor.pred q0, q0, q2;\n\t"
+            "@q0 or.b32 %3, %3, %11;\n\t}"
+            : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(m)
+            : "d"(x), "d"(Ad[0]), "d"(Bd[0]), "d"(Ad[1]), "d"(Bd[1]), "d"(Ad[2]), "d"(Bd[2]), "r"(bit));
+    } else if (NI == 4) {
+        asm("{\n\t.reg .pred pb, q0, q1, q2, q3;\n\t"
+            "setp.lt.f64 pb, %5, %6;\n\t@pb add.u32 %0, %0, 1;\n\tsetp.le.and.f64 q0, %5, %7, !pb;\n\t"
+            "setp.lt.f64 pb, %5, %8;\n\t@pb add.u32 %1, %1, 1;\n\tsetp.le.and.f64 q1, %5, %9, !pb;\n\t"
+            "setp.lt.f64 pb, %5, %10;\n\t@pb add.u32 %2, %2, 1;\n\tsetp.le.and.f64 q2, %5, %11, !pb;\n\t"
+            "setp.lt.f64 pb, %5, %12;\n\t@pb add.u32 %3, %3, 1;\n\tsetp.le.and.f64 q3, %5, %13, !pb;\n\t"
+            "or.pred q0, q0, q1;\n\tor.pred q2, q2, q3;\n\tor.pred q0, q0, q2;\n\t"
+            "@q0 or.b32 %4, %4, %14;\n\t}"
+            : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]), "+r"(m)
+            : "d"(x), "d"(Ad[0]), "d"(Bd[0]), "d"(Ad[1]), "d"(Bd[1]), "d"(Ad[2]), "d"(Bd[2]), "d"(Ad[3]), "d"(Bd[3]), "r"(bit));
+    }
+}
+// mn <= x && x <= mx for four samples (one predicate chain; false for NaN)
+__device__ __forceinline__ uint32_t plain4(double x0, double x1, double x2, double x3, double mn, double mx) {
+    uint32_t ok;
+    asm("{\n\t.reg .pred p;\n\t"
+        "setp.ge.f64 p, %1, %5;\n\tsetp.le.and.f64 p, %1, %6, p;\n\t"
+        "setp.ge.and.f64 p, %2, %5, p;\n\tsetp.le.and.f64 p, %2, %6, p;\n\t"
+        "setp.ge.and.f64 p, %3, %5, p;\n\tsetp.le.and.f64 p, %3, %6, p;\n\t"
+        "setp.ge.and.f64 p, %4, %5, p;\n\tsetp.le.and.f64 p, %4, %6, p;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "d"(x0), "d"(x1), "d"(x2), "d"(x3), "d"(mn), "d"(mx));
+    return ok;
 }
 
-// Two warp steps at once: 8 samples per lane (two independent groups of four keep the pipes busy).
-// NI intervals.  addr: the lane's 16 bytes of the first step.  Slots of a stage that lie outside the series have been
-// overwritten with NaN before (patch_stage_edges), so every slot is either a sample or NaN here.
+// Two warp steps at once: 8 samples per lane.  NI intervals.  addr: the lane's 16 bytes of the first step.  Slots of a
+// stage that lie outside the series have been overwritten with NaN before (patch_stage_edges), so every slot is
+// either a sample or NaN here.  Everything per sample is a double comparison (DSETP on the FP64 pipe, which is
+// otherwise idle: the integer pipe was the bound of this kernel) feeding a predicated add or a predicate:
+//   below interval i:   x < Ad[i]                        -> c[i] += 1
+//   inside interval i:  !(x < Ad[i]) && x <= Bd[i]       -> flag bit
+//   nothing special:    mn <= x && x <= mx               (false for NaN, a new extreme, an infinity beyond them)
+// NaN compares false everywhere, so stale samples are neither below nor inside anything.
 template <int NI>
-__device__ __forceinline__ uint32_t stream_step2(uint32_t addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
-                                                 const uint32_t (&W)[NI_MAX]) {
+__device__ __forceinline__ uint32_t stream_step2(uint32_t addr, StreamAcc& acc, const double (&Ad)[NI_MAX],
+                                                 const double (&Bd)[NI_MAX]) {
     double x[8];
     lds_v2f64(addr, x[0], x[1]);
     lds_v2f64(addr + 512u, x[2], x[3]);
     lds_v2f64(addr + 1024u, x[4], x[5]);
     lds_v2f64(addr + 1536u, x[6], x[7]);
-    uint32_t k[8];
+    const bool plain = (plain4(x[0], x[2], x[4], x[6], acc.mn, acc.mx) & plain4(x[1], x[3], x[5], x[7], acc.mn, acc.mx)) != 0u;
+    uint32_t m = 0u;   // bit e: sample e of this lane lies in one of the intervals
+    if (NI > 0) {
 #pragma unroll
-    for (int e = 0; e < 8; ++e) k[e] = hi_key((uint32_t)__double2hiint(x[e]));
-    const uint32_t kmx = max(max(max(k[0], k[1]), max(k[2], k[3])), max(max(k[4], k[5]), max(k[6], k[7])));
-    const uint32_t kmn = min(min(min(k[0], k[1]), min(k[2], k[3])), min(min(k[4], k[5]), min(k[6], k[7])));
-    const bool rare = (kmx >= acc.rhi) || (kmn <= acc.rlo);
-    if (__any_sync(0xffffffffu, rare)) {
-        // Somewhere in the warp: a NaN (stale sample), an infinity, or a candidate for a new extreme.  The running
-        // extremes are the WARP's (kept equal in all lanes), so new extremes die out like 1 / samples seen.
+        for (int e = 0; e < 8; ++e) sample_intervals<NI>(x[e], Ad, Bd, acc.c, m, 1u << e);
+    }
+    if (__any_sync(0xffffffffu, !plain)) {
+        // Somewhere in the warp: a NaN (stale sample) or a new extreme.  The running extremes are the WARP's (kept
+        // equal in all lanes), so new extremes die out like 1 / samples seen.
         bool changed = false;
-        if (rare) {
+        if (!plain) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-                const uint32_t h = (uint32_t)__double2hiint(x[e]), l = (uint32_t)__double2loint(x[e]);
-                if (bits_nan(h, l)) {
+                if (x[e] != x[e]) {
                     acc.nan += 1u;
                     x[e] = 0.0;
-                    k[e] = HK_NONE;
                 } else {
                     if (x[e] < acc.mn) {
                         acc.mn = x[e];
@@ -774,36 +835,19 @@ __device__ __forceinline__ uint32_t stream_step2(uint32_t addr, StreamAcc& acc, 
                 acc.mn = fmin(acc.mn, __shfl_xor_sync(0xffffffffu, acc.mn, o));
                 acc.mx = fmax(acc.mx, __shfl_xor_sync(0xffffffffu, acc.mx, o));
             }
-            acc_bounds(acc);
         }
     }
     // (pairwise inside the step, two running sums: short dependent chains without more live registers)
     acc.s0 += (x[0] + x[2]) + (x[4] + x[6]);
     acc.s1 += (x[1] + x[3]) + (x[5] + x[7]);
-    uint32_t m = 0u;   // bit e: sample e of this lane lies in one of the intervals
-    if (NI > 0) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            bool q = false;
-#pragma unroll
-            for (int i = 0; i < NI; ++i) {
-                uint32_t d;
-                // d = k - A, and c -= (k < A): sub.cc / subc is the borrow chain of a two-word subtraction,
-                // so c goes down by the borrow whatever polarity the carry flag has in hardware
-                asm("sub.cc.u32 %0, %2, %3;\n\tsubc.u32 %1, %1, 0;" : "=r"(d), "+r"(acc.c[i]) : "r"(k[e]), "r"(A[i]));
-                q = q || (d <= W[i]);
-            }
-            m |= q ? (1u << e) : 0u;
-        }
-    }
     return m;
 }
 
 // One stage: returns the lane's 16 in-interval flags.  Bit b = t * 8 + e flags the sample at stage offset
 // (b >> 1) * 64 + lane * 2 + (b & 1): sample e of step t sits at t * 256 + (e >> 1) * 64 + lane * 2 + (e & 1).
 template <int NI>
-__device__ __forceinline__ uint32_t stream_stage(uint32_t stage_addr, StreamAcc& acc, const uint32_t (&A)[NI_MAX],
-                                                 const uint32_t (&W)[NI_MAX], int lane) {
+__device__ __forceinline__ uint32_t stream_stage(uint32_t stage_addr, StreamAcc& acc, const double (&A)[NI_MAX],
+                                                 const double (&W)[NI_MAX], int lane) {
     uint32_t m = 0u;
 #pragma unroll 1
     for (int t = 0; t < 2; ++t)
@@ -910,11 +954,11 @@ __device__ __forceinline__ void patch_stage_edges(uint32_t stage_addr, int lane,
 template <int NI>
 __device__ __forceinline__ void stream_series(const SeriesArgs& a, const FlowSmem& sm, const FlowSlot* sl, StreamAcc& acc,
                                               int ws, int ns, int lane, bool single, uint32_t kser, uint32_t& flags) {
-    uint32_t A[NI_MAX], W[NI_MAX];
+    double A[NI_MAX], W[NI_MAX];   // interval bounds as doubles (only the first NI are live)
 #pragma unroll
     for (int i = 0; i < NI_MAX; ++i) {
-        A[i] = sl->A[i];
-        W[i] = sl->W[i];
+        A[i] = sl->Ad[i];
+        W[i] = sl->Bd[i];
     }
     const int n = sl->nstages;
     const int npad = (n + F_GS - 1) / F_GS * F_GS;
@@ -1469,7 +1513,6 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             acc.nan = 0;
 #pragma unroll
             for (int i = 0; i < NI_MAX; ++i) acc.c[i] = 0;
-            acc_bounds(acc);
             const int ni = sl->ni;
             // the shared-memory window was last used by series k - 1 (one pool) or k - 2 (two halves); until the
             // finish warps have released it this series' candidates go to the spill window
@@ -1495,7 +1538,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const unsigned nn = __reduce_add_sync(0xffffffffu, acc.nan);
             unsigned c[NI_MAX];
 #pragma unroll
-            for (int i = 0; i < NI_MAX; ++i) c[i] = __reduce_add_sync(0xffffffffu, 0u - acc.c[i]);
+            for (int i = 0; i < NI_MAX; ++i) c[i] = __reduce_add_sync(0xffffffffu, acc.c[i]);
             __syncwarp();
             if (lane == 0) {
                 FlowPartial* p = sm.part(d, ws);
