@@ -107,6 +107,8 @@ struct PlanScratch {      // planner scratch
     unsigned tcum[F_NT];     // sample keys below that sub-bin (whole sample)
     unsigned tcnt[F_NT];     // sample keys inside that sub-bin
     unsigned long long hmin[F_NT], hmax[F_NT];   // smallest / largest sample key of that sub-bin (tie level check)
+    unsigned hklo[F_NT], hkhi[F_NT];             // smallest / largest HIGH key among the sample points of that sub-bin
+    unsigned hifirst[F_NT], hilast[F_NT];        // first / last sample point (index) of that sub-bin
 };
 
 struct FinState {
@@ -358,7 +360,7 @@ __device__ __forceinline__ bool warp_find_bin(const unsigned* hist, unsigned rho
 // ------------------------------------------------------------------------------------------------ planner
 __device__ __forceinline__ int sample_size(int L) {
     int s = 256;
-    while (s < F_SMAX && s * 8 <= L) s <<= 1;   // about L/8 .. L/16 points, 256 .. 4096
+    while (s < F_SMAX && s * 16 <= L) s <<= 1;   // about L/16 .. L/32 points, 256 .. 8192
     return s;
 }
 // The pre-sample is taken as S/4 aligned runs of four neighbouring samples: one 32-byte request fetches four points,
@@ -552,6 +554,10 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
             ps->tcnt[lane] = 0;
             ps->hmin[lane] = ~0ull;
             ps->hmax[lane] = 0ull;
+            ps->hklo[lane] = ~0u;
+            ps->hkhi[lane] = 0u;
+            ps->hifirst[lane] = ~0u;
+            ps->hilast[lane] = 0u;
         }
         // the look-up table "which ends live in this bin": byte-wide OR through 32-bit atomics
         if (lane < F_NT && tb >= 0)
@@ -602,7 +608,10 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
     plan_sync(NT);
     FT_MARK(12);   // round 2
     // ---- heavy tie levels: a sub-bin at an interval end that holds many sample points may be one repeated value
-    // (an integer-valued gauge, a clamp).  It is, when the smallest and the largest sample key inside it are equal.
+    // (an integer-valued gauge, a clamp).  It is taken for one when all its sample points have the same high key and
+    // its first and its last point have the same low word too (the low words are not kept in shared memory: two
+    // points are fetched again, not all of them).  A wrong guess costs candidates, never correctness: samples that do
+    // not equal the listed key are stored like any other.
     const unsigned heavy_min = 16;
 #pragma unroll
     for (int t = 0; t < F_NT; ++t) heavy_any |= (ps->tbin[t] >= 0 && ps->tcnt[t] >= heavy_min) ? (1u << t) : 0u;
@@ -614,20 +623,24 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
             const uint32_t d = k - hkmin;
             unsigned m = sm.lut()[d >> sh1] & heavy_any;
             const uint32_t sub = (d >> sh2) & submask;
-            unsigned long long key = 0ull;
-            bool have = false;
             while (m) {
                 const int t = __ffs(m) - 1;
                 m &= m - 1;
                 if (ps->tsub[t] == sub) {
-                    if (!have) {   // (the low words are not kept: fetch the sample again)
-                        key = ko_okey(v[quad_pos(idx >> 2, L, nquad, lead4) + (idx & 3)] + 0.0);
-                        have = true;
-                    }
-                    red_shared_min_u64(&ps->hmin[t], key);
-                    red_shared_max_u64(&ps->hmax[t], key);
+                    atomicMin(&ps->hklo[t], k);
+                    atomicMax(&ps->hkhi[t], k);
+                    atomicMin(&ps->hifirst[t], (unsigned)idx);
+                    atomicMax(&ps->hilast[t], (unsigned)idx);
                 }
             }
+        }
+        plan_sync(NT);
+        if (ptid < F_NT && ((heavy_any >> ptid) & 1u) && ps->hklo[ptid] == ps->hkhi[ptid]) {
+            const int i0 = (int)ps->hifirst[ptid], i1 = (int)ps->hilast[ptid];
+            const unsigned long long k0 = ko_okey(v[quad_pos(i0 >> 2, L, nquad, lead4) + (i0 & 3)] + 0.0);
+            const unsigned long long k1 = ko_okey(v[quad_pos(i1 >> 2, L, nquad, lead4) + (i1 & 3)] + 0.0);
+            ps->hmin[ptid] = k0 < k1 ? k0 : k1;
+            ps->hmax[ptid] = k0 < k1 ? k1 : k0;
         }
         plan_sync(NT);
     }
