@@ -3,21 +3,16 @@
 // PromQL strings for this (core/apps/kubeops_api/prometheus_client.py:90-111), see include/korollup.h.
 //
 // HBM-bound by design: 8 algorithmic bytes per sample, read once.  Kernels of one call:
-//   classify_series   — builds the work list of long series (scratch) and validates offsets
-//   series_small      — one warp per series of <= 1024 samples: coalesced streaming loads, shuffle reductions;
-//                       quantiles from a register bitonic sort (<= 256 samples) or a warp-private shared-memory
-//                       radix select
-//   series_plan       — one warp per long series: a strided 1024-point pre-sample, sorted in registers with
-//                       shuffles, gives a value bracket per quantile (or a list of distinct levels for
-//                       integer-valued series); the plan goes to a window in scratch
-//   series_pipe       — persistent, one CTA of 23 warps per SM, warp-specialised: plan loader, TMA producer
-//                       (cp.async.bulk + mbarrier ring, tiles asked into L2 ahead of it), 12 stream warps that
-//                       fuse the statistics with "count below the bracket, keep what is inside it" in ONE pass,
-//                       a prologue warp, 8 finish warps that select the exact order statistic among the kept
-//                       candidates of the previous series meanwhile
-//   series_pipe again — second attempt with wide brackets over the few quantiles the first could not answer
-//   series_long       — exact multi-pass slow path (histogram refinement in key space) over what is left
-// Every bracket is verified by exact counts, so the result is always the oracle's value.
+//   classify_series   - builds the work list of long series (scratch), finds the longest, validates offsets
+//   series_small      - series of <= 256 samples, 16 per warp: four windows of <= 32 samples side by side (quantiles
+//                       by rank counting), 33..256 samples in registers with a one-pass histogram select
+//   series_medium     - series of 257..1024 samples: one warp per series, keys in shared memory, MSB radix select
+//   series_flow       - series_flow.cu: persistent, one CTA of 32 warps per SM, warp-specialised; plan (pre-sample,
+//                       key interval per quantile), TMA ring, scan (statistics + "count below the interval, keep
+//                       what is inside it") and exact selection among the kept candidates in ONE pass over HBM
+//   series_flow again - second attempt with wide intervals over the few quantiles the first could not answer
+//   series_long       - exact multi-pass slow path (histogram refinement in key space) over what is left
+// Every interval is verified by exact counts, so the result is always the oracle's value.
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
