@@ -82,16 +82,36 @@ int ko_init(const int* devices, int n_devices, ko_ctx** out) {
     ko_ctx* ctx = new ko_ctx();
     ctx->device = devices[0];
     ctx->num_sms = prop.multiProcessorCount;
-    KO_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    KO_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 2; ++i) {
-        KO_CUDA(cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming));
-        KO_CUDA(cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+    // streams and events; on any failure what exists so far is destroyed again and *out stays NULL
+    auto create_all = [&]() -> cudaError_t {
+        cudaError_t r;
+        if ((r = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return r;
+        if ((r = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return r;
+        for (int i = 0; i < 2; ++i) {
+            if ((r = cudaEventCreateWithFlags(&ctx->ev_copied[i], cudaEventDisableTiming)) != cudaSuccess) return r;
+            if ((r = cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming)) != cudaSuccess) return r;
+        }
+        if ((r = cudaEventCreate(&ctx->ev_k0)) != cudaSuccess) return r;
+        if ((r = cudaEventCreate(&ctx->ev_k1)) != cudaSuccess) return r;
+        if ((r = cudaEventCreate(&ctx->ev_p0)) != cudaSuccess) return r;
+        return cudaEventCreate(&ctx->ev_p1);
+    };
+    const cudaError_t ce = create_all();
+    if (ce != cudaSuccess) {
+        ko_set_error("ko_init: creating streams / events failed: %s", cudaGetErrorString(ce));
+        for (int i = 0; i < 2; ++i) {
+            if (ctx->ev_copied[i]) cudaEventDestroy(ctx->ev_copied[i]);
+            if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+        }
+        cudaEvent_t evs[] = {ctx->ev_k0, ctx->ev_k1, ctx->ev_p0, ctx->ev_p1};
+        for (cudaEvent_t ev : evs)
+            if (ev) cudaEventDestroy(ev);
+        if (ctx->stream) cudaStreamDestroy(ctx->stream);
+        if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+        delete ctx;
+        (void)cudaGetLastError();
+        return ce == cudaErrorMemoryAllocation ? KO_ENOMEM : KO_ECUDA;
     }
-    KO_CUDA(cudaEventCreate(&ctx->ev_k0));
-    KO_CUDA(cudaEventCreate(&ctx->ev_k1));
-    KO_CUDA(cudaEventCreate(&ctx->ev_p0));
-    KO_CUDA(cudaEventCreate(&ctx->ev_p1));
     ctx->alive = true;
     *out = ctx;
     return KO_OK;
