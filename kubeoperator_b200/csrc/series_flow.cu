@@ -6,7 +6,7 @@
 //   PLANNER   (8 warps)  series k+1: strided pre-sample of up to 8192 points (aligned runs of four), two rounds of
 //                        256-bin histograms over the 32-bit "high keys" (top half of the order-preserving image of
 //                        an f64) give, per wanted quantile, a key interval [A, A+W] that holds its rank with
-//                        ~3 sigma; heavy tie levels at the interval ends are listed so that they are counted instead
+//                        2.5 sigma; heavy tie levels at the interval ends are listed so that they are counted instead
 //                        of stored.
 //   PRODUCER  (1 lane)   series k: cp.async.bulk (TMA, SASS UBLKCP) of 16 KB groups into a 7-group ring, completion
 //                        on mbarrier transaction counts, groups asked into L2 ahead of the ring.
@@ -527,7 +527,7 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
             const int j = lane >> 1;
             unsigned tr = 0;
             if (j < nq && (qsel < 0 || j == qsel)) {
-                const double z = a.wide ? 5.0 : 3.0;
+                const double z = a.wide ? 5.0 : 2.5;
                 const double p = a.q[j];
                 const double n = (double)ns;
                 double fpc = 1.0 - (double)S / (double)L;
@@ -914,8 +914,10 @@ __device__ __forceinline__ void store_candidates(const SeriesArgs& a, const Flow
             while (*rel < pw.use) __nanosleep(200);
             ok = true;
         }
-        if (ok) flags |= 1u;
-        __threadfence_block();
+        if (ok) {
+            flags |= 1u;
+            __threadfence_block();   // (only when the window changes hands)
+        }
     }
     if (n == 0u) return;
     // Every lane reserves room for its own candidates: one atomic instruction for the warp (lanes that hit the same

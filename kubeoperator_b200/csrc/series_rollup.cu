@@ -1607,7 +1607,7 @@ int series_set_attributes(int device) {
 }
 
 // The kernels of the long-series path, enqueued on `st`:
-//   1. series_flow over every long series: one pass per series, intervals 3 sigma wide (series_flow.cu);
+//   1. series_flow over every long series: one pass per series, intervals 2.5 sigma wide (series_flow.cu);
 //   2. series_flow again over what step 1 could not finish (a rank outside its interval, ~1 % of the series;
 //      a candidate pool that overflowed), with intervals 5 sigma wide and the whole pool for one series;
 //   3. series_long, the exact multi-pass slow path, over what is still left (series with almost no valid samples,
