@@ -3,19 +3,20 @@
 // ships PromQL strings for range windows (core/apps/kubeops_api/prometheus_client.py:90-111).
 //
 // One persistent CTA per SM, 32 warps, warp-specialised; three series are in flight per CTA:
-//   PLANNER   (8 warps)  series k+1: strided pre-sample of up to 8192 points (aligned runs of four), two rounds of
+//   PLANNER   (8 / 4 warps)  series k+1: strided pre-sample of up to 8192 points (aligned runs of four), two rounds of
 //                        256-bin histograms over the 32-bit "high keys" (top half of the order-preserving image of
 //                        an f64) give, per wanted quantile, a key interval [A, A+W] that holds its rank with
 //                        2.5 sigma; heavy tie levels at the interval ends are listed so that they are counted instead
 //                        of stored.
 //   PRODUCER  (1 lane)   series k: cp.async.bulk (TMA, SASS UBLKCP) of 16 KB groups into a 7-group ring, completion
 //                        on mbarrier transaction counts, groups asked into L2 ahead of the ring.
-//   STREAM    (15 warps) series k: each warp owns whole 4 KB stages.  Per sample: sum (f64), and on the high key
-//                        alone (integer pipe) the running-extreme / NaN filter, "count below A" per interval
-//                        (sub.cc / subc) and the in-interval test.  The in-interval flags stay in a register (16 per
-//                        lane and stage); after the stage's scan the warp reserves room for its flagged samples in
-//                        the candidate pool (one shared-memory atomic per stage; shared memory first, global spill
-//                        behind it), copies them there as 64-bit keys and hands the stage back to the producer.
+//   STREAM    (15 / 19 warps) series k: each warp owns whole 4 KB stages.  Per sample: sum, and - as double
+//                        comparisons on the FP64 pipe with the results kept in predicates - the running-extreme /
+//                        NaN filter, "count below the interval" and the in-interval test per interval.  The
+//                        in-interval flags stay in a register (16 per lane and stage); after the stage's scan every
+//                        lane reserves room for its flagged samples in the candidate pool (one shared-memory atomic;
+//                        shared memory first, global spill behind it), copies them there as 64-bit keys, and the
+//                        stage goes back to the producer.
 //   FINISH    (8 warps)  series k-1: combines the warps' partial statistics, checks every interval by exact counts
 //                        and selects the wanted order statistics among the candidates by 256-bin histogram refinement
 //                        in 64-bit key space; writes the outputs.
@@ -216,8 +217,7 @@ struct FlowSmem {
 };
 
 // Where one series' candidates live: a window of the shared-memory pool and a window of the CTA's global spill,
-// both filled through a cursor shared by the collector warps (a monotone series has all candidates of an interval
-// in a few consecutive ring groups, i.e. in the hands of one or two collectors).  Cursors, tie-level counters and
+// both filled through cursors shared by the stream warps (one atomic per lane and stage).  Cursors, tie-level counters and
 // the spill window belong to the series' slot (k % F_ND: a slot is reused only after the finish warps are done
 // with it).  The shared-memory pool is halved when series are short enough (two series in flight), otherwise it is
 // one window; either way the next series may only enter a window once the finish warps have released it (a release
@@ -256,13 +256,6 @@ __device__ __forceinline__ void wait_group_full(const FlowSmem& sm, uint32_t grp
 __device__ __forceinline__ void plan_sync(int nthreads) { asm volatile("bar.sync 3, %0;" ::"r"(nthreads) : "memory"); }
 __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(F_NF * 32) : "memory"); }
 
-__device__ __forceinline__ uint32_t hi_key(uint32_t h) {   // top half of ko_okey()
-    return h ^ (((uint32_t)((int32_t)h >> 31)) | 0x80000000u);
-}
-__device__ __forceinline__ bool bits_nan(uint32_t h, uint32_t l) {
-    const uint32_t ah = h & 0x7FFFFFFFu;
-    return ah > 0x7FF00000u || (ah == 0x7FF00000u && l != 0u);
-}
 __device__ __forceinline__ uint64_t createpolicy_evict_first() {
     uint64_t p;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
@@ -282,16 +275,8 @@ __device__ __forceinline__ unsigned long long ld_cg_u64(const unsigned long long
     asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(v) : "l"(p));
     return v;
 }
-__device__ __forceinline__ uint32_t lds_u32f(uint32_t addr) {
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
-}
 __device__ __forceinline__ void sts_f64(uint32_t addr, double x) {
     asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(x) : "memory");
-}
-__device__ __forceinline__ void sts_v4u32(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ void red_shared_max_u64(const void* p, unsigned long long v) {
     asm volatile("red.shared.max.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
@@ -300,21 +285,9 @@ __device__ __forceinline__ void red_shared_min_u64(const void* p, unsigned long 
     asm volatile("red.shared.min.u64 [%0], %1;" ::"r"(smem_u32(p)), "l"(v) : "memory");
 }
 
-__device__ __forceinline__ double ld_cg_f64(const double* p) {
-    double v;
-    asm volatile("ld.global.cg.f64 %0, [%1];" : "=d"(v) : "l"(p));
-    return v;
-}
 __device__ __forceinline__ void ld_v4f64(const double* p, double& x, double& y, double& z, double& w) {   // 32 bytes
     asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(x), "=d"(y), "=d"(z), "=d"(w) : "l"(p));
 }
-__device__ __forceinline__ void lds_v2u32(uint32_t addr, uint32_t& a, uint32_t& b) {
-    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
-}
-__device__ __forceinline__ void sts_u32f(uint32_t addr, uint32_t v) {
-    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
-
 // Locate the bin whose cumulative count first reaches rho (1-based) in a 256-bin histogram; one full warp.
 // Returns false when the histogram holds fewer than rho entries.  total = all entries.
 __device__ __forceinline__ bool warp_find_bin(const unsigned* hist, unsigned rho, int lane, int& bin, unsigned& before,
