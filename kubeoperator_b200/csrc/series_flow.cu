@@ -124,6 +124,7 @@ struct FinState {
     int sh[NI_MAX];
     unsigned rho[NI_MAX];
     unsigned long long lo[NI_MAX];
+    uint32_t hi32[NI_MAX];   // last high key of the quantile's interval: nothing above it takes part in its rounds
     unsigned long long ans[NI_MAX];
     unsigned list_n[NI_MAX];
 };
@@ -1077,6 +1078,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                 } else {
                     const unsigned long long range = ((unsigned long long)sl->W[iv] << 32) | 0xFFFFFFFFull;
                     fs->lo[j] = (unsigned long long)sl->A[iv] << 32;
+                    fs->hi32[j] = sl->A[iv] + sl->W[iv];
                     fs->sh[j] = max(0, 64 - __clzll((long long)range) - 8);
                     fs->rho[j] = r - cb;
                     st = Q_HIST;
@@ -1115,8 +1117,13 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                                                               : (1ull << she) - 1ull;
             unsigned long long end = loj[j] + width;
             if (end < loj[j]) end = ~0ull;
+            // The 256 bins of a round may reach beyond the interval's own end (an interval that is open below starts
+            // with bins of 2^56 keys): candidates of the NEXT interval must not be counted there, or a rank that lies
+            // above this interval would be answered from the neighbour's candidates instead of being reported.
+            uint32_t e32 = (uint32_t)(end >> 32);
+            e32 = e32 < fs->hi32[j] ? e32 : fs->hi32[j];
             lo32[j] = (uint32_t)(loj[j] >> 32);
-            span32[j] = stj[j] <= Q_COLLECT ? (uint32_t)(end >> 32) - lo32[j] : 0u;
+            span32[j] = stj[j] <= Q_COLLECT ? e32 - lo32[j] : 0u;
             if (stj[j] > Q_COLLECT) lo32[j] = 0xFFFFFFFFu;   // no high word passes: (hk - lo32) wraps above span
         }
         auto visit = [&](unsigned long long key, unsigned mult) {
