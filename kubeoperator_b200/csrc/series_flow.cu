@@ -1190,7 +1190,9 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
                     bool hv = false;
                     if (lane < nheavy) {
                         const unsigned long long hk = sl->heavy[lane];
-                        hv = hk >= nlo && ((hk - nlo) >> sh) == 0ull && sm.hcnt()[pw.d * F_NH + lane] == cnt;
+                        // (inside the bin AND inside the interval: only then was it counted into this bin)
+                        hv = hk >= nlo && ((hk - nlo) >> sh) == 0ull && (uint32_t)(hk >> 32) <= fs->hi32[j] &&
+                             sm.hcnt()[pw.d * F_NH + lane] == cnt;
                     }
                     const unsigned hb = __ballot_sync(0xffffffffu, hv);
                     if (lane == 0) {
