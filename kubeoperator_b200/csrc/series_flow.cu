@@ -47,7 +47,12 @@ constexpr int F_STAGE = 512;                   // samples per ring stage (4 KB):
 constexpr int F_STAGE_BYTES = F_STAGE * 8;
 constexpr int F_GS = 4;                        // stages per ring group: one TMA copy and one pair of barriers (16 KB)
 constexpr int F_GROUP_BYTES = F_GS * F_STAGE_BYTES;
-constexpr int F_NGROUPS = 7;
+constexpr int F_NGROUPS = 7;                   // ring groups when two series share the candidate pool (112 KB)
+// Long-series mode: 19 stream warps hold 19 of the ring's stages, which left 9 stages for copies in flight.  The
+// candidate pool is of little use there (until the finish warps release it, most of a series' candidates go to the
+// spill), so the ring takes 32 KB of it: 9 groups = 36 stages, and 3 072 pool entries remain.
+constexpr int F_NGROUPS_LONG = 9;
+constexpr int F_NGROUPS_MAX = 9;
 constexpr int F_NSTAGES = F_NGROUPS * F_GS;
 constexpr int F_PF = 8;                        // groups asked into L2 ahead of the ring
 constexpr int F_ND = 4;                        // series slots (descriptor + plan + partials)
@@ -63,7 +68,7 @@ constexpr uint32_t HK_NINF = 0x000FFFFFu;      // high key of -inf; anything bel
 constexpr uint32_t HK_NONE = 0xFFFFFFFFu;      // a sample that takes no part (stale or outside the series)
 constexpr uint32_t HK_UNUSED = 0xFFFFFFFEu;    // A of an unused interval (W = 0): no key equals it, HK_NONE is above
 
-enum { FB_FULL = 0, FB_EMPTY = FB_FULL + F_NGROUPS, FB_DESC = FB_EMPTY + F_NGROUPS, FB_PLAN = FB_DESC + F_ND,
+enum { FB_FULL = 0, FB_EMPTY = FB_FULL + F_NGROUPS_MAX, FB_DESC = FB_EMPTY + F_NGROUPS_MAX, FB_PLAN = FB_DESC + F_ND,
        FB_FREE = FB_PLAN + F_ND, FB_SDONE = FB_FREE + F_ND, FB_START = FB_SDONE + F_ND, FB_COUNT = FB_START + F_ND };
 
 struct alignas(16) FlowSlot {
@@ -238,8 +243,8 @@ __device__ __forceinline__ PoolWin pool_window(bool single, uint32_t k, int spil
     if (single) {
         w.win = 0;
         w.use = k;
-        w.s_base = 0;
-        w.s_cap = F_POOL;
+        w.s_base = (uint32_t)(F_NGROUPS_LONG - F_NGROUPS) * F_GROUP_BYTES / 8u;   // behind the ring's extra groups
+        w.s_cap = F_POOL - w.s_base;
     } else {
         w.win = (int)(k & 1u);
         w.use = k >> 1;
@@ -249,10 +254,19 @@ __device__ __forceinline__ PoolWin pool_window(bool single, uint32_t k, int spil
     return w;
 }
 
-__device__ __forceinline__ void wait_group_full(const FlowSmem& sm, uint32_t grp) {
+// Ring slot and use count of ring group grp: grp / ng by a multiplication (exact for grp < 2^32 / 9).
+__device__ __forceinline__ void ring_slot(uint32_t grp, bool single, uint32_t& s, uint32_t& u) {
+    const uint32_t ng = single ? (uint32_t)F_NGROUPS_LONG : (uint32_t)F_NGROUPS;
+    const uint32_t magic = single ? 0xFFFFFFFFu / F_NGROUPS_LONG + 1u : 0xFFFFFFFFu / F_NGROUPS + 1u;
+    u = __umulhi(grp, magic);
+    s = grp - u * ng;
+}
+__device__ __forceinline__ void wait_group_full(const FlowSmem& sm, uint32_t grp, bool single) {
     volatile unsigned* iss = sm.issued();
     while (*iss <= grp) __nanosleep(64);
-    mbar_wait(sm.bar(FB_FULL + (int)(grp % F_NGROUPS)), (grp / F_NGROUPS) & 1u);
+    uint32_t s, u;
+    ring_slot(grp, single, s, u);
+    mbar_wait(sm.bar(FB_FULL + (int)s), u & 1u);
 }
 __device__ __forceinline__ void plan_sync(int nthreads) { asm volatile("bar.sync 3, %0;" ::"r"(nthreads) : "memory"); }
 __device__ __forceinline__ void fin_sync() { asm volatile("bar.sync 2, %0;" ::"n"(F_NF * 32) : "memory"); }
@@ -944,7 +958,7 @@ __device__ __forceinline__ void patch_stage_edges(uint32_t stage_addr, int lane,
     __syncwarp();
 }
 
-// Stage j of a series (ring stage g = g0 + j) belongs to stream warp j % ns and to ring group (g / F_GS) % F_NGROUPS.  A series
+// Stage j of a series (ring stage g = g0 + j) belongs to stream warp j % ns and to ring group (g / F_GS) % (ring groups).  A series
 // starts on a group boundary; the stage numbers that pad its last group are visited too (wait, release, no work),
 // so that every group gets its F_GS releases.
 template <int NI>
@@ -967,10 +981,11 @@ __device__ __forceinline__ void stream_series(const SeriesArgs& a, const FlowSme
     for (int j = ws; j < npad; j += ns) {
         const uint32_t g = *reinterpret_cast<const volatile uint32_t*>(&sl->g0) + (uint32_t)j;   // (reloaded: registers)
         const uint32_t grp = g / F_GS;
-        const uint32_t s = grp % F_NGROUPS;
+        uint32_t s, u_unused;
+        ring_slot(grp, single, s, u_unused);
         const uint32_t stage_addr = ring0 + s * (uint32_t)F_GROUP_BYTES + (g % F_GS) * (uint32_t)F_STAGE_BYTES;
         if (lane == 0 && ws < 3) FP(5 + ws, 0, 16 + j);
-        wait_group_full(sm, grp);
+        wait_group_full(sm, grp, single);
         FT_MARK(32);   // stream warp 0: waiting for a full stage
         if (j < n) {
             if (j == 0 || j == n - 1) {
@@ -1317,7 +1332,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
     const int ns = single ? F_NS_LONG : F_NS_SHORT, np = single ? F_NP_LONG : F_NP_SHORT;
     const int w_fin = ns, w_plan = ns + F_NF;
     if (tid == 0) {
-        for (int s = 0; s < F_NGROUPS; ++s) {
+        for (int s = 0; s < F_NGROUPS_MAX; ++s) {
             mbar_init(sm.bar(FB_FULL + s), 1);
             mbar_init(sm.bar(FB_EMPTY + s), F_GS);   // the four warps that scan the group's stages
         }
@@ -1365,7 +1380,8 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
                 }
                 for (int gi = 0; gi < ngroups; ++gi) {
                     const uint32_t grp = grp0 + (uint32_t)gi;
-                    const uint32_t s = grp % F_NGROUPS, u = grp / F_NGROUPS;
+                    uint32_t s, u;
+                    ring_slot(grp, single, s, u);
                     FT_MARK(2);   // producer: issuing
                     FP(0, k, 16 + gi);
                     if (u > 0) mbar_wait(sm.bar(FB_EMPTY + s), (u - 1u) & 1u);
