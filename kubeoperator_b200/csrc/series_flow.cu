@@ -94,6 +94,11 @@ struct alignas(16) FlowSlot {
     int qiv[NI_MAX];         // interval of quantile j
     double mn_seed, mx_seed; // valid samples of the series (or +inf / -inf): start of the running extremes
     unsigned long long heavy[F_NH];  // keys of heavy tie levels (zero canonical)
+    // the same levels in a 16-slot hash table (the scan looks every flagged sample up): slot heavy_slot(key, hmul) holds
+    // the key (or ~0) and htab_h its index in heavy[]; hmul == 0: no collision-free multiplier found, linear search
+    unsigned long long htab[16];
+    unsigned char htab_h[16];
+    uint32_t hmul;
 };
 
 struct alignas(16) FlowPartial {
@@ -346,6 +351,10 @@ __device__ __forceinline__ bool warp_find_bin(const unsigned* hist, unsigned rho
 }
 
 // ------------------------------------------------------------------------------------------------ planner
+__device__ __forceinline__ uint32_t heavy_slot(unsigned long long key, uint32_t mul) {
+    const uint32_t t = (uint32_t)(key >> 32) ^ ((uint32_t)key * 0x85EBCA6Bu);
+    return (t * mul) >> 28;
+}
 __device__ __forceinline__ int sample_size(int L) {
     int s = 256;
     while (s < F_SMAX && s * 16 <= L) s <<= 1;   // about L/16 .. L/32 points, 256 .. 8192
@@ -712,6 +721,28 @@ __device__ __forceinline__ void planner_plan(const SeriesArgs& a, const FlowSmem
         const double expect = (double)pts * (double)L / (double)S * 1.25 + 256.0;
         sl->ni = ni;
         sl->nheavy = nh;
+        {   // hash table of the listed levels
+            uint32_t mul = 0u;
+            for (int tr = 0; tr < 16 && mul == 0u && nh > 0; ++tr) {
+                const uint32_t m = (0x9E3779B1u + (uint32_t)tr * 0x632BE5ABu) | 1u;
+                unsigned used = 0u;
+                bool ok = true;
+                for (int h = 0; h < nh; ++h) {
+                    const unsigned bit = 1u << heavy_slot(sl->heavy[h], m);
+                    ok = ok && !(used & bit);
+                    used |= bit;
+                }
+                if (ok) mul = m;
+            }
+            for (int i = 0; i < 16; ++i) sl->htab[i] = ~0ull;
+            if (mul != 0u)
+                for (int h = 0; h < nh; ++h) {
+                    const uint32_t i = heavy_slot(sl->heavy[h], mul);
+                    sl->htab[i] = sl->heavy[h];
+                    sl->htab_h[i] = (unsigned char)h;
+                }
+            sl->hmul = mul;
+        }
         sl->mn_seed = ko_key2d(kmin64);
         sl->mx_seed = ko_key2d(kmax64);
         if (expect > (double)(pw.s_cap + pw.g_cap)) {
@@ -879,17 +910,32 @@ __device__ __forceinline__ void store_candidates(const SeriesArgs& a, const Flow
     const int nheavy = sl->nheavy;
     if (nheavy > 0) {
         uint32_t rest = m;
+        const uint32_t hmul = sl->hmul;
+        if (hmul != 0u) {   // one probe of the 16-slot table per flagged sample
 #pragma unroll 1
-        while (rest) {
-            const int b = __ffs(rest) - 1;
-            rest &= rest - 1;
-            const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lane * 16u + flag_offset(b)) + 0.0);
-            int hit = -1;
+            while (rest) {
+                const int b = __ffs(rest) - 1;
+                rest &= rest - 1;
+                const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lane * 16u + flag_offset(b)) + 0.0);
+                const uint32_t i = heavy_slot(key, hmul);
+                if (sl->htab[i] == key) {
+                    red_shared_add(&sm.hcnt()[pw.d * F_NH + sl->htab_h[i]], 1u);
+                    m &= ~(1u << b);
+                }
+            }
+        } else {
 #pragma unroll 1
-            for (int h = 0; h < nheavy; ++h) hit = sl->heavy[h] == key ? h : hit;
-            if (hit >= 0) {
-                red_shared_add(&sm.hcnt()[pw.d * F_NH + hit], 1u);
-                m &= ~(1u << b);
+            while (rest) {
+                const int b = __ffs(rest) - 1;
+                rest &= rest - 1;
+                const unsigned long long key = ko_okey(lds_f64(stage_addr + (uint32_t)lane * 16u + flag_offset(b)) + 0.0);
+                int hit = -1;
+#pragma unroll 1
+                for (int h = 0; h < nheavy; ++h) hit = sl->heavy[h] == key ? h : hit;
+                if (hit >= 0) {
+                    red_shared_add(&sm.hcnt()[pw.d * F_NH + hit], 1u);
+                    m &= ~(1u << b);
+                }
             }
         }
         if (!__any_sync(0xffffffffu, m != 0u)) return;
