@@ -75,10 +75,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "r"(parity)
         : "memory");
 }
-// Wait for roles that idle for long: one look at the barrier, then a plain nanosleep.  (Measured on B200: neither
-// this loop nor a try_wait loop with a time hint really sleeps - both come back every 15-30 cycles - but the
-// instructions they issue fill slots nobody else wants: the kernel is bound by dependent-instruction latency in the
-// scan warps, and its time is the same with either form of waiting.)
+// Wait for roles that idle for long: one look at the barrier, then a plain nanosleep (measured on B200:
+// nanosleep(400) suspends a warp for ~1 000 cycles, whatever the number of resident warps).  Whether the long waits
+// poll every 400 ns or every 4 us, or sit in a try_wait loop, makes no measurable difference to the kernel.
 template <int NS>
 __device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
