@@ -25,7 +25,8 @@ cudaError_t ko_flow_launch(const void* series_args, int grid, cudaStream_t st);
 
 namespace {
 
-constexpr int SMALL_MAX = 1024;      // series up to this length take the warp path
+constexpr int SMALL_MAX = 1024;      // series up to this length take the warp paths
+constexpr int SMALL_SHORT = 256;     // ... up to this one series_small, above it series_medium (through a work list)
 constexpr int NCONS = 256;           // consumer threads of series_long
 constexpr int NCWARPS = NCONS / 32;
 constexpr int NTHREADS = NCONS + 32; // + one producer warp
@@ -81,19 +82,34 @@ __device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"
 
 
 // ------------------------------------------------------------------------------------ classify kernel
+// Appends `item` of every lane with `want` set to list[...] behind the counter: one atomic per warp.
+__device__ __forceinline__ void warp_append(int* counter, int* list, bool want, int item) {
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == __ffs(m) - 1) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+    if (want) list[base + __popc(m & ((1u << lane) - 1u))] = item;
+}
 __global__ void classify_series(SeriesArgs a) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.n_series) return;
-    int64_t L = a.offsets[i + 1] - a.offsets[i];
-    if (L < 0 || L >= 2147483647LL) {
-        atomicExch(&a.counters[2], 1);
-        return;
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // (blockDim.x is a multiple of 32: whole warps)
+    int64_t L = 0;
+    if (i < a.n_series) {
+        L = a.offsets[i + 1] - a.offsets[i];
+        if (L < 0 || L >= 2147483647LL) {
+            atomicExch(&a.counters[2], 1);
+            L = 0;
+        }
     }
-    if (L > SMALL_MAX) {
-        int pos = atomicAdd(&a.counters[0], 1);
-        a.long_list[pos] = (int)i;
-        atomicMax(&a.counters[8], (int)L);   // series_flow: whether two series can share the candidate pool
-    }
+    const bool is_long = L > SMALL_MAX, is_medium = !is_long && L > SMALL_SHORT;
+    warp_append(&a.counters[0], a.long_list, is_long, (int)i);
+    // (the list of medium series lives where the first series_flow launch later writes its deferred items:
+    // series_medium is done by then)
+    warp_append(&a.counters[16], a.defer_list, is_medium, (int)i);
+    int Lmax = is_long ? (int)L : 0;
+    Lmax = __reduce_max_sync(0xffffffffu, Lmax);
+    if ((threadIdx.x & 31) == 0 && Lmax > 0) atomicMax(&a.counters[8], Lmax);   // series_flow: may two series share the pool
 }
 
 // ------------------------------------------------------------------------------- warp path (<= 1024)
@@ -511,7 +527,6 @@ __device__ __forceinline__ SmallStats small_stats(const SeriesArgs& a, const dou
 // Series of at most SMALL_SHORT samples: SMALL_PER_WARP consecutive series per warp.  When all of them have at most 32
 // samples they are computed four at a time side by side (small_quad), the loads of all of them issued before the
 // first is used; else one after the other by the whole warp (small_one).  Longer series are skipped here.
-constexpr int SMALL_SHORT = 256;
 constexpr int SMALL_PER_WARP = 16;
 __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
     extern __shared__ __align__(16) unsigned char smem_small[];
@@ -568,15 +583,11 @@ __global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
     }
 }
 
-// Series of SMALL_SHORT + 1 .. SMALL_MAX samples: one warp per series, keys in shared memory, MSB-first radix select.
-__global__ void __launch_bounds__(256) series_medium(SeriesArgs a) {
-    extern __shared__ __align__(16) unsigned char smem_small[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t sid = (int64_t)blockIdx.x * 8 + warp;
-    if (sid >= a.n_series) return;
+__device__ __forceinline__ void series_medium_one(const SeriesArgs& a, int64_t sid, int warp, int lane,
+                                                  unsigned char* smem_small) {
     const int64_t off0 = a.offsets[sid];
     const int64_t Ll = a.offsets[sid + 1] - off0;
-    if (Ll > SMALL_MAX || Ll <= SMALL_SHORT) return;
+    if (Ll > SMALL_MAX || Ll <= SMALL_SHORT) return;   // (direct mode: not every series is this kernel's)
     const int L = (int)Ll;
     const double* v = a.values + off0;
     unsigned long long* keys = nullptr;
@@ -597,6 +608,24 @@ __global__ void __launch_bounds__(256) series_medium(SeriesArgs a) {
             }
             if (lane == 0) a.out_quant[sid * a.nq + a.qcol[j]] = r;
         }
+    }
+}
+
+// Series of SMALL_SHORT + 1 .. SMALL_MAX samples: one warp per series of the list classify_series made (a fixed grid
+// walks it: a batch without such series costs one idle launch, not a CTA per eight series), keys in shared memory,
+// MSB-first radix select.
+__global__ void __launch_bounds__(256) series_medium(SeriesArgs a, int direct) {
+    extern __shared__ __align__(16) unsigned char smem_small[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (direct) {   // statistics only: no key buffers, CTAs are cheap, one warp per series of the batch
+        const int64_t sid = (int64_t)blockIdx.x * 8 + warp;
+        if (sid < a.n_series) series_medium_one(a, sid, warp, lane, smem_small);
+        return;
+    }
+    const int n_medium = a.counters[16];
+    for (int w = blockIdx.x * 8 + warp; w < n_medium; w += gridDim.x * 8) {
+        series_medium_one(a, a.defer_list[w], warp, lane, smem_small);
+        __syncwarp();   // the warp's key buffer is reused by its next series
     }
 }
 
@@ -1581,7 +1610,7 @@ __global__ void series_tally(const int* counters, int* tally) {
     tally[2] |= counters[2];
 }
 
-constexpr int N_COUNTERS = 16;
+constexpr int N_COUNTERS = 24;   // [16]: series of SMALL_SHORT + 1 .. SMALL_MAX samples (series_medium's list)
 constexpr int SPILL_MAX = 65536;         // candidate keys one series_flow CTA may spill to global scratch
 // counters + the two work lists, rounded so that the spill space behind them is 256-byte aligned.  A list has room
 // for KO_MAX_QUANTILES entries per series: the first attempt of series_flow defers single quantiles.
@@ -1673,7 +1702,15 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
 static void launch_short_paths(const SeriesArgs& a, int64_t n_series, int nq, cudaStream_t st) {
     series_small<<<(unsigned)((n_series + 8 * SMALL_PER_WARP - 1) / (8 * SMALL_PER_WARP)), 256, 8 * SMALL_SCRATCH_BYTES, st>>>(a);
     const size_t medium_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
-    series_medium<<<(unsigned)((n_series + 7) / 8), 256, medium_smem, st>>>(a);
+    unsigned mgrid = (unsigned)((n_series + 7) / 8);
+    // with key buffers (74 KB per CTA, three per SM) a fixed grid walks the list: a batch of a million alert windows
+    // must not pay for 125 000 CTAs that find nothing to do
+    // statistics only and a batch of moderate size: one warp per series of the batch, no list (CTAs without key
+    // buffers that find nothing to do are cheap up to a few ten thousand of them)
+    const int direct = (nq == 0 && n_series <= 262144) ? 1 : 0;
+    const unsigned mcap = nq > 0 ? 12u * 148u : 64u * 148u;
+    if (!direct && mgrid > mcap) mgrid = mcap;
+    series_medium<<<mgrid, 256, medium_smem, st>>>(a, direct);
 }
 
 static int fill_args(SeriesArgs& a, const double* d_values, const int64_t* d_offsets, int64_t n_series,
