@@ -3,10 +3,12 @@
 // PromQL strings for this (core/apps/kubeops_api/prometheus_client.py:90-111), see include/korollup.h.
 //
 // HBM-bound by design: 8 algorithmic bytes per sample, read once.  Kernels of one call:
-//   classify_series   - builds the work list of long series (scratch), finds the longest, validates offsets
+//   classify_series   - builds the work lists of long and of medium series (scratch), finds the longest, validates
+//                       offsets
 //   series_small      - series of <= 256 samples, 16 per warp: four windows of <= 32 samples side by side (quantiles
 //                       by rank counting), 33..256 samples in registers with a one-pass histogram select
-//   series_medium     - series of 257..1024 samples: one warp per series, keys in shared memory, MSB radix select
+//   series_medium     - series of 257..1024 samples, from classify's list: one warp per series, keys in shared
+//                       memory, MSB radix select
 //   series_flow       - series_flow.cu: persistent, one CTA of 32 warps per SM, warp-specialised; plan (pre-sample,
 //                       key interval per quantile), TMA ring, scan (statistics + "count below the interval, keep
 //                       what is inside it") and exact selection among the kept candidates in ONE pass over HBM
