@@ -530,7 +530,7 @@ __device__ __forceinline__ SmallStats small_stats(const SeriesArgs& a, const dou
 // samples they are computed four at a time side by side (small_quad), the loads of all of them issued before the
 // first is used; else one after the other by the whole warp (small_one).  Longer series are skipped here.
 constexpr int SMALL_PER_WARP = 16;
-__global__ void __launch_bounds__(256) series_small(SeriesArgs a) {
+__global__ void __launch_bounds__(256, 4) series_small(SeriesArgs a) {
     extern __shared__ __align__(16) unsigned char smem_small[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t sid0 = ((int64_t)blockIdx.x * 8 + warp) * SMALL_PER_WARP;
