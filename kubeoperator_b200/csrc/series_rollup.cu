@@ -495,17 +495,25 @@ __device__ __forceinline__ SmallStats small_stats(const SeriesArgs& a, const dou
     double sum = 0.0, mn = INFINITY, mx = -INFINITY;
     unsigned nv = 0;
     int last_idx = -1;
-    for (int i = lane; i < L; i += 32) {
-        double x = ko_ld_stream(v + i);
-        bool ok = (x == x);
-        if (ok) {
-            sum += x;
-            nv++;
-            last_idx = i;
+    const double qnan = __longlong_as_double(0x7FF8000000000000LL);
+    for (int i0 = lane; i0 < L; i0 += 128) {   // four loads of a lane in flight
+        double x4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) x4[u] = i0 + 32 * u < L ? ko_ld_stream(v + i0 + 32 * u) : qnan;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = i0 + 32 * u;
+            const double x = x4[u];
+            const bool ok = (x == x);
+            if (ok) {
+                sum += x;
+                nv++;
+                last_idx = i;
+            }
+            mn = fmin(mn, x);
+            mx = fmax(mx, x);
+            if (keys && i < L) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
         }
-        mn = fmin(mn, x);
-        mx = fmax(mx, x);
-        if (keys) keys[i] = ok ? ko_okey(x + 0.0) : KO_KEY_NAN;
     }
     sum = warp_sum(sum);
     mn = warp_min(mn);
@@ -585,6 +593,93 @@ __global__ void __launch_bounds__(256, 4) series_small(SeriesArgs a) {
     }
 }
 
+// Quantiles of a series whose keys lie in shared memory (257 .. 1024 samples): like small_hist_quantiles - one 256-bin
+// histogram over [min, max] for all quantiles, then per quantile the keys of its bin are compacted (<= 32) and
+// rank-counted.  Returns false (nothing written) when a bin is more crowded: the caller falls back to the radix select.
+constexpr int MEDIUM_SMEM_BYTES = 8 * SMALL_MAX * 8 + 8 * HBINS * 4 + 8 * 32 * 8;
+__device__ __forceinline__ bool medium_hist_quantiles(const SeriesArgs& a, const unsigned long long* keys, int L,
+                                                      unsigned nv, double mn, double mx, int64_t sid, int lane,
+                                                      unsigned* hist, unsigned long long* cand) {
+    const unsigned long long kmin = ko_okey(mn + 0.0), diff = ko_okey(mx + 0.0) - kmin;
+    const int sh = max(0, 56 - __clzll((long long)diff));   // (diff >> sh) <= 255
+    reinterpret_cast<uint4*>(hist)[lane * 2] = make_uint4(0u, 0u, 0u, 0u);
+    reinterpret_cast<uint4*>(hist)[lane * 2 + 1] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    for (int i = lane; i < L; i += 32) {
+        const unsigned long long k = keys[i];
+        if (k != KO_KEY_NAN) red_shared_add(&hist[(unsigned)((k - kmin) >> sh)], 1u);
+    }
+    __syncwarp();
+    const uint4 h0 = reinterpret_cast<const uint4*>(hist)[lane * 2], h1 = reinterpret_cast<const uint4*>(hist)[lane * 2 + 1];
+    const unsigned c[8] = {h0.x, h0.y, h0.z, h0.w, h1.x, h1.y, h1.z, h1.w};
+    unsigned s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += c[i];
+    unsigned incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    unsigned qb[NI_MAX], qbefore[NI_MAX], qcnt[NI_MAX];
+    bool crowded = false;
+#pragma unroll
+    for (int j = 0; j < NI_MAX; ++j) {
+        qb[j] = qbefore[j] = qcnt[j] = 0u;
+        if (j < a.nq) {
+            const unsigned p = nearest_rank_dev(nv, a.q[j]) - 1u;
+            const int src = __ffs(__ballot_sync(0xffffffffu, incl > p)) - 1;
+            unsigned b = 0, before = 0, cnt = 0;
+            if (lane == src) {
+                unsigned run = incl - s;
+                bool found = false;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (!found && run + c[i] > p) {
+                        b = (unsigned)(lane * 8 + i);
+                        before = run;
+                        cnt = c[i];
+                        found = true;
+                    }
+                    run += c[i];
+                }
+            }
+            qb[j] = __shfl_sync(0xffffffffu, b, src);
+            qbefore[j] = __shfl_sync(0xffffffffu, before, src);
+            qcnt[j] = __shfl_sync(0xffffffffu, cnt, src);
+            crowded = crowded || qcnt[j] > 32u;
+        }
+    }
+    if (crowded) return false;
+#pragma unroll
+    for (int j = 0; j < NI_MAX; ++j) {
+        if (j < a.nq) {
+            unsigned base = 0;
+            for (int i0 = 0; i0 < L; i0 += 32) {
+                const int i = i0 + lane;
+                const unsigned long long k = i < L ? keys[i] : KO_KEY_NAN;
+                const bool hit = k != KO_KEY_NAN && (unsigned)((k - kmin) >> sh) == qb[j];
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) cand[base + __popc(m & ((1u << lane) - 1u))] = k;
+                base += __popc(m);
+            }
+            __syncwarp();
+            const unsigned cnt = qcnt[j], rho = nearest_rank_dev(nv, a.q[j]) - 1u - qbefore[j];
+            const unsigned long long mine = lane < (int)cnt ? cand[lane] : KO_KEY_NAN;
+            int less = 0;
+#pragma unroll 1
+            for (unsigned i = 0; i < cnt; ++i) less += cand[i] < mine ? 1 : 0;
+            const int best = (lane < (int)cnt && (unsigned)less <= rho) ? less : -1;
+            const int top = __reduce_max_sync(0xffffffffu, best);
+            const int owner = __ffs(__ballot_sync(0xffffffffu, best == top)) - 1;
+            const unsigned long long key = __shfl_sync(0xffffffffu, mine, owner);
+            if (lane == 0) a.out_quant[sid * a.nq + a.qcol[j]] = ko_key2d(key);
+            __syncwarp();   // cand is reused by the next quantile
+        }
+    }
+    return true;
+}
+
 __device__ __forceinline__ void series_medium_one(const SeriesArgs& a, int64_t sid, int warp, int lane,
                                                   unsigned char* smem_small) {
     const int64_t off0 = a.offsets[sid];
@@ -601,6 +696,12 @@ __device__ __forceinline__ void series_medium_one(const SeriesArgs& a, int64_t s
     const SmallStats st = small_stats(a, v, L, sid, lane, keys);
     if (a.nq > 0 && a.out_quant) {
         __syncwarp();
+        if (st.nv > 0 && st.mn != st.mx) {
+            unsigned long long* cand = reinterpret_cast<unsigned long long*>(smem_small + (size_t)8 * SMALL_MAX * 8 +
+                                                                             (size_t)8 * HBINS * 4) + warp * 32;
+            if (medium_hist_quantiles(a, keys, L, st.nv, st.mn, st.mx, sid, lane, hist, cand)) return;
+            __syncwarp();
+        }
         const unsigned long long kmin = ko_okey(st.mn + 0.0), kmax = ko_okey(st.mx + 0.0);
         for (int j = 0; j < a.nq; ++j) {
             double r = __longlong_as_double(0x7FF8000000000000LL);
@@ -1630,8 +1731,7 @@ int series_set_attributes(int device) {
     std::lock_guard<std::mutex> lk(g_attr_mu);
     if (g_attr_dev[device]) return KO_OK;
     KO_CUDA(cudaFuncSetAttribute(series_long, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LONG_SMEM_BYTES));
-    KO_CUDA(cudaFuncSetAttribute(series_medium, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 8 * SMALL_MAX * 8 + 8 * HBINS * 4));
+    KO_CUDA(cudaFuncSetAttribute(series_medium, cudaFuncAttributeMaxDynamicSharedMemorySize, MEDIUM_SMEM_BYTES));
     KO_CUDA(ko_flow_set_attributes());
     g_attr_dev[device] = true;
     return KO_OK;
@@ -1703,7 +1803,7 @@ static cudaError_t launch_long_path(SeriesArgs a, int num_sms, int64_t n_series,
 // The two kernels of the series that are not long: each skips the series that are not its own.
 static void launch_short_paths(const SeriesArgs& a, int64_t n_series, int nq, cudaStream_t st) {
     series_small<<<(unsigned)((n_series + 8 * SMALL_PER_WARP - 1) / (8 * SMALL_PER_WARP)), 256, 8 * SMALL_SCRATCH_BYTES, st>>>(a);
-    const size_t medium_smem = nq > 0 ? (size_t)8 * SMALL_MAX * 8 + (size_t)8 * HBINS * 4 : 0;
+    const size_t medium_smem = nq > 0 ? (size_t)MEDIUM_SMEM_BYTES : 0;
     unsigned mgrid = (unsigned)((n_series + 7) / 8);
     // with key buffers (74 KB per CTA, three per SM) a fixed grid walks the list: a batch of a million alert windows
     // must not pay for 125 000 CTAs that find nothing to do
