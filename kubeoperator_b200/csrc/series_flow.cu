@@ -900,7 +900,7 @@ __device__ __forceinline__ uint32_t flag_offset(int b) { return (uint32_t)(b >> 
 // warp's candidates is reserved with one atomic on the slot's cursor (shared-memory window first - when the finish
 // warps have released it - then the global spill window), then every lane copies its own.  Samples on a listed tie
 // level are counted instead.  flags: bit 0 = the shared-memory window is ours, bit 1 = something did not fit,
-// bit 2 = something went to the spill.
+// bit 2 = something went to the spill, bit 3 = short series: wait for the window rather than spill.
 __device__ __forceinline__ void store_candidates(const SeriesArgs& a, const FlowSmem& sm, bool single, uint32_t kser,
                                                  uint32_t stage_addr, uint32_t m, int lane, uint32_t& flags) {
     // (everything but the flags is looked up again here: the scan loop around this call has no registers to spare)
@@ -944,7 +944,9 @@ __device__ __forceinline__ void store_candidates(const SeriesArgs& a, const Flow
     if (!(flags & 1u)) {   // shared-memory window not released yet: spill, or wait when the spill is full
         volatile unsigned* rel = reinterpret_cast<volatile unsigned*>(&sm.rel()[pw.win]);
         bool ok = *rel >= pw.use;
-        if (!ok && *reinterpret_cast<volatile unsigned*>(&sm.cgl()[pw.d]) + 512u > pw.g_cap) {
+        // Short series (their finish is quick and is what bounds the CTA): wait, so that the finish warps find every
+        // candidate in shared memory instead of reading the spill back through L2.
+        if (!ok && ((flags & 8u) || *reinterpret_cast<volatile unsigned*>(&sm.cgl()[pw.d]) + 512u > pw.g_cap)) {
             while (*rel < pw.use) __nanosleep(200);
             ok = true;
         }
@@ -1060,6 +1062,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
     const int nq = a.nq, ni = sl->ni;
     const int L = sl->L, sid = sl->sid;
     const double nan = __longlong_as_double(0x7FF8000000000000LL);
+    FT_BEGIN(blockIdx.x == 0 && ftid == 0);
     // ---- A. partial statistics (warp 0, fixed order) and the last valid sample (warp 1)
     if (fw == 0) {
         const FlowPartial* p = sm.part(d, lane < ns ? lane : 0);
@@ -1103,6 +1106,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
         fs->last = lastv;
     }
     fin_sync();
+    FT_MARK(23);   // finish A: partials, last sample
     const unsigned nvalid = fs->nvalid;
     unsigned npool_raw = 0;
     const unsigned nsm_all = ni > 0 ? min(sm.csm()[pw.d], pw.s_cap) : 0u;
@@ -1155,11 +1159,16 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
         if (st == Q_FAIL) fs->fail = 1;
     }
     fin_sync();
+    FT_MARK(24);   // finish B: start state
     // ---- C. rounds: histogram refinement, then direct selection among <= F_LIST candidates
     int guard = 0;
     while (fs->pending > 0 && guard++ < 24) {   // (a quantile that fails does not stop the others)
+#ifdef KO_FLOW_TIMING
+        if (_ftc) atomicAdd(&g_flow_phase[26], 1000ull);   // rounds (x 1000: the report divides by 1000)
+#endif
         for (int i = ftid; i < NI_MAX * 256; i += F_NF * 32) sm.fbins()[i] = 0;
         fin_sync();
+        FT_MARK(28);   // finish C: clearing the bins
         int stj[NI_MAX], shj[NI_MAX];
         unsigned long long loj[NI_MAX];
 #pragma unroll
@@ -1211,6 +1220,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
             const unsigned long long* wbase = sm.pool() + pw.s_base;
 #pragma unroll 1
             for (unsigned i = ftid; i < nsm; i += F_NF * 32) visit(wbase[i], 1u);
+            FT_MARK(29);   // finish C: candidates in shared memory
             if (ng > 0u) {   // spilled part: global loads, four in flight
                 const unsigned long long* gbase = spill + pw.g_base;
 #pragma unroll 1
@@ -1230,6 +1240,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
             if (mult) visit(sl->heavy[ftid], mult);
         }
         fin_sync();
+        FT_MARK(27);   // finish C: visiting the candidates
         // warp j settles quantile j
         if (fw < nq && fs->st[fw] <= Q_COLLECT) {
             const int j = fw;
@@ -1319,6 +1330,7 @@ __device__ __forceinline__ void finish_series(const SeriesArgs& a, const FlowSme
         }
         fin_sync();
     }
+    FT_MARK(25);   // finish C: rounds
     // ---- D. outputs
     if (ftid == 0) {
         const bool fail = fs->fail != 0 || fs->pending > 0;
@@ -1582,7 +1594,7 @@ __global__ void __launch_bounds__(F_THREADS, 1) series_flow(SeriesArgs a) {
             const int ni = sl->ni;
             // the shared-memory window was last used by series k - 1 (one pool) or k - 2 (two halves); until the
             // finish warps have released it this series' candidates go to the spill window
-            uint32_t flags = pool_window(single, k, a.spill_cap).use == 0u ? 1u : 0u;
+            uint32_t flags = (pool_window(single, k, a.spill_cap).use == 0u ? 1u : 0u) | (sl->depth1 == 0 ? 8u : 0u);
             switch (ni) {
                 case 0: stream_series<0>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;
                 case 1: stream_series<1>(a, sm, sl, acc, ws, ns, lane, single, k, flags); break;

@@ -33,7 +33,7 @@ pms = r.last_series_pipe_ms()
 names = {0: "producer wait desc", 1: "producer wait empty stage", 2: "producer issue", 5: "planner wait finish",
          6: "planner plan (total)", 10: "  plan: gather", 11: "  plan: round 1 + targets", 12: "  plan: round 2",
          13: "  plan: heavy levels", 14: "  plan: thread 0", 20: "finish wait plan", 21: "finish wait stream",
-         22: "finish work", 30: "stream0 wait plan", 31: "stream0 series work (all)", 32: "  stream0 wait full stage",
+         22: "finish work", 23: "  finish A: partials, last sample", 24: "  finish B: start state", 25: "  finish C: rounds (settling part)", 26: "  finish C: number of rounds", 27: "  finish C: spilled candidates + sync", 28: "  finish C: clearing the bins", 29: "  finish C: prefilter + candidates in shared memory", 30: "stream0 wait plan", 31: "stream0 series work (all)", 32: "  stream0 wait full stage",
          33: "  stream0 scan", 34: "  stream0 store candidates"}
 per = max(1, n // 148)
 print("L=%d n=%d nq=%d series_flow %.3f ms (%.0f GB/s), ~%d series per CTA; kcycles per series in CTA 0:" %
