@@ -383,11 +383,16 @@ def run_ours(args, rank, world, local_rank):
     fleet_out, fleet_ws = {}, {}
     fleet_rollup = Rollup(local_rank) if world > 1 else None   # own context: keeps the kernel timers of `rollup`
 
+    merge_events = []
+
     def step_dev():
         rollup.series_rollup_dev(d_values.data_ptr(), d_offsets.data_ptr(), n_series, QS, outs["sum"].data_ptr(),
                                  outs["mean"].data_ptr(), outs["min"].data_ptr(), outs["max"].data_ptr(),
                                  outs["last"].data_ptr(), d_count.data_ptr(), d_quant.data_ptr(), stream)
         if world > 1:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            merge_events.append(ev)
+            ev[0].record()
             # fleet-wide merges over NCCL, all on the device, nothing read back inside the step: p95 / p99
             # over all per-series p95 values by all-reduced key histograms (16 bits per round, digit selection by a
             # one-CTA kernel), top-10 of the per-series maxima, sums of the additive scalars
@@ -396,6 +401,7 @@ def run_ours(args, rank, world, local_rank):
             fleet_out["top10_series_max"] = fleet.fleet_topk_device(outs["max"], lo, 10, dist)
             fleet_out["sum_and_count"] = fleet.fleet_scalars_device(
                 torch.stack([outs["sum"].nansum(), d_count.sum().double()]), dist)
+            ev[1].record()
 
     def sync_all():
         if world > 1:
@@ -412,11 +418,13 @@ def run_ours(args, rank, world, local_rank):
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
+    merge_events.clear()
     e0.record()
     for _ in range(args.steps):
         step_dev()
     e1.record()
     sync_all()
+    merge_ms = float(np.mean([a_.elapsed_time(b_) for a_, b_ in merge_events])) if merge_events else 0.0
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -558,6 +566,7 @@ def run_ours(args, rank, world, local_rank):
                           "reference-defined rows are pinned by tests/golden)",
         }
         if world > 1:
+            line["fleet_merge_ms_per_step"] = merge_ms     # rank 0: the NCCL merges inside the step (waits for the slowest rank)
             line["fleet"] = {k: ([x.tolist() for x in v] if isinstance(v, tuple) else v.tolist())
                              for k, v in fleet_out.items()}
         if world == 1 and not args.no_cpu_baseline:

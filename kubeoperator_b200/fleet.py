@@ -215,32 +215,37 @@ def fleet_quantiles_device(values, qs, rollup, dist=None, workspace=None):
 def fleet_topk_device(values, global_offset, k, dist=None):
     """Fleet top-k of per-series ``values`` (CUDA float64, NaN = no value) by (value descending, global index
     ascending): every shard's own top-k goes through ONE all-gather and is merged on the GPU.  Returns
-    (values[k], global_index[k]) CUDA tensors, padded with -inf / -1 when the fleet holds fewer than k values."""
+    (values[k], global_index[k]) CUDA tensors, padded with -inf / -1 when the fleet holds fewer than k values.
+    Shards hold ascending, disjoint ranges of global indices (rank order), so two stable descending sorts - one per
+    shard, one over the gathered lists in rank order - give the index-ascending order among equal values."""
     import torch
     dev = values.device
     v = values.reshape(-1)
     v = torch.where(v != v, torch.full_like(v, float("-inf")), v)            # NaN only: +inf stays +inf
     kk = min(k, v.numel())
-    top_v = torch.full((k,), float("-inf"), dtype=torch.float64, device=dev)
-    top_i = torch.full((k,), -1, dtype=torch.int64, device=dev)
     if kk:
-        order = torch.argsort(v, descending=True, stable=True)[:kk]          # ties: lower index first
-        top_v[:kk] = v[order]
-        top_i[:kk] = order + int(global_offset)
+        sv, si = torch.sort(v, descending=True, stable=True)                  # ties: lower index first
+    if kk == k:
+        top_v, top_i = sv[:k].contiguous(), si[:k] + int(global_offset)
+    else:
+        top_v = torch.full((k,), float("-inf"), dtype=torch.float64, device=dev)
+        top_i = torch.full((k,), -1, dtype=torch.int64, device=dev)
+        if kk:
+            top_v[:kk] = sv[:kk]
+            top_i[:kk] = si[:kk] + int(global_offset)
     world = dist.get_world_size() if (dist is not None and dist.is_initialized()) else 1
     if world > 1:
         gv = torch.empty(world * k, dtype=torch.float64, device=dev)
         gi = torch.empty(world * k, dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(gv, top_v)
         dist.all_gather_into_tensor(gi, top_i)
+        # (padding entries are -inf / -1 and sort behind every value; a real -inf keeps its index)
+        out_v, order = torch.sort(gv, descending=True, stable=True)
+        out_v, out_i = out_v[:k], gi[order[:k]]
     else:
-        gv, gi = top_v, top_i
-    gi_key = torch.where(gi < 0, torch.full_like(gi, torch.iinfo(torch.int64).max), gi)
-    o1 = torch.argsort(gi_key, stable=True)                                   # secondary key first (stable sorts)
-    o2 = torch.argsort(gv[o1], descending=True, stable=True)
-    sel = o1[o2][:k]
-    out_v, out_i = gv[sel], gi[sel]
-    out_i = torch.where(torch.isinf(out_v) & (out_v < 0), torch.full_like(out_i, -1), out_i)
+        out_v, out_i = top_v, top_i
+    # "no value" (NaN, mapped to -inf above) and padding carry index -1
+    out_i = torch.where(out_v == float("-inf"), torch.full_like(out_i, -1), out_i)
     return out_v, out_i
 
 
