@@ -57,9 +57,10 @@ const char* ko_last_error(void);
 int ko_init(const int* devices, int n_devices, ko_ctx** out);
 void ko_destroy(ko_ctx* ctx);
 int ko_get_counters(ko_ctx* ctx, ko_counters* out);
-/* Device time of the long-series kernels (series_plan, series_pipe, second attempt, series_long) of the most
- * recent series rollup on this ctx, measured with CUDA events on the launching stream; waits for them to
- * finish.  ko_last_series_pipe_ms: the dominant kernel alone (the first series_pipe launch of that rollup).
+/* Device time of the long-series kernels (series_flow, its second attempt, series_long) of the most recent series
+ * rollup on this ctx, measured with CUDA events on the launching stream; waits for them to finish.
+ * ko_last_series_pipe_ms: the dominant kernel alone - the first launch of the one-pass kernel of that rollup
+ * (series_flow today; the entry point keeps the name it had when that kernel was called series_pipe).
  * Used for roofline reports; no counterpart in the reference. */
 int ko_last_series_kernel_ms(ko_ctx* ctx, float* out_ms);
 int ko_last_series_pipe_ms(ko_ctx* ctx, float* out_ms);

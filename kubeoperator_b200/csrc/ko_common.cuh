@@ -45,7 +45,7 @@ struct ko_ctx {
     cudaEvent_t ev_copied[2] = {nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr};
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr;  // around the long-series kernels of the last series rollup
-    cudaEvent_t ev_p0 = nullptr, ev_p1 = nullptr;  // around its first series_pipe launch alone (roofline timing)
+    cudaEvent_t ev_p0 = nullptr, ev_p1 = nullptr;  // around its first series_flow launch alone (roofline timing)
     bool k_timed = false;
     cudaStream_t last_series_stream = nullptr;  // stream of the last ko_series_rollup_dev
     int* last_series_scratch = nullptr;         // its counters (device)

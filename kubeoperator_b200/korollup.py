@@ -174,7 +174,7 @@ class Rollup:
         return float(ms.value)
 
     def last_series_pipe_ms(self):
-        """Device time of the dominant kernel alone (first series_pipe launch of the last series rollup)."""
+        """Device time of the dominant kernel alone (first series_flow launch of the last series rollup)."""
         ms = ctypes.c_float(0)
         self._check(self._lib.ko_last_series_pipe_ms(self._ctx, ctypes.byref(ms)))
         return float(ms.value)
