@@ -47,7 +47,7 @@ typedef struct ko_counters {
     int64_t kernel_launches; /* kernels of this library launched through the ctx since ko_init       */
     int64_t h2d_bytes;       /* bytes copied host->device by host-pointer entry points               */
     int64_t d2h_bytes;       /* bytes copied device->host by host-pointer entry points               */
-    int64_t series_fallback; /* long series the pipelined fast path deferred to the slow path (last call) */
+    int64_t series_fallback; /* long series the first attempt of the one-pass kernel could not finish (last call)  */
 } ko_counters;
 
 /* ---- life cycle (no reference counterpart: the reference is pure Python) ------------------------- */
