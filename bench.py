@@ -385,6 +385,16 @@ def run_ours(args, rank, world, local_rank):
 
     merge_events = []
 
+    def merges():
+        # fleet-wide merges over NCCL, all on the device, nothing read back inside the step: p95 / p99
+        # over all per-series p95 values by all-reduced key histograms (16 bits per round, digit selection by a
+        # one-CTA kernel), top-10 of the per-series maxima, sums of the additive scalars
+        fleet_out["p95_p99_of_series_p95"] = fleet.fleet_quantiles_device(d_quant[:, 1], [0.95, 0.99], fleet_rollup,
+                                                                          dist, fleet_ws)
+        fleet_out["top10_series_max"] = fleet.fleet_topk_device(outs["max"], lo, 10, dist)
+        fleet_out["sum_and_count"] = fleet.fleet_scalars_device(
+            torch.stack([outs["sum"].nansum(), d_count.sum().double()]), dist)
+
     def step_dev():
         rollup.series_rollup_dev(d_values.data_ptr(), d_offsets.data_ptr(), n_series, QS, outs["sum"].data_ptr(),
                                  outs["mean"].data_ptr(), outs["min"].data_ptr(), outs["max"].data_ptr(),
@@ -393,14 +403,7 @@ def run_ours(args, rank, world, local_rank):
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             merge_events.append(ev)
             ev[0].record()
-            # fleet-wide merges over NCCL, all on the device, nothing read back inside the step: p95 / p99
-            # over all per-series p95 values by all-reduced key histograms (16 bits per round, digit selection by a
-            # one-CTA kernel), top-10 of the per-series maxima, sums of the additive scalars
-            fleet_out["p95_p99_of_series_p95"] = fleet.fleet_quantiles_device(d_quant[:, 1], [0.95, 0.99], fleet_rollup,
-                                                                              dist, fleet_ws)
-            fleet_out["top10_series_max"] = fleet.fleet_topk_device(outs["max"], lo, 10, dist)
-            fleet_out["sum_and_count"] = fleet.fleet_scalars_device(
-                torch.stack([outs["sum"].nansum(), d_count.sum().double()]), dist)
+            merges()
             ev[1].record()
 
     def sync_all():
