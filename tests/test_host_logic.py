@@ -124,3 +124,21 @@ def test_usage_alert_payload_equals_reference(golden_dir):
         want["content"] = ref_content
         assert msg == want and list(msg) == list(ref_msg)
         assert json.dumps(msg, ensure_ascii=False) == json.dumps(want, ensure_ascii=False)
+
+
+def test_fleet_topk_device_on_cpu_tensors():
+    """fleet_topk_device is plain torch (two stable descending sorts): the same code runs on CPU tensors."""
+    import torch
+    rng = np.random.default_rng(9)
+    v = rng.integers(0, 7, 300).astype(np.float64)
+    v[rng.random(300) < 0.1] = np.nan
+    v[5], v[200] = np.inf, -np.inf
+    tv, ti = fleet.fleet_topk_device(torch.from_numpy(v), 40, 12)
+    keys = np.where(np.isnan(v), -np.inf, v)
+    order = np.argsort(-keys, kind="stable")[:12]
+    assert np.array_equal(ti.numpy(), order + 40)
+    assert np.array_equal(tv.numpy(), keys[order])
+    tv, ti = fleet.fleet_topk_device(torch.tensor([np.nan, 2.5], dtype=torch.float64), 0, 3)
+    assert ti.tolist() == [1, -1, -1] and tv.tolist()[0] == 2.5
+    tv, ti = fleet.fleet_topk_device(torch.zeros(0, dtype=torch.float64), 0, 2)
+    assert ti.tolist() == [-1, -1]
