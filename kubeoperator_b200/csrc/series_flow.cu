@@ -268,7 +268,7 @@ __device__ __forceinline__ void ring_slot(uint32_t grp, bool single, uint32_t& s
 }
 __device__ __forceinline__ void wait_group_full(const FlowSmem& sm, uint32_t grp, bool single) {
     volatile unsigned* iss = sm.issued();
-    while (*iss <= grp) __nanosleep(64);
+    while (*iss <= grp) __nanosleep(20);
     uint32_t s, u;
     ring_slot(grp, single, s, u);
     mbar_wait(sm.bar(FB_FULL + (int)s), u & 1u);
