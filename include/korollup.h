@@ -74,7 +74,8 @@ int ko_unpin(void* ptr);
  * with count = nodes - #{cpu_usage==0 and mem_usage==0} (:174-175; sums are left undivided when
  * count==0, :180); out_alert_flag[i]=1 where the reference enters the alert branch :176 (usage >
  * threshold, evaluated only for nodes that are not all-zero).  cluster_of_node must be non-decreasing
- * (nodes grouped by cluster, as the reference visits them).  out_band_* (may be NULL) give the UI colour
+ * (nodes grouped by cluster, as the reference visits them).  The sums are taken node by node in input order,
+ * so the four floats equal the reference's bit for bit.  out_band_* (may be NULL) give the UI colour
  * band of usage*100 per node: ui/src/app/shared/pipe/progress-color.pipe.ts:8-23. */
 int ko_cluster_rollup(ko_ctx* ctx, const double* cpu, const double* mem, const double* cpu_usage,
                       const double* mem_usage, const int32_t* cluster_of_node, int64_t n_nodes,

@@ -51,7 +51,10 @@ __global__ void node_flags(const double* __restrict__ cu, const double* __restri
     if (k < 0 || k >= n_clusters || (i > 0 && cl[i - 1] > k)) atomicExch(err, 1);
 }
 
-// cluster_monitor.py:163-173,180-182: one warp per cluster over its contiguous node range
+// cluster_monitor.py:163-173,180-182: one warp per cluster over its contiguous node range.  The four sums are taken in
+// NODE ORDER, like the reference's loop (x = x + float(...), :170-173), so that the floats of the blob are the
+// reference's to the last bit: the warp loads 32 nodes at a time (coalesced) into shared memory and lane 0 adds them
+// one after the other - four independent chains, about ten cycles per node.
 __global__ void cluster_reduce(const double* __restrict__ cpu, const double* __restrict__ mem,
                                const double* __restrict__ cu, const double* __restrict__ mu,
                                const int32_t* __restrict__ cl, int64_t n, int32_t n_clusters,
@@ -72,20 +75,32 @@ __global__ void cluster_reduce(const double* __restrict__ cpu, const double* __r
         if (cl[mid] <= (int32_t)c) lo = mid + 1; else hi = mid;
     }
     const int64_t e = lo;
+    __shared__ double stage[8][4][32];   // per warp of the block: 32 nodes x 4 columns
+    double (*st)[32] = stage[(threadIdx.x >> 5) & 7];
     double s_cpu = 0, s_mem = 0, s_cu = 0, s_mu = 0;
     long long zeros = 0;
-    for (int64_t i = b + lane; i < e; i += 32) {
-        const double a = cu[i], m = mu[i];
-        s_cpu += cpu[i];
-        s_mem += mem[i];
-        s_cu += a;
-        s_mu += m;
-        zeros += (a == 0.0 && m == 0.0) ? 1 : 0;
+    for (int64_t i0 = b; i0 < e; i0 += 32) {
+        const int64_t i = i0 + lane;
+        if (i < e) {
+            const double a = cu[i], m = mu[i];
+            st[0][lane] = cpu[i];
+            st[1][lane] = mem[i];
+            st[2][lane] = a;
+            st[3][lane] = m;
+            zeros += (a == 0.0 && m == 0.0) ? 1 : 0;
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const int cnt = (int)((e - i0) < 32 ? (e - i0) : 32);
+            for (int k = 0; k < cnt; ++k) {
+                s_cpu += st[0][k];
+                s_mem += st[1][k];
+                s_cu += st[2][k];
+                s_mu += st[3][k];
+            }
+        }
+        __syncwarp();
     }
-    s_cpu = wsum(s_cpu);
-    s_mem = wsum(s_mem);
-    s_cu = wsum(s_cu);
-    s_mu = wsum(s_mu);
     zeros = wsum_ll(zeros);
     if (lane == 0) {
         const long long count = (long long)(e - b) - zeros;
@@ -109,16 +124,35 @@ __global__ void fleet_rollup_kernel(const int64_t* __restrict__ counts, const do
     const int lane = threadIdx.x;
     long long pods = 0, ns = 0, dep = 0, cont = 0, nodes = 0, maxpod = 0, zero = 0;
     double ct = 0, mt = 0, cu = 0, mu = 0;
+    // the four float sums in CLUSTER ORDER (the UI's forEach, dashboard.component.ts:121-133): lane 0 adds what the
+    // warp staged in shared memory, 32 clusters at a time
+    __shared__ double st[4][32];
+    for (int64_t c0 = 0; c0 < n; c0 += 32) {
+        const int64_t c = c0 + lane;
+        if (c < n) {
+            st[0][lane] = cpu_total[c];
+            st[1][lane] = mem_total[c];
+            st[2][lane] = cpu_usage[c];
+            st[3][lane] = mem_usage[c];
+        }
+        __syncwarp();
+        if (lane == 0) {
+            const int cnt = (int)((n - c0) < 32 ? (n - c0) : 32);
+            for (int k = 0; k < cnt; ++k) {
+                ct += st[0][k];
+                mt += st[1][k];
+                cu += st[2][k];
+                mu += st[3][k];
+            }
+        }
+        __syncwarp();
+    }
     for (int64_t c = lane; c < n; c += 32) {
         pods += counts[c * 6 + 0];
         ns += counts[c * 6 + 1];
         dep += counts[c * 6 + 2];
         cont += counts[c * 6 + 3];
         nodes += counts[c * 6 + 4];
-        ct += cpu_total[c];
-        mt += mem_total[c];
-        cu += cpu_usage[c];
-        mu += mem_usage[c];
         zero += (cpu_total[c] == 0.0 && mem_total[c] == 0.0) ? 1 : 0;
         // :136-143: only a cluster the UI's own list knows adds capacity (ui_nodes >= 0 = cluster.nodes.length);
         // MAX_PODS === undefined (passed as a negative value) means 110, a configured 0 stays 0
@@ -128,7 +162,6 @@ __global__ void fleet_rollup_kernel(const int64_t* __restrict__ counts, const do
     }
     pods = wsum_ll(pods); ns = wsum_ll(ns); dep = wsum_ll(dep); cont = wsum_ll(cont);
     nodes = wsum_ll(nodes); maxpod = wsum_ll(maxpod); zero = wsum_ll(zero);
-    ct = wsum(ct); mt = wsum(mt); cu = wsum(cu); mu = wsum(mu);
     if (lane == 0) {
         const long long count = (long long)n - zero;
         if (count > 0) {
